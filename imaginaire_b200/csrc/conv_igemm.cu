@@ -1,0 +1,485 @@
+// Implicit-GEMM convolution on the 5th-generation tensor cores (SURVEY.md section 8
+// rows a4, a6): tcgen05.mma with fp32 accumulators in TMEM, operands staged by TMA.
+//
+// ref: torch.nn.Conv2d inside Conv2dBlock  imaginaire/layers/conv.py:93-104, 262-327
+//      SPADE gamma/beta projection + modulation  imaginaire/layers/activation_norm.py:226-233
+//
+// GEMM view:  D[pixel, co] = sum_{kh,kw,ci} A[pixel @ tap(kh,kw), ci] * B[co, (kh,kw,ci)]
+//   M tile = 128 output pixels = a (th x tw) spatial patch of one image (tw * th = 128),
+//   N tile = BN output channels (32..256),  K step = one filter tap x 64 input channels.
+// The A tile of a tap is ONE 4-D TMA box {64 ch, tw, th, 1} of the NHWC activation at the
+// tap's spatial offset: the zero padding (and any ragged edge) is TMA out-of-bounds fill,
+// so no im2col buffer and no halo logic exist.  Stride-2 convolutions use the tensor map's
+// element strides.  The B tile is a {64, 1, BN} box of the packed filter
+// [Cout][KH*KW][Cin_p].  Both land in shared memory in the 128-byte-swizzled K-major
+// layout that tcgen05.mma consumes directly.
+//
+// Warp roles (256 threads, persistent CTAs, one per SM):
+//   warp 0   TMA producer (one lane)            smem ring: full[]/empty[] mbarriers
+//   warp 1   MMA issuer (one lane)              tcgen05.commit -> empty[] / tmem_full[]
+//   warp 2   TMEM allocator
+//   warps 4-7 epilogue: tcgen05.ld -> bias/act/residual/(SPADE modulation) -> global
+// TMEM holds two accumulator stages (2 x BN columns) so the epilogue of tile i overlaps
+// the main loop of tile i+1.
+#include "imx_common.cuh"
+#include "imx_ptx.cuh"
+#include "../../include/imx.h"
+
+#include "imx_tma_host.cuh"
+
+namespace {
+
+using namespace imx::ptx;
+using imx::encode_tmap;
+using imx::num_sms;
+
+constexpr int BM = 128;          // pixels per tile
+constexpr int BK = 64;           // channels per K step (128 bytes of bf16: one swizzle row)
+constexpr int UMMA_K = 16;
+constexpr int kThreads = 256;
+constexpr int kEpiWarp0 = 4;     // first epilogue warp (warp % 4 == TMEM lane quarter)
+constexpr int A_BYTES = BM * BK * 2;
+
+template <int BN> struct Cfg {
+    static constexpr int B_BYTES = BN * BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+    static constexpr int TMEM_COLS = (2 * BN < 32) ? 32 : 2 * BN;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+struct ConvArgs {
+    // geometry
+    int N, H, W, Ho, Wo;
+    int Cout, Cout_p;
+    int KH, KW, stride, pad;
+    int tw_log2, tw, th;
+    int tiles_x, tiles_y, tiles_n, total_tiles;
+    int kc_blocks;
+    int flags;
+    // plain epilogue
+    const float* bias;
+    const uint16_t* residual;
+    void* out;
+    float* stats;
+    // SPADE-fused epilogue (mode 1)
+    const float* bias_beta;
+    const uint16_t* x;
+    const float* mean;
+    const float* rstd;
+    const float* nw;
+    const float* nb;
+    int C, per_instance, act, up2x;
+};
+
+__device__ __forceinline__ float act_apply(float v, int act) {
+    if (act == 1) return v > 0.0f ? v : 0.2f * v;
+    if (act == 2) return fmaxf(v, 0.0f);
+    return v;
+}
+
+// kMode 0: plain conv epilogue.   kMode 1: SPADE gamma/beta projection + modulation.
+template <int BN, int kMode>
+__global__ void __launch_bounds__(kThreads, 1)
+conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                  const ConvArgs p) {
+    using C = Cfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    // 128-byte swizzle atoms must sit on 1024-byte boundaries.
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem_a = smem;
+    uint8_t* smem_b = smem + C::STAGES * A_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+    uint64_t* full_bar = bars;
+    uint64_t* empty_bar = bars + C::STAGES;
+    uint64_t* tmem_full = bars + 2 * C::STAGES;
+    uint64_t* tmem_empty = bars + 2 * C::STAGES + 2;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * C::STAGES + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmap_a);
+        prefetch_tmap(&tmap_b);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < C::STAGES; ++i) {
+            mbar_init(&full_bar[i], 1);
+            mbar_init(&empty_bar[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&tmem_full[i], 1);
+            mbar_init(&tmem_empty[i], 4 * 32);
+        }
+        fence_mbar_init();
+    }
+    if (warp == 2) tmem_alloc(tmem_ptr, C::TMEM_COLS);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    const int taps = p.KH * p.KW;
+    const int k_iters = taps * p.kc_blocks;
+    const int tiles_per_img = p.tiles_x * p.tiles_y;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ===== TMA producer =====
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+                const int n_tile = tile % p.tiles_n;
+                const int m_tile = tile / p.tiles_n;
+                const int img = m_tile / tiles_per_img;
+                const int rem = m_tile - img * tiles_per_img;
+                const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
+                const int iy0 = ty * p.th * p.stride - p.pad;
+                const int ix0 = tx * p.tw * p.stride - p.pad;
+                const int n0 = n_tile * BN;
+                for (int tap = 0; tap < taps; ++tap) {
+                    const int kh = tap / p.KW, kw = tap - kh * p.KW;
+                    for (int kc = 0; kc < p.kc_blocks; ++kc) {
+                        mbar_wait(&empty_bar[stage], phase ^ 1);
+                        mbar_arrive_expect_tx(&full_bar[stage], C::STAGE_BYTES);
+                        tma_load_4d(smem_a + stage * A_BYTES, &tmap_a, &full_bar[stage], kc * BK, ix0 + kw, iy0 + kh, img);
+                        tma_load_3d(smem_b + stage * C::B_BYTES, &tmap_b, &full_bar[stage], kc * BK, tap, n0);
+                        if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ===== MMA issuer =====
+            constexpr uint32_t idesc = make_idesc_bf16_f32(BM, BN);
+            int stage = 0;
+            uint32_t phase = 0;
+            int iter = 0;
+            for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++iter) {
+                const int as = iter & 1;
+                const uint32_t aphase = (iter >> 1) & 1;
+                mbar_wait(&tmem_empty[as], aphase ^ 1);
+                tc_fence_after_sync();
+                const uint32_t d_tmem = tmem_base + as * BN;
+                for (int k = 0; k < k_iters; ++k) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after_sync();
+                    const uint64_t da = make_kmajor_sw128_desc(smem_u32(smem_a + stage * A_BYTES));
+                    const uint64_t db = make_kmajor_sw128_desc(smem_u32(smem_b + stage * C::B_BYTES));
+#pragma unroll
+                    for (int j = 0; j < BK / UMMA_K; ++j) {
+                        // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in (addr >> 4)
+                        umma_bf16_ss(d_tmem, da + 2 * j, db + 2 * j, idesc, (k | j) != 0);
+                    }
+                    umma_commit(&empty_bar[stage]);
+                    if (k == k_iters - 1) umma_commit(&tmem_full[as]);
+                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp >= kEpiWarp0) {
+        // ===== epilogue =====
+        const int q = warp & 3;                 // TMEM lane quarter owned by this warp
+        const int row = q * 32 + lane;          // row of the 128-pixel tile
+        const int pr = row >> p.tw_log2, pc = row & (p.tw - 1);
+        int iter = 0;
+        for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++iter) {
+            const int as = iter & 1;
+            const uint32_t aphase = (iter >> 1) & 1;
+            const int n_tile = tile % p.tiles_n;
+            const int m_tile = tile / p.tiles_n;
+            const int img = m_tile / tiles_per_img;
+            const int rem = m_tile - img * tiles_per_img;
+            const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
+            const int oy = ty * p.th + pr, ox = tx * p.tw + pc;
+            const bool valid = (oy < p.Ho) && (ox < p.Wo);
+            const size_t pix = ((size_t)img * p.Ho + oy) * p.Wo + ox;
+            const int n0 = n_tile * BN;
+
+            mbar_wait(&tmem_full[as], aphase);
+            tc_fence_after_sync();
+            const uint32_t t_acc = tmem_base + as * BN + (static_cast<uint32_t>(q * 32) << 16);
+
+            if constexpr (kMode == 0) {
+#pragma unroll 1
+                for (int ch = 0; ch < BN / 32; ++ch) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(t_acc + ch * 32, v);
+                    tmem_ld_wait();
+                    if (ch == BN / 32 - 1) {
+                        // accumulator fully drained into registers: hand the TMEM stage back
+                        tc_fence_before_sync();
+                        mbar_arrive(&tmem_empty[as]);
+                    }
+                    const int nb = n0 + ch * 32;
+                    if (nb >= p.Cout_p) continue;   // warp-uniform
+                    float f[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+                    if (p.flags & IMX_EPI_BIAS) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (nb + j < p.Cout) f[j] += __ldg(p.bias + nb + j);
+                    }
+                    if ((p.flags & IMX_EPI_RESIDUAL) && valid) {
+                        const uint4* r = reinterpret_cast<const uint4*>(p.residual + pix * p.Cout_p + nb);
+#pragma unroll
+                        for (int g = 0; g < 4; ++g) {
+                            if (nb + g * 8 < p.Cout_p) {
+                                const uint4 rv = __ldg(r + g);
+                                f[g * 8 + 0] += imx::bf16_lo(rv.x); f[g * 8 + 1] += imx::bf16_hi(rv.x);
+                                f[g * 8 + 2] += imx::bf16_lo(rv.y); f[g * 8 + 3] += imx::bf16_hi(rv.y);
+                                f[g * 8 + 4] += imx::bf16_lo(rv.z); f[g * 8 + 5] += imx::bf16_hi(rv.z);
+                                f[g * 8 + 6] += imx::bf16_lo(rv.w); f[g * 8 + 7] += imx::bf16_hi(rv.w);
+                            }
+                        }
+                    }
+                    if (p.flags & IMX_EPI_LRELU) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) f[j] = f[j] > 0.0f ? f[j] : 0.2f * f[j];
+                    }
+                    if (p.flags & IMX_EPI_RELU) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.0f);
+                    }
+                    if (p.flags & IMX_EPI_TANH) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) f[j] = tanhf(f[j]);
+                    }
+                    if (p.flags & IMX_EPI_OUT_F32) {
+                        if (valid) {
+                            float4* o = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + pix * p.Cout_p + nb);
+#pragma unroll
+                            for (int g = 0; g < 8; ++g)
+                                if (nb + g * 4 < p.Cout_p) o[g] = make_float4(f[g * 4], f[g * 4 + 1], f[g * 4 + 2], f[g * 4 + 3]);
+                        }
+                    } else {
+                        uint32_t o[16];
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) o[j] = imx::pack_bf16(f[2 * j], f[2 * j + 1]);
+                        if (valid) {
+                            uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.out) + pix * p.Cout_p + nb);
+#pragma unroll
+                            for (int g = 0; g < 4; ++g)
+                                if (nb + g * 8 < p.Cout_p) dst[g] = make_uint4(o[4 * g], o[4 * g + 1], o[4 * g + 2], o[4 * g + 3]);
+                        }
+                        if (p.flags & IMX_EPI_STATS) {
+                            // statistics of the values as stored (bf16-rounded), so a later
+                            // normalisation of the stored tensor is self-consistent
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) {
+                                f[2 * j] = valid ? imx::bf16_lo(o[j]) : 0.0f;
+                                f[2 * j + 1] = valid ? imx::bf16_hi(o[j]) : 0.0f;
+                            }
+                        }
+                    }
+                    if (p.flags & IMX_EPI_STATS) {
+                        if (p.flags & IMX_EPI_OUT_F32) {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) f[j] = valid ? f[j] : 0.0f;
+                        }
+                        float s_mine = 0.0f, q_mine = 0.0f;
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const float s = imx::warp_sum(f[j]);
+                            const float qq = imx::warp_sum(f[j] * f[j]);
+                            if (lane == j) { s_mine = s; q_mine = qq; }
+                        }
+                        if (nb + lane < p.Cout) {
+                            atomicAdd(p.stats + nb + lane, s_mine);
+                            atomicAdd(p.stats + p.Cout + nb + lane, q_mine);
+                        }
+                    }
+                }
+            } else {
+                // ---- SPADE: columns [g*128, g*128+64) = gamma, [g*128+64, g*128+128) = beta of
+                //      channels c0 + [0, 64);  y = act(((x-mean)*rstd*w+b) * (1+gamma) + beta)
+                const int oyx = p.up2x ? (oy >> 1) : oy, oxx = p.up2x ? (ox >> 1) : ox;
+                const int Hx = p.up2x ? (p.Ho >> 1) : p.Ho, Wx = p.up2x ? (p.Wo >> 1) : p.Wo;
+                const size_t xpix = ((size_t)img * Hx + oyx) * Wx + oxx;
+#pragma unroll 1
+                for (int g = 0; g < BN / 128; ++g) {
+                    const int c0 = (n0 / 128 + g) * 64;
+#pragma unroll 1
+                    for (int h = 0; h < 2; ++h) {
+                        uint32_t vg[32], vb[32];
+                        tmem_ld_32x32(t_acc + g * 128 + h * 32, vg);
+                        tmem_ld_32x32(t_acc + g * 128 + 64 + h * 32, vb);
+                        tmem_ld_wait();
+                        if (g == BN / 128 - 1 && h == 1) {
+                            tc_fence_before_sync();
+                            mbar_arrive(&tmem_empty[as]);
+                        }
+                        const int cb = c0 + h * 32;
+                        if (cb >= p.C) continue;   // warp-uniform (C % 32 == 0 enforced on the host)
+                        uint32_t xr[16];
+                        if (valid) {
+                            const uint4* xp = reinterpret_cast<const uint4*>(p.x + xpix * p.C + cb);
+#pragma unroll
+                            for (int t = 0; t < 4; ++t) {
+                                const uint4 xv = __ldg(xp + t);
+                                xr[4 * t] = xv.x; xr[4 * t + 1] = xv.y; xr[4 * t + 2] = xv.z; xr[4 * t + 3] = xv.w;
+                            }
+                        } else {
+#pragma unroll
+                            for (int t = 0; t < 16; ++t) xr[t] = 0u;
+                        }
+                        const int so = (p.per_instance ? img * p.C : 0) + cb;
+                        uint32_t o[16];
+#pragma unroll
+                        for (int j = 0; j < 32; j += 2) {
+                            float y2[2];
+#pragma unroll
+                            for (int e = 0; e < 2; ++e) {
+                                const int c = j + e;
+                                const float xv = e == 0 ? imx::bf16_lo(xr[j >> 1]) : imx::bf16_hi(xr[j >> 1]);
+                                const float m = __ldg(p.mean + so + c), rs = __ldg(p.rstd + so + c);
+                                float xh = (xv - m) * rs;
+                                if (p.nw) xh = fmaf(xh, __ldg(p.nw + cb + c), p.nb ? __ldg(p.nb + cb + c) : 0.0f);
+                                float gam = __uint_as_float(vg[c]), bet = __uint_as_float(vb[c]);
+                                if (p.bias) gam += __ldg(p.bias + cb + c);
+                                if (p.bias_beta) bet += __ldg(p.bias_beta + cb + c);
+                                y2[e] = act_apply(fmaf(xh, 1.0f + gam, bet), p.act);
+                            }
+                            o[j >> 1] = imx::pack_bf16(y2[0], y2[1]);
+                        }
+                        if (valid) {
+                            uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.out) + pix * p.C + cb);
+#pragma unroll
+                            for (int t = 0; t < 4; ++t) dst[t] = make_uint4(o[4 * t], o[4 * t + 1], o[4 * t + 2], o[4 * t + 3]);
+                        }
+                    }
+                }
+            }
+        }
+    }
+
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after_sync();
+        tmem_dealloc(tmem_base, C::TMEM_COLS);
+    }
+}
+
+// ------------------------------------------------------------------ host side
+
+template <int BN, int kMode>
+int launch(const CUtensorMap& ta, const CUtensorMap& tb, const ConvArgs& a, cudaStream_t stream) {
+    using C = Cfg<BN>;
+    static bool attr_set = false;   // per (BN, mode) instantiation
+    auto kern = conv_igemm_kernel<BN, kMode>;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
+        if (e != cudaSuccess) return imx::set_error((int)e, "conv_igemm: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        attr_set = true;
+    }
+    const int grid = a.total_tiles < num_sms() ? a.total_tiles : num_sms();
+    kern<<<grid, kThreads, C::SMEM_BYTES, stream>>>(ta, tb, a);
+    return imx::check_launch("conv_igemm");
+}
+
+// Common geometry + tensor maps.  `rows_b` = number of rows of the packed filter matrix.
+int setup(ConvArgs& a, CUtensorMap& ta, CUtensorMap& tb, const void* x, const void* wpk, int N, int H, int W,
+          int Cin_p, int rows_b, int KH, int KW, int stride, int pad, int BN) {
+    a.N = N; a.H = H; a.W = W;
+    a.KH = KH; a.KW = KW; a.stride = stride; a.pad = pad;
+    a.Ho = (H + 2 * pad - KH) / stride + 1;
+    a.Wo = (W + 2 * pad - KW) / stride + 1;
+    if (a.Ho <= 0 || a.Wo <= 0) return imx::set_error(IMX_ERR_INVALID_ARG, "conv_igemm: empty output (%d x %d)", a.Ho, a.Wo);
+    // pixel tile: tw = largest power of two <= min(Wo, 128) (at least 8 so th <= 16), th = 128 / tw
+    int tw = 128;
+    while (tw > 8 && tw > a.Wo) tw >>= 1;
+    a.tw = tw; a.th = BM / tw;
+    a.tw_log2 = 0;
+    while ((1 << a.tw_log2) < tw) ++a.tw_log2;
+    a.tiles_x = (a.Wo + a.tw - 1) / a.tw;
+    a.tiles_y = (a.Ho + a.th - 1) / a.th;
+    a.tiles_n = (rows_b + BN - 1) / BN;
+    const long total = (long)N * a.tiles_x * a.tiles_y * a.tiles_n;
+    if (total > 0x7fffffffL) return imx::set_error(IMX_ERR_TOO_LARGE, "conv_igemm: too many tiles");
+    a.total_tiles = (int)total;
+    a.kc_blocks = (Cin_p + BK - 1) / BK;
+
+    const uint64_t dims_a[4] = {(uint64_t)Cin_p, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+    const uint64_t str_a[3] = {(uint64_t)Cin_p * 2, (uint64_t)W * Cin_p * 2, (uint64_t)H * W * Cin_p * 2};
+    const uint32_t box_a[4] = {(uint32_t)BK, (uint32_t)((a.tw - 1) * stride + 1), (uint32_t)((a.th - 1) * stride + 1), 1u};
+    const uint32_t es_a[4] = {1u, (uint32_t)stride, (uint32_t)stride, 1u};
+    if (box_a[1] > 256 || box_a[2] > 256) return imx::set_error(IMX_ERR_UNSUPPORTED, "conv_igemm: TMA box too large for stride %d", stride);
+    int rc = encode_tmap(&ta, x, 4, dims_a, str_a, box_a, es_a);
+    if (rc) return rc;
+    const uint64_t dims_b[3] = {(uint64_t)Cin_p, (uint64_t)(KH * KW), (uint64_t)rows_b};
+    const uint64_t str_b[2] = {(uint64_t)Cin_p * 2, (uint64_t)KH * KW * Cin_p * 2};
+    const uint32_t box_b[3] = {(uint32_t)BK, 1u, (uint32_t)BN};
+    const uint32_t es_b[3] = {1u, 1u, 1u};
+    return encode_tmap(&tb, wpk, 3, dims_b, str_b, box_b, es_b);
+}
+
+using imx::aligned16;
+
+}  // namespace
+
+extern "C" int imx_conv2d_igemm_fprop_bf16(const imx_bf16* x, const imx_bf16* wpk, const float* bias,
+                                           const imx_bf16* residual, void* out, float* stats,
+                                           int N, int H, int W, int Cin_p,
+                                           int Cout, int Cout_p, int KH, int KW,
+                                           int stride, int pad, int flags, imx_stream_t stream) {
+    IMX_REQUIRE(x && wpk && out, "conv2d_fprop: null pointer");
+    IMX_REQUIRE(N >= 0 && H > 0 && W > 0, "conv2d_fprop: bad input size");
+    IMX_REQUIRE(Cin_p > 0 && Cin_p % 8 == 0, "conv2d_fprop: Cin_p (%d) must be a positive multiple of 8", Cin_p);
+    IMX_REQUIRE(Cout > 0 && Cout_p >= Cout && Cout_p % 8 == 0, "conv2d_fprop: Cout_p (%d) must be >= Cout (%d) and a multiple of 8", Cout_p, Cout);
+    IMX_REQUIRE(KH > 0 && KW > 0 && KH <= 16 && KW <= 16, "conv2d_fprop: bad kernel size");
+    IMX_REQUIRE(stride >= 1 && stride <= 2 && pad >= 0, "conv2d_fprop: stride must be 1 or 2, pad >= 0");
+    IMX_REQUIRE(!(flags & IMX_EPI_BIAS) || bias, "conv2d_fprop: bias flag without bias");
+    IMX_REQUIRE(!(flags & IMX_EPI_RESIDUAL) || residual, "conv2d_fprop: residual flag without residual");
+    IMX_REQUIRE(!(flags & IMX_EPI_STATS) || stats, "conv2d_fprop: stats flag without stats buffer");
+    IMX_REQUIRE(aligned16(x) && aligned16(wpk) && aligned16(out) && aligned16(residual), "conv2d_fprop: pointers must be 16-byte aligned");
+    if (N == 0) return IMX_OK;
+    const int BN = Cout_p > 128 ? 256 : (Cout_p > 64 ? 128 : (Cout_p > 32 ? 64 : 32));
+    ConvArgs a{};
+    CUtensorMap ta, tb;
+    int rc = setup(a, ta, tb, x, wpk, N, H, W, Cin_p, Cout, KH, KW, stride, pad, BN);
+    if (rc) return rc;
+    a.Cout = Cout; a.Cout_p = Cout_p; a.flags = flags;
+    a.bias = bias; a.residual = residual; a.out = out; a.stats = stats;
+    cudaStream_t s = (cudaStream_t)stream;
+    switch (BN) {
+        case 256: return launch<256, 0>(ta, tb, a, s);
+        case 128: return launch<128, 0>(ta, tb, a, s);
+        case 64: return launch<64, 0>(ta, tb, a, s);
+        default: return launch<32, 0>(ta, tb, a, s);
+    }
+}
+
+extern "C" int imx_spade_gb_conv_modulate_bf16(const imx_bf16* hidden, const imx_bf16* wgb,
+                                               const float* bias_gamma, const float* bias_beta,
+                                               const imx_bf16* x, const float* mean, const float* rstd,
+                                               const float* w, const float* b, imx_bf16* y,
+                                               int N, int H, int W, int Ch_p, int C, int KH, int KW, int pad,
+                                               int stats_per_instance, int act, int up2x,
+                                               imx_stream_t stream) {
+    IMX_REQUIRE(hidden && wgb && x && mean && rstd && y, "spade_gb_conv_modulate: null pointer");
+    IMX_REQUIRE(N >= 0 && H > 0 && W > 0, "spade_gb_conv_modulate: bad size");
+    IMX_REQUIRE(Ch_p > 0 && Ch_p % 8 == 0, "spade_gb_conv_modulate: Ch_p must be a positive multiple of 8");
+    IMX_REQUIRE(C > 0 && C % 32 == 0, "spade_gb_conv_modulate: C (%d) must be a multiple of 32", C);
+    IMX_REQUIRE(KH > 0 && KW > 0 && KH <= 16 && KW <= 16 && pad >= 0, "spade_gb_conv_modulate: bad kernel size");
+    IMX_REQUIRE(2 * pad == KH - 1 && 2 * pad == KW - 1, "spade_gb_conv_modulate: needs a 'same' convolution (pad = (K-1)/2)");
+    IMX_REQUIRE(act >= 0 && act <= 2, "spade_gb_conv_modulate: bad act");
+    IMX_REQUIRE(!up2x || (H % 2 == 0 && W % 2 == 0), "spade_gb_conv_modulate: up2x needs even H, W");
+    IMX_REQUIRE((w != nullptr) || (b == nullptr), "spade_gb_conv_modulate: norm bias without norm weight");
+    IMX_REQUIRE(aligned16(hidden) && aligned16(wgb) && aligned16(x) && aligned16(y), "spade_gb_conv_modulate: pointers must be 16-byte aligned");
+    if (N == 0) return IMX_OK;
+    const int rows_b = 2 * ((C + 63) / 64 * 64);
+    const int BN = rows_b >= 256 ? 256 : 128;
+    ConvArgs a{};
+    CUtensorMap ta, tb;
+    int rc = setup(a, ta, tb, hidden, wgb, N, H, W, Ch_p, rows_b, KH, KW, 1, pad, BN);
+    if (rc) return rc;
+    a.out = y; a.bias = bias_gamma; a.bias_beta = bias_beta;
+    a.x = x; a.mean = mean; a.rstd = rstd; a.nw = w; a.nb = b;
+    a.C = C; a.per_instance = stats_per_instance; a.act = act; a.up2x = up2x;
+    cudaStream_t s = (cudaStream_t)stream;
+    return BN == 256 ? launch<256, 1>(ta, tb, a, s) : launch<128, 1>(ta, tb, a, s);
+}

@@ -1,0 +1,371 @@
+// Convolution weight gradient as an implicit GEMM on tcgen05 (SURVEY.md section 8 rows
+// a4, a6, backward): for every filter tap
+//     dW[co, tap, ci] = sum_{pixels} dY[pixel, co] * X[pixel @ tap, ci]
+// i.e. M = Cout (128-row tiles), N = Cin (<= 256), K = N*Ho*Wo output pixels.
+//
+// ref: autograd of torch.nn.Conv2d inside Conv2dBlock, imaginaire/layers/conv.py:93-104
+//
+// Both operands are "MN-major" for the tensor core (the GEMM's M/N index - the channel -
+// is the contiguous one in NHWC memory), which tcgen05 reads directly from the
+// 128-byte-swizzled TMA boxes: a K step is a 64-pixel spatial patch; dY arrives as two
+// {64 co, tw, th} boxes, X as BN/64 {64 ci, tw, th} boxes at the tap's spatial offset
+// (zero padding = TMA out-of-bounds fill, stride 2 = tensor-map element strides).
+//
+// The pixel reduction is split over CTAs (split-K) so that small-channel / large-image
+// layers still fill 148 SMs; each work unit (co tile, ci tile, tap, split) writes an fp32
+// partial tile to the caller's workspace and a second kernel sums the splits into the
+// PyTorch-layout gradient [Cout][Cin][KH][KW].
+#include "imx_common.cuh"
+#include "imx_ptx.cuh"
+#include "imx_tma_host.cuh"
+#include "../../include/imx.h"
+
+namespace {
+
+using namespace imx::ptx;
+using imx::aligned16;
+using imx::encode_tmap;
+using imx::num_sms;
+
+constexpr int BM = 128;      // output channels per tile
+constexpr int BKP = 64;      // pixels per K step
+constexpr int UMMA_K = 16;
+constexpr int kThreads = 256;
+constexpr int kEpiWarp0 = 4;
+constexpr int BOX_BYTES = BKP * 64 * 2;   // one {64 ch x 64 px} box
+constexpr int A_BYTES = 2 * BOX_BYTES;
+
+template <int BN> struct WCfg {
+    static constexpr int B_BYTES = (BN / 64) * BOX_BYTES;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+    static constexpr int TMEM_COLS = 2 * BN;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+};
+
+struct WgradArgs {
+    int N, Ho, Wo;
+    int KH, KW, stride, pad;
+    int tw_log2, tw, th, tiles_x, tiles_y, ptiles;   // pixel tiles (K steps) in total
+    int co_tiles, ci_tiles, splits, total_units;
+    int co_r, ci_r;                                   // tile-rounded extents of the workspace
+    float* ws;
+};
+
+struct Unit { int co_t, ci_t, tap, split; };
+
+__device__ __forceinline__ Unit decode_unit(int u, const WgradArgs& p) {
+    Unit r;
+    const int taps = p.KH * p.KW;
+    r.split = u % p.splits; u /= p.splits;
+    r.tap = u % taps; u /= taps;
+    r.ci_t = u % p.ci_tiles;
+    r.co_t = u / p.ci_tiles;
+    return r;
+}
+
+template <int BN>
+__global__ void __launch_bounds__(kThreads, 1)
+conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_constant__ CUtensorMap tmap_x,
+                  const WgradArgs p) {
+    using C = WCfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem_a = smem;
+    uint8_t* smem_b = smem + C::STAGES * A_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+    uint64_t* full_bar = bars;
+    uint64_t* empty_bar = bars + C::STAGES;
+    uint64_t* tmem_full = bars + 2 * C::STAGES;
+    uint64_t* tmem_empty = bars + 2 * C::STAGES + 2;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * C::STAGES + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmap_dy);
+        prefetch_tmap(&tmap_x);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < C::STAGES; ++i) {
+            mbar_init(&full_bar[i], 1);
+            mbar_init(&empty_bar[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&tmem_full[i], 1);
+            mbar_init(&tmem_empty[i], 4 * 32);
+        }
+        fence_mbar_init();
+    }
+    if (warp == 2) tmem_alloc(tmem_ptr, C::TMEM_COLS);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    const int tiles_per_img = p.tiles_x * p.tiles_y;
+    // pixel tiles [k_begin, k_end) of split s
+    auto k_range = [&](int split, int& kb, int& ke) {
+        const int per = (p.ptiles + p.splits - 1) / p.splits;
+        kb = split * per;
+        ke = kb + per < p.ptiles ? kb + per : p.ptiles;
+        if (kb > ke) kb = ke;
+    };
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int u = blockIdx.x; u < p.total_units; u += gridDim.x) {
+                const Unit un = decode_unit(u, p);
+                const int kh = un.tap / p.KW, kw = un.tap - kh * p.KW;
+                int kb, ke;
+                k_range(un.split, kb, ke);
+                for (int k = kb; k < ke; ++k) {
+                    const int img = k / tiles_per_img;
+                    const int rem = k - img * tiles_per_img;
+                    const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
+                    const int oy0 = ty * p.th, ox0 = tx * p.tw;
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    mbar_arrive_expect_tx(&full_bar[stage], C::STAGE_BYTES);
+                    uint8_t* sa = smem_a + stage * A_BYTES;
+                    tma_load_4d(sa, &tmap_dy, &full_bar[stage], un.co_t * BM, ox0, oy0, img);
+                    tma_load_4d(sa + BOX_BYTES, &tmap_dy, &full_bar[stage], un.co_t * BM + 64, ox0, oy0, img);
+                    uint8_t* sb = smem_b + stage * C::B_BYTES;
+#pragma unroll
+                    for (int j = 0; j < BN / 64; ++j)
+                        tma_load_4d(sb + j * BOX_BYTES, &tmap_x, &full_bar[stage], un.ci_t * BN + j * 64,
+                                    ox0 * p.stride + kw - p.pad, oy0 * p.stride + kh - p.pad, img);
+                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc_bf16_f32(BM, BN, 1, 1);   // both operands MN-major
+            int stage = 0;
+            uint32_t phase = 0;
+            int iter = 0;
+            for (int u = blockIdx.x; u < p.total_units; u += gridDim.x, ++iter) {
+                const Unit un = decode_unit(u, p);
+                int kb, ke;
+                k_range(un.split, kb, ke);
+                const int as = iter & 1;
+                const uint32_t aphase = (iter >> 1) & 1;
+                mbar_wait(&tmem_empty[as], aphase ^ 1);
+                tc_fence_after_sync();
+                const uint32_t d_tmem = tmem_base + as * BN;
+                for (int k = kb; k < ke; ++k) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after_sync();
+                    const uint32_t a0 = smem_u32(smem_a + stage * A_BYTES);
+                    const uint32_t b0 = smem_u32(smem_b + stage * C::B_BYTES);
+#pragma unroll
+                    for (int j = 0; j < BKP / UMMA_K; ++j) {
+                        // 16 pixels = 16 rows of 128 B inside every 64-channel box
+                        const uint64_t da = make_mnmajor_sw128_desc(a0 + j * UMMA_K * 128, 1024, BOX_BYTES);
+                        const uint64_t db = make_mnmajor_sw128_desc(b0 + j * UMMA_K * 128, 1024, BOX_BYTES);
+                        umma_bf16_ss(d_tmem, da, db, idesc, (k > kb) || (j > 0));
+                    }
+                    umma_commit(&empty_bar[stage]);
+                    if (k == ke - 1) umma_commit(&tmem_full[as]);
+                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                }
+                if (kb == ke) {
+                    // empty split (cannot happen with the host's split choice; keep the
+                    // pipeline consistent anyway): nothing was accumulated
+                    umma_commit(&tmem_full[as]);
+                }
+            }
+        }
+    } else if (warp >= kEpiWarp0) {
+        const int q = warp & 3;
+        const int row = q * 32 + lane;   // output channel inside the tile
+        const int taps = p.KH * p.KW;
+        int iter = 0;
+        for (int u = blockIdx.x; u < p.total_units; u += gridDim.x, ++iter) {
+            const Unit un = decode_unit(u, p);
+            int kb, ke;
+            k_range(un.split, kb, ke);
+            const int as = iter & 1;
+            const uint32_t aphase = (iter >> 1) & 1;
+            mbar_wait(&tmem_full[as], aphase);
+            tc_fence_after_sync();
+            const uint32_t t_acc = tmem_base + as * BN + (static_cast<uint32_t>(q * 32) << 16);
+            float* dst = p.ws + ((((size_t)un.split * taps + un.tap) * p.co_r + un.co_t * BM + row) * p.ci_r) + un.ci_t * BN;
+#pragma unroll 1
+            for (int ch = 0; ch < BN / 32; ++ch) {
+                uint32_t v[32];
+                tmem_ld_32x32(t_acc + ch * 32, v);
+                tmem_ld_wait();
+                if (ch == BN / 32 - 1) {
+                    tc_fence_before_sync();
+                    mbar_arrive(&tmem_empty[as]);
+                }
+                float4* o = reinterpret_cast<float4*>(dst + ch * 32);
+#pragma unroll
+                for (int g = 0; g < 8; ++g) {
+                    float4 f;
+                    if (kb == ke) f = make_float4(0.f, 0.f, 0.f, 0.f);
+                    else f = make_float4(__uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1]),
+                                         __uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3]));
+                    o[g] = f;
+                }
+            }
+        }
+    }
+
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after_sync();
+        tmem_dealloc(tmem_base, C::TMEM_COLS);
+    }
+}
+
+// dw[co][ci][kh][kw] = sum_split ws[split][tap][co][ci]
+__global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw, int Cout, int Cin,
+                                    int taps, int splits, int co_r, int ci_r) {
+    const long total = (long)Cout * Cin * taps;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        // consecutive threads -> consecutive ci (coalesced workspace reads)
+        const int ci = (int)(i % Cin);
+        long t = i / Cin;
+        const int tap = (int)(t % taps);
+        const int co = (int)(t / taps);
+        float acc = 0.0f;
+        for (int s = 0; s < splits; ++s)
+            acc += __ldg(ws + (((size_t)s * taps + tap) * co_r + co) * ci_r + ci);
+        dw[((size_t)co * Cin + ci) * taps + tap] = acc;
+    }
+}
+
+struct Plan {
+    int BN, Ho, Wo, tw, th, tw_log2, tiles_x, tiles_y, ptiles, co_tiles, ci_tiles, splits;
+    long ws_floats;
+};
+
+int make_plan(Plan& pl, int N, int H, int W, int Cin_p, int Cout_p, int KH, int KW, int stride, int pad) {
+    pl.Ho = (H + 2 * pad - KH) / stride + 1;
+    pl.Wo = (W + 2 * pad - KW) / stride + 1;
+    if (pl.Ho <= 0 || pl.Wo <= 0) return imx::set_error(IMX_ERR_INVALID_ARG, "conv2d_wgrad: empty output");
+    pl.BN = Cin_p > 128 ? 256 : (Cin_p > 64 ? 128 : 64);
+    int tw = 64;
+    while (tw > 8 && tw > pl.Wo) tw >>= 1;
+    pl.tw = tw; pl.th = BKP / tw;
+    pl.tw_log2 = 0;
+    while ((1 << pl.tw_log2) < tw) ++pl.tw_log2;
+    pl.tiles_x = (pl.Wo + pl.tw - 1) / pl.tw;
+    pl.tiles_y = (pl.Ho + pl.th - 1) / pl.th;
+    const long ptiles = (long)N * pl.tiles_x * pl.tiles_y;
+    if (ptiles > 0x7fffffffL) return imx::set_error(IMX_ERR_TOO_LARGE, "conv2d_wgrad: too many pixel tiles");
+    pl.ptiles = (int)ptiles;
+    pl.co_tiles = (Cout_p + BM - 1) / BM;
+    pl.ci_tiles = (Cin_p + pl.BN - 1) / pl.BN;
+    const long base_units = (long)pl.co_tiles * pl.ci_tiles * KH * KW;
+    // enough units for ~2 waves, but keep at least 8 K steps per unit
+    long splits = (2L * imx::kNumSMs + base_units - 1) / base_units;
+    long max_splits = ptiles / 8 > 1 ? ptiles / 8 : 1;
+    if (splits > max_splits) splits = max_splits;
+    if (splits < 1) splits = 1;
+    // no empty splits: per = ceil(ptiles / splits) must leave work for the last split
+    while (splits > 1 && (splits - 1) * ((ptiles + splits - 1) / splits) >= ptiles) --splits;
+    pl.splits = (int)splits;
+    pl.ws_floats = splits * KH * KW * (long)pl.co_tiles * BM * (long)pl.ci_tiles * pl.BN;
+    return IMX_OK;
+}
+
+template <int BN>
+int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const WgradArgs& a, cudaStream_t stream) {
+    using C = WCfg<BN>;
+    auto kern = conv_wgrad_kernel<BN>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
+        if (e != cudaSuccess) return imx::set_error((int)e, "conv2d_wgrad: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        attr_set = true;
+    }
+    const int grid = a.total_units < num_sms() ? a.total_units : num_sms();
+    kern<<<grid, kThreads, C::SMEM_BYTES, stream>>>(tdy, tx, a);
+    return imx::check_launch("conv2d_wgrad");
+}
+
+int check_wgrad_args(int N, int H, int W, int Cin, int Cin_p, int Cout, int Cout_p, int KH, int KW, int stride, int pad) {
+    IMX_REQUIRE(N >= 0 && H > 0 && W > 0, "conv2d_wgrad: bad input size");
+    IMX_REQUIRE(Cin > 0 && Cin_p >= Cin && Cin_p % 8 == 0, "conv2d_wgrad: Cin_p must be >= Cin and a multiple of 8");
+    IMX_REQUIRE(Cout > 0 && Cout_p >= Cout && Cout_p % 8 == 0, "conv2d_wgrad: Cout_p must be >= Cout and a multiple of 8");
+    IMX_REQUIRE(KH > 0 && KW > 0 && KH <= 16 && KW <= 16, "conv2d_wgrad: bad kernel size");
+    IMX_REQUIRE(stride >= 1 && stride <= 2 && pad >= 0, "conv2d_wgrad: stride must be 1 or 2, pad >= 0");
+    return IMX_OK;
+}
+
+}  // namespace
+
+extern "C" int64_t imx_conv2d_wgrad_workspace_bytes(int N, int H, int W, int Cin, int Cin_p,
+                                                    int Cout, int Cout_p, int KH, int KW,
+                                                    int stride, int pad) {
+    if (check_wgrad_args(N, H, W, Cin, Cin_p, Cout, Cout_p, KH, KW, stride, pad)) return -1;
+    if (N == 0) return 0;
+    Plan pl;
+    if (make_plan(pl, N, H, W, Cin_p, Cout_p, KH, KW, stride, pad)) return -1;
+    return pl.ws_floats * 4;
+}
+
+extern "C" int imx_conv2d_igemm_wgrad_bf16(const imx_bf16* x, const imx_bf16* dy, float* dw,
+                                           void* workspace, int64_t workspace_bytes,
+                                           int N, int H, int W, int Cin, int Cin_p,
+                                           int Cout, int Cout_p, int KH, int KW,
+                                           int stride, int pad, imx_stream_t stream) {
+    IMX_REQUIRE(x && dy && dw, "conv2d_wgrad: null pointer");
+    int rc = check_wgrad_args(N, H, W, Cin, Cin_p, Cout, Cout_p, KH, KW, stride, pad);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (N == 0) {
+        cudaError_t e = cudaMemsetAsync(dw, 0, (size_t)Cout * Cin * KH * KW * 4, s);
+        return e == cudaSuccess ? IMX_OK : imx::set_error((int)e, "conv2d_wgrad: memset failed");
+    }
+    Plan pl;
+    rc = make_plan(pl, N, H, W, Cin_p, Cout_p, KH, KW, stride, pad);
+    if (rc) return rc;
+    IMX_REQUIRE(workspace && workspace_bytes >= pl.ws_floats * 4,
+                "conv2d_wgrad: workspace too small (%lld bytes given, %lld needed)", (long long)workspace_bytes,
+                (long long)pl.ws_floats * 4);
+    IMX_REQUIRE(aligned16(x) && aligned16(dy) && aligned16(workspace), "conv2d_wgrad: pointers must be 16-byte aligned");
+
+    WgradArgs a{};
+    a.N = N; a.Ho = pl.Ho; a.Wo = pl.Wo;
+    a.KH = KH; a.KW = KW; a.stride = stride; a.pad = pad;
+    a.tw = pl.tw; a.th = pl.th; a.tw_log2 = pl.tw_log2;
+    a.tiles_x = pl.tiles_x; a.tiles_y = pl.tiles_y; a.ptiles = pl.ptiles;
+    a.co_tiles = pl.co_tiles; a.ci_tiles = pl.ci_tiles; a.splits = pl.splits;
+    a.total_units = pl.co_tiles * pl.ci_tiles * KH * KW * pl.splits;
+    a.co_r = pl.co_tiles * BM; a.ci_r = pl.ci_tiles * pl.BN;
+    a.ws = reinterpret_cast<float*>(workspace);
+
+    CUtensorMap tdy, tx;
+    const uint64_t dims_dy[4] = {(uint64_t)Cout_p, (uint64_t)pl.Wo, (uint64_t)pl.Ho, (uint64_t)N};
+    const uint64_t str_dy[3] = {(uint64_t)Cout_p * 2, (uint64_t)pl.Wo * Cout_p * 2, (uint64_t)pl.Ho * pl.Wo * Cout_p * 2};
+    const uint32_t box_dy[4] = {64u, (uint32_t)pl.tw, (uint32_t)pl.th, 1u};
+    const uint32_t es1[4] = {1u, 1u, 1u, 1u};
+    rc = encode_tmap(&tdy, dy, 4, dims_dy, str_dy, box_dy, es1);
+    if (rc) return rc;
+    const uint64_t dims_x[4] = {(uint64_t)Cin_p, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+    const uint64_t str_x[3] = {(uint64_t)Cin_p * 2, (uint64_t)W * Cin_p * 2, (uint64_t)H * W * Cin_p * 2};
+    const uint32_t box_x[4] = {64u, (uint32_t)((pl.tw - 1) * stride + 1), (uint32_t)((pl.th - 1) * stride + 1), 1u};
+    const uint32_t es_x[4] = {1u, (uint32_t)stride, (uint32_t)stride, 1u};
+    rc = encode_tmap(&tx, x, 4, dims_x, str_x, box_x, es_x);
+    if (rc) return rc;
+
+    switch (pl.BN) {
+        case 256: rc = launch_wgrad<256>(tdy, tx, a, s); break;
+        case 128: rc = launch_wgrad<128>(tdy, tx, a, s); break;
+        default: rc = launch_wgrad<64>(tdy, tx, a, s); break;
+    }
+    if (rc) return rc;
+    const long total = (long)Cout * Cin * KH * KW;
+    long blocks = (total + 255) / 256;
+    if (blocks > 16L * imx::kNumSMs) blocks = 16L * imx::kNumSMs;
+    wgrad_reduce_kernel<<<(int)blocks, 256, 0, s>>>(a.ws, dw, Cout, Cin, KH * KW, pl.splits, a.co_r, a.ci_r);
+    return imx::check_launch("conv2d_wgrad_reduce");
+}

@@ -1,0 +1,275 @@
+// Layout / resize helpers around the SPADE block:
+// label-map nearest resize into the NHWC bf16 conv operand layout, nearest x2
+// feature upsample, NCHW fp32 <-> NHWC bf16 boundary conversion and the conv-weight
+// repack (W / sigma, bf16, GEMM layout).  All plain HBM-bound copies with 128-bit
+// accesses on the NHWC side.
+#include "imx_common.cuh"
+#include "../../include/imx.h"
+
+namespace {
+
+using imx::pack_bf16;
+
+// dst[n,y,x,0:Cp] from src[n,0:L,sy,sx].  One thread per 8 output channels; the
+// NCHW source is read with stride H*W between channels (label maps are small and
+// L2-resident: the resize runs once per resolution per forward).
+__global__ void nearest_resize_kernel(const float* __restrict__ src, uint4* __restrict__ dst,
+                                      int N, int L, int H, int W, int h, int w, int Cp) {
+    const int cg = Cp / 8;
+    const long total = (long)N * h * w * cg;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int c8 = (int)(i % cg);
+        long p = i / cg;
+        const int x = (int)(p % w); p /= w;
+        const int y = (int)(p % h);
+        const int n = (int)(p / h);
+        // torch 'nearest': src index = floor(dst_index * (in / out)), scale in fp32
+        const float sy_f = (float)H / (float)h, sx_f = (float)W / (float)w;
+        const int sy = min((int)floorf((float)y * sy_f), H - 1);
+        const int sx = min((int)floorf((float)x * sx_f), W - 1);
+        const float* s = src + ((size_t)n * L * H + sy) * W + sx;
+        float f[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int c = c8 * 8 + k;
+            f[k] = c < L ? __ldg(s + (size_t)c * H * W) : 0.0f;
+        }
+        dst[i] = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+    }
+}
+
+__global__ void upsample2x_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst,
+                                  int N, int H, int W, int cg) {
+    // one thread per source 16-byte chunk, written to the 2x2 destination block
+    const long total = (long)N * H * W * cg;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int c8 = (int)(i % cg);
+        long p = i / cg;
+        const int x = (int)(p % W); p /= W;
+        const int y = (int)(p % H);
+        const int n = (int)(p / H);
+        const uint4 v = imx::ldg_stream(src + i);
+        uint4* d = dst + (((size_t)n * 2 * H + 2 * y) * 2 * W + 2 * x) * cg + c8;
+        imx::stg_stream(d, v);
+        imx::stg_stream(d + cg, v);
+        imx::stg_stream(d + (size_t)2 * W * cg, v);
+        imx::stg_stream(d + (size_t)2 * W * cg + cg, v);
+    }
+}
+
+__global__ void upsample2x_bwd_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst,
+                                      int N, int H, int W, int cg) {
+    const long total = (long)N * H * W * cg;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int c8 = (int)(i % cg);
+        long p = i / cg;
+        const int x = (int)(p % W); p /= W;
+        const int y = (int)(p % H);
+        const int n = (int)(p / H);
+        const uint4* s = src + (((size_t)n * 2 * H + 2 * y) * 2 * W + 2 * x) * cg + c8;
+        const uint4 a = imx::ldg_stream(s), b = imx::ldg_stream(s + cg);
+        const uint4 c = imx::ldg_stream(s + (size_t)2 * W * cg), d = imx::ldg_stream(s + (size_t)2 * W * cg + cg);
+        const uint32_t av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+        const uint32_t cv[4] = {c.x, c.y, c.z, c.w}, dv[4] = {d.x, d.y, d.z, d.w};
+        uint32_t o[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float lo = imx::bf16_lo(av[k]) + imx::bf16_lo(bv[k]) + imx::bf16_lo(cv[k]) + imx::bf16_lo(dv[k]);
+            const float hi = imx::bf16_hi(av[k]) + imx::bf16_hi(bv[k]) + imx::bf16_hi(cv[k]) + imx::bf16_hi(dv[k]);
+            o[k] = pack_bf16(lo, hi);
+        }
+        imx::stg_stream(dst + i, make_uint4(o[0], o[1], o[2], o[3]));
+    }
+}
+
+// NCHW fp32 -> NHWC bf16 through a 32(pixels) x 32(channels) shared-memory transpose so
+// both sides are coalesced.
+__global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst,
+                                    int C, long HW, int Cp) {
+    __shared__ float tile[32][33];
+    const int n = blockIdx.z;
+    const long p0 = (long)blockIdx.x * 32;
+    const int c0 = blockIdx.y * 32;
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        const int c = c0 + j;
+        const long p = p0 + threadIdx.x;
+        tile[j][threadIdx.x] = (c < C && p < HW) ? __ldg(src + ((size_t)n * C + c) * HW + p) : 0.0f;
+    }
+    __syncthreads();
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        const long p = p0 + j;
+        const int c = c0 + threadIdx.x;
+        if (p < HW && c < Cp) dst[((size_t)n * HW + p) * Cp + c] = __float2bfloat16_rn(tile[threadIdx.x][j]);
+    }
+}
+
+__global__ void nhwc_to_nchw_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst,
+                                    int C, long HW, int Cp, int apply_tanh) {
+    __shared__ float tile[32][33];
+    const int n = blockIdx.z;
+    const long p0 = (long)blockIdx.x * 32;
+    const int c0 = blockIdx.y * 32;
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        const long p = p0 + j;
+        const int c = c0 + threadIdx.x;
+        tile[j][threadIdx.x] = (p < HW && c < C) ? __bfloat162float(src[((size_t)n * HW + p) * Cp + c]) : 0.0f;
+    }
+    __syncthreads();
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        const int c = c0 + j;
+        const long p = p0 + threadIdx.x;
+        if (c < C && p < HW) {
+            float v = tile[threadIdx.x][j];
+            if (apply_tanh) v = tanhf(v);
+            dst[((size_t)n * C + c) * HW + p] = v;
+        }
+    }
+}
+
+// packed[co][kh][kw][ci_p] = w[co][ci][kh][kw] * inv_sigma   (transpose_flip == 0)
+// packed[ci][K-1-kh][K-1-kw][co_p] = w[co][ci][kh][kw] * inv_sigma   (transpose_flip != 0)
+__global__ void pack_weight_kernel(const float* __restrict__ w, const float* __restrict__ inv_sigma,
+                                   __nv_bfloat16* __restrict__ packed, int Cout, int Cin, int KH, int KW,
+                                   int Cp, int transpose_flip) {
+    const float s = inv_sigma ? __ldg(inv_sigma) : 1.0f;
+    const int rows = transpose_flip ? Cin : Cout;    // rows of the packed matrix
+    const int inner = transpose_flip ? Cout : Cin;   // valid extent of the innermost packed dim
+    const long total = (long)rows * KH * KW * Cp;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int ci = (int)(i % Cp);
+        long t = i / Cp;
+        const int kw = (int)(t % KW); t /= KW;
+        const int kh = (int)(t % KH);
+        const int r = (int)(t / KH);
+        float v = 0.0f;
+        if (ci < inner) {
+            if (!transpose_flip) v = __ldg(w + (((size_t)r * Cin + ci) * KH + kh) * KW + kw) * s;
+            else v = __ldg(w + (((size_t)ci * Cin + r) * KH + (KH - 1 - kh)) * KW + (KW - 1 - kw)) * s;
+        }
+        packed[i] = __float2bfloat16_rn(v);
+    }
+}
+
+// Interleaved gamma/beta filter for the fused projection+modulation conv: packed row
+// (c / 64) * 128 + (c % 64) holds gamma's filter for channel c, row + 64 holds beta's.
+__global__ void pack_gb_weight_kernel(const float* __restrict__ wg, const float* __restrict__ wb,
+                                      const float* __restrict__ isg, const float* __restrict__ isb,
+                                      __nv_bfloat16* __restrict__ packed, int C, int Ch, int KH, int KW, int Cp) {
+    const float sg = isg ? __ldg(isg) : 1.0f, sb = isb ? __ldg(isb) : 1.0f;
+    const int Cr = (C + 63) / 64 * 64;
+    const long total = (long)2 * Cr * KH * KW * Cp;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int ci = (int)(i % Cp);
+        long t = i / Cp;
+        const int kw = (int)(t % KW); t /= KW;
+        const int kh = (int)(t % KH);
+        const int row = (int)(t / KH);
+        const int blk = row / 128, within = row % 128;
+        const bool is_beta = within >= 64;
+        const int c = blk * 64 + (within % 64);
+        float v = 0.0f;
+        if (ci < Ch && c < C) {
+            const float* src = is_beta ? wb : wg;
+            v = __ldg(src + (((size_t)c * Ch + ci) * KH + kh) * KW + kw) * (is_beta ? sb : sg);
+        }
+        packed[i] = __float2bfloat16_rn(v);
+    }
+}
+
+inline int grid_for(long total, int threads) {
+    long b = (total + threads - 1) / threads;
+    long cap = 16L * imx::kNumSMs;
+    return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+
+}  // namespace
+
+extern "C" int imx_nearest_resize_nchw_f32_to_nhwc_bf16(const float* src, imx_bf16* dst,
+                                                        int N, int L, int H, int W,
+                                                        int h, int w, int Cp, imx_stream_t stream) {
+    IMX_REQUIRE(src && dst, "nearest_resize: null pointer");
+    IMX_REQUIRE(N >= 0 && L > 0 && H > 0 && W > 0 && h > 0 && w > 0, "nearest_resize: bad size");
+    IMX_REQUIRE(Cp >= L && Cp % 8 == 0, "nearest_resize: Cp (%d) must be >= L (%d) and a multiple of 8", Cp, L);
+    const long total = (long)N * h * w * (Cp / 8);
+    if (total == 0) return IMX_OK;
+    nearest_resize_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(
+        src, reinterpret_cast<uint4*>(dst), N, L, H, W, h, w, Cp);
+    return imx::check_launch("nearest_resize");
+}
+
+extern "C" int imx_upsample2x_nhwc_bf16(const imx_bf16* src, imx_bf16* dst,
+                                        int N, int H, int W, int C, imx_stream_t stream) {
+    IMX_REQUIRE(src && dst, "upsample2x: null pointer");
+    IMX_REQUIRE(N >= 0 && H >= 0 && W >= 0 && C >= 0 && C % 8 == 0, "upsample2x: bad size (C %% 8 must be 0)");
+    const long total = (long)N * H * W * (C / 8);
+    if (total == 0) return IMX_OK;
+    upsample2x_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const uint4*>(src), reinterpret_cast<uint4*>(dst), N, H, W, C / 8);
+    return imx::check_launch("upsample2x");
+}
+
+extern "C" int imx_upsample2x_bwd_nhwc_bf16(const imx_bf16* src, imx_bf16* dst,
+                                            int N, int H, int W, int C, imx_stream_t stream) {
+    IMX_REQUIRE(src && dst, "upsample2x_bwd: null pointer");
+    IMX_REQUIRE(N >= 0 && H >= 0 && W >= 0 && C >= 0 && C % 8 == 0, "upsample2x_bwd: bad size (C %% 8 must be 0)");
+    const long total = (long)N * H * W * (C / 8);
+    if (total == 0) return IMX_OK;
+    upsample2x_bwd_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const uint4*>(src), reinterpret_cast<uint4*>(dst), N, H, W, C / 8);
+    return imx::check_launch("upsample2x_bwd");
+}
+
+extern "C" int imx_nchw_f32_to_nhwc_bf16(const float* src, imx_bf16* dst, int N, int C, int H, int W,
+                                         int Cp, imx_stream_t stream) {
+    IMX_REQUIRE(src && dst, "nchw_to_nhwc: null pointer");
+    IMX_REQUIRE(N >= 0 && C >= 0 && H >= 0 && W >= 0 && Cp >= C, "nchw_to_nhwc: bad size");
+    IMX_REQUIRE(N <= 65535, "nchw_to_nhwc: batch too large");
+    const long HW = (long)H * W;
+    if ((long)N * HW * Cp == 0) return IMX_OK;
+    dim3 grid((unsigned)((HW + 31) / 32), (Cp + 31) / 32, N), block(32, 8);
+    IMX_REQUIRE(grid.y <= 65535, "nchw_to_nhwc: too many channels");
+    nchw_to_nhwc_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(
+        src, reinterpret_cast<__nv_bfloat16*>(dst), C, HW, Cp);
+    return imx::check_launch("nchw_to_nhwc");
+}
+
+extern "C" int imx_nhwc_bf16_to_nchw_f32(const imx_bf16* src, float* dst, int N, int C, int H, int W,
+                                         int Cp, int apply_tanh, imx_stream_t stream) {
+    IMX_REQUIRE(src && dst, "nhwc_to_nchw: null pointer");
+    IMX_REQUIRE(N >= 0 && C >= 0 && H >= 0 && W >= 0 && Cp >= C, "nhwc_to_nchw: bad size");
+    IMX_REQUIRE(N <= 65535, "nhwc_to_nchw: batch too large");
+    const long HW = (long)H * W;
+    if ((long)N * HW * C == 0) return IMX_OK;
+    dim3 grid((unsigned)((HW + 31) / 32), (C + 31) / 32, N), block(32, 8);
+    IMX_REQUIRE(grid.y <= 65535, "nhwc_to_nchw: too many channels");
+    nhwc_to_nchw_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const __nv_bfloat16*>(src), dst, C, HW, Cp, apply_tanh);
+    return imx::check_launch("nhwc_to_nchw");
+}
+
+extern "C" int imx_pack_conv_weight_bf16(const float* w, const float* inv_sigma, imx_bf16* packed,
+                                         int Cout, int Cin, int KH, int KW, int Cin_p,
+                                         int transpose_flip, imx_stream_t stream) {
+    IMX_REQUIRE(w && packed, "pack_conv_weight: null pointer");
+    IMX_REQUIRE(Cout > 0 && Cin > 0 && KH > 0 && KW > 0, "pack_conv_weight: bad size");
+    IMX_REQUIRE(Cin_p % 8 == 0 && Cin_p >= (transpose_flip ? Cout : Cin),
+                "pack_conv_weight: padded inner dim (%d) too small or not a multiple of 8", Cin_p);
+    const long total = (long)(transpose_flip ? Cin : Cout) * KH * KW * Cin_p;
+    pack_weight_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(
+        w, inv_sigma, reinterpret_cast<__nv_bfloat16*>(packed), Cout, Cin, KH, KW, Cin_p, transpose_flip);
+    return imx::check_launch("pack_conv_weight");
+}
+
+extern "C" int imx_pack_spade_gb_weight_bf16(const float* w_gamma, const float* w_beta,
+                                             const float* inv_sigma_gamma, const float* inv_sigma_beta,
+                                             imx_bf16* packed, int C, int Ch, int KH, int KW, int Ch_p,
+                                             imx_stream_t stream) {
+    IMX_REQUIRE(w_gamma && w_beta && packed, "pack_spade_gb_weight: null pointer");
+    IMX_REQUIRE(C > 0 && Ch > 0 && KH > 0 && KW > 0, "pack_spade_gb_weight: bad size");
+    IMX_REQUIRE(Ch_p % 8 == 0 && Ch_p >= Ch, "pack_spade_gb_weight: bad Ch_p");
+    const long total = (long)2 * ((C + 63) / 64 * 64) * KH * KW * Ch_p;
+    pack_gb_weight_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(
+        w_gamma, w_beta, inv_sigma_gamma, inv_sigma_beta, reinterpret_cast<__nv_bfloat16*>(packed),
+        C, Ch, KH, KW, Ch_p);
+    return imx::check_launch("pack_spade_gb_weight");
+}

@@ -1,0 +1,447 @@
+// Normalisation statistics and the fused normalise * (1+gamma) + beta -> activation
+// kernels of the SPADE block.
+//
+// ref: SpatiallyAdaptiveNorm.forward  imaginaire/layers/activation_norm.py:211-234
+//      AdaptiveNorm.forward           imaginaire/layers/activation_norm.py:79-106
+//      inner norm factory             imaginaire/layers/activation_norm.py:377-432
+//      LeakyReLU(0.2)                 imaginaire/layers/nonlinearity.py:22
+//
+// All tensors are NHWC bf16; every thread owns one fixed group of 8 channels (one
+// 128-bit load) and walks down the pixel rows, so per-channel parameters live in
+// registers and every warp-level access is a contiguous 512-byte row segment.
+// HBM-bound: algorithmic bytes are 2*NHWC (stats: read x) and
+// 2*NHWC*(2 + 2*[gamma/beta materialised]) (modulate: read x, gamma, beta, write y).
+#include "imx_common.cuh"
+#include "../../include/imx.h"
+
+namespace {
+
+using imx::bf16_hi;
+using imx::bf16_lo;
+using imx::pack_bf16;
+
+constexpr int kThreads = 256;
+
+struct RowMap {
+    int cg;    // 8-channel groups per pixel (C / 8)
+    int tpr;   // threads per pixel row actually used
+    int rows;  // pixel rows covered per block iteration
+};
+
+inline RowMap make_rowmap(int C) {
+    RowMap m;
+    m.cg = C / 8;
+    m.tpr = m.cg < kThreads ? m.cg : kThreads;
+    m.rows = kThreads / m.tpr;
+    return m;
+}
+
+// Split `np` pixels of one group over blocks: a few CTAs per SM, whole rows-per-iteration.
+inline int pick_blocks(long np, int rows, int groups) {
+    long iters = (np + rows - 1) / rows;
+    long want = (8L * imx::kNumSMs + groups - 1) / groups;
+    long b = iters < want ? iters : want;
+    return (int)(b < 1 ? 1 : b);
+}
+
+__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
+    f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
+    f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+    return make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+}
+__device__ __forceinline__ void load8f(const float* p, float (&f)[8]) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(p));
+    const float4 b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+    f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+
+// ------------------------------------------------------------------ statistics
+
+// grid = (blocks, groups); group g covers pixels [g*HWg, (g+1)*HWg).
+template <bool kWithSq>
+__global__ void __launch_bounds__(kThreads)
+stats_kernel(const uint4* __restrict__ x, float* __restrict__ sum, float* __restrict__ sumsq,
+             long HWg, int C, int cg, int tpr, int rows, int row_stride_c8) {
+    __shared__ float red[kThreads][9];
+    const int tid = threadIdx.x;
+    const int ci = tid % tpr, r = tid / tpr;
+    const bool active = r < rows;
+    const int g = blockIdx.y;
+    // this block's pixel range inside the group
+    const long per = (HWg + gridDim.x - 1) / gridDim.x;
+    const long p0 = (long)blockIdx.x * per;
+    const long p1 = p0 + per < HWg ? p0 + per : HWg;
+    const uint4* base = x + (size_t)g * HWg * row_stride_c8;
+    for (int c8 = ci; c8 < cg; c8 += tpr) {
+        float s[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (active) {
+            long p = p0 + r;
+            // 4 independent 128-bit loads in flight per thread
+            for (; p + 3L * rows < p1; p += 4L * rows) {
+                uint4 v[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) v[u] = imx::ldg_stream(base + (size_t)(p + (long)u * rows) * row_stride_c8 + c8);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    float f[8];
+                    unpack8(v[u], f);
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) { s[k] += f[k]; if (kWithSq) q[k] = fmaf(f[k], f[k], q[k]); }
+                }
+            }
+            for (; p < p1; p += rows) {
+                float f[8];
+                unpack8(imx::ldg_stream(base + (size_t)p * row_stride_c8 + c8), f);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) { s[k] += f[k]; if (kWithSq) q[k] = fmaf(f[k], f[k], q[k]); }
+            }
+        }
+        // reduce the `rows` partial sums that share this channel group
+#pragma unroll
+        for (int pass = 0; pass < (kWithSq ? 2 : 1); ++pass) {
+            __syncthreads();
+#pragma unroll
+            for (int k = 0; k < 8; ++k) red[tid][k] = pass == 0 ? s[k] : q[k];
+            __syncthreads();
+            if (r == 0) {
+                float acc[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) acc[k] = red[tid][k];
+                for (int rr = 1; rr < rows; ++rr)
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) acc[k] += red[tid + rr * tpr][k];
+                float* dst = (pass == 0 ? sum : sumsq) + (size_t)g * C + c8 * 8;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) atomicAdd(dst + k, acc[k]);
+            }
+        }
+    }
+}
+
+__global__ void finalize_kernel(const float* __restrict__ sum, const float* __restrict__ sumsq,
+                                float count, float eps, float* __restrict__ mean,
+                                float* __restrict__ rstd, float* running_mean, float* running_var,
+                                float momentum, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float m = sum[i] / count;
+    const float var = fmaxf(sumsq[i] / count - m * m, 0.0f);
+    mean[i] = m;
+    rstd[i] = rsqrtf(var + eps);
+    if (running_mean) {
+        const float unbiased = count > 1.0f ? var * (count / (count - 1.0f)) : var;
+        running_mean[i] = (1.0f - momentum) * running_mean[i] + momentum * m;
+        running_var[i] = (1.0f - momentum) * running_var[i] + momentum * unbiased;
+    }
+}
+
+// --------------------------------------------------------------- modulation
+
+__device__ __forceinline__ float act_fwd(float v, int act) {
+    if (act == 1) return v > 0.0f ? v : 0.2f * v;
+    if (act == 2) return fmaxf(v, 0.0f);
+    return v;
+}
+__device__ __forceinline__ float act_grad(float pre, int act) {
+    if (act == 1) return pre > 0.0f ? 1.0f : 0.2f;
+    if (act == 2) return pre > 0.0f ? 1.0f : 0.0f;
+    return 1.0f;
+}
+
+struct ModArgs {
+    const uint4* x;
+    const uint4* dy;
+    const float* mean;
+    const float* rstd;
+    const float* w;
+    const float* b;
+    const void* gamma;
+    const void* beta;
+    int N, H, W, C;
+    int per_instance, gb_mode, act, up2x;
+};
+
+// Per-thread channel parameters: xn = x * rs + mr (inner norm), xh = xn * w + b (affine).
+__device__ __forceinline__ void load_norm_params(const ModArgs& a, int n, int c, float (&rs)[8], float (&mr)[8],
+                                                 float (&ww)[8], float (&bb)[8]) {
+    float m[8];
+    const int so = (a.per_instance ? n * a.C : 0) + c;
+    load8f(a.mean + so, m);
+    load8f(a.rstd + so, rs);
+    if (a.w) load8f(a.w + c, ww);
+    if (a.b) load8f(a.b + c, bb);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        mr[k] = -m[k] * rs[k];
+        if (!a.w) ww[k] = 1.0f;
+        if (!a.b) bb[k] = 0.0f;
+    }
+}
+
+// grid = (blocks, N).  Each block walks a pixel range of one sample.
+template <int kMode>  // 0: forward   1: backward pass 1 (dgamma/dbeta + reductions)   2: backward pass 2 (dx)
+__global__ void __launch_bounds__(kThreads)
+modulate_kernel(ModArgs a, uint4* __restrict__ out0, void* __restrict__ out1, void* __restrict__ out2,
+                float* __restrict__ red, float inv_count, int use_batch_stats,
+                int cg, int tpr, int rows) {
+    __shared__ float sred[kMode == 1 ? kThreads : 1][17];
+    const int tid = threadIdx.x;
+    const int ci = tid % tpr, r = tid / tpr;
+    const bool active = r < rows;
+    const int n = blockIdx.y;
+    const long HW = (long)a.H * a.W;
+    const long per = (HW + gridDim.x - 1) / gridDim.x;
+    const long p0 = (long)blockIdx.x * per;
+    const long p1 = p0 + per < HW ? p0 + per : HW;
+    const int Wx = a.up2x ? a.W / 2 : a.W;
+    const long HWx = a.up2x ? HW / 4 : HW;
+    const uint4* xb = a.x + (size_t)n * HWx * cg;
+    const size_t ob = (size_t)n * HW * cg;
+
+    for (int c8 = ci; c8 < cg; c8 += tpr) {
+        const int c = c8 * 8;
+        float rs[8], mr[8], ww[8], bb[8];
+        load_norm_params(a, n, c, rs, mr, ww, bb);
+        float gv[8], bv[8];
+        if (a.gb_mode == 1) {
+            load8f(reinterpret_cast<const float*>(a.gamma) + (size_t)n * a.C + c, gv);
+            load8f(reinterpret_cast<const float*>(a.beta) + (size_t)n * a.C + c, bv);
+        }
+        float m1[8], m2[8];  // pass 2: mean(g), mean(g * xn) in xhat-affine units
+        if (kMode == 2) {
+            if (use_batch_stats) {
+                const int so = (a.per_instance ? n * a.C : 0) + c;
+                const int G = a.per_instance ? a.N : 1;
+                load8f(red + so, m1);
+                load8f(red + (size_t)G * a.C + so, m2);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) { m1[k] *= inv_count; m2[k] *= inv_count; }
+            } else {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) { m1[k] = 0.0f; m2[k] = 0.0f; }
+            }
+        }
+        float r1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, r2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        float ag[8] = {0, 0, 0, 0, 0, 0, 0, 0}, ab[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (active) {
+            for (long p = p0 + r; p < p1; p += rows) {
+                long px = p;
+                if (a.up2x) {
+                    const int yy = (int)(p / a.W), xx = (int)(p - (long)yy * a.W);
+                    px = (long)(yy >> 1) * Wx + (xx >> 1);
+                }
+                float xv[8], g[8], be[8];
+                unpack8(a.up2x ? __ldg(xb + (size_t)px * cg + c8) : imx::ldg_stream(xb + (size_t)px * cg + c8), xv);
+                if (a.gb_mode == 0) {
+                    unpack8(imx::ldg_stream(reinterpret_cast<const uint4*>(a.gamma) + ob + (size_t)p * cg + c8), g);
+                    unpack8(imx::ldg_stream(reinterpret_cast<const uint4*>(a.beta) + ob + (size_t)p * cg + c8), be);
+                } else if (a.gb_mode == 1) {
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) { g[k] = gv[k]; be[k] = bv[k]; }
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) { g[k] = 0.0f; be[k] = 0.0f; }
+                }
+                if (kMode == 0) {
+                    float y[8];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const float xh = fmaf(fmaf(xv[k], rs[k], mr[k]), ww[k], bb[k]);
+                        y[k] = act_fwd(fmaf(xh, 1.0f + g[k], be[k]), a.act);
+                    }
+                    imx::stg_stream(out0 + ob + (size_t)p * cg + c8, pack8(y));
+                } else {
+                    float dyv[8];
+                    unpack8(imx::ldg_stream(a.dy + ob + (size_t)p * cg + c8), dyv);
+                    float o0[8], o1[8];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const float xn = fmaf(xv[k], rs[k], mr[k]);       // normalised x
+                        const float xh = fmaf(xn, ww[k], bb[k]);          // + inner affine
+                        const float pre = fmaf(xh, 1.0f + g[k], be[k]);
+                        const float dpre = dyv[k] * act_grad(pre, a.act);
+                        const float dxh = dpre * (1.0f + g[k]);           // grad wrt xh
+                        if (kMode == 1) {
+                            o0[k] = dpre * xh;   // dgamma
+                            o1[k] = dpre;        // dbeta
+                            r1[k] += dxh;                  // -> dbias of the inner norm
+                            r2[k] = fmaf(dxh, xn, r2[k]);  // -> dweight of the inner norm
+                            if (a.gb_mode == 1) { ag[k] += o0[k]; ab[k] += o1[k]; }
+                        } else {
+                            // dx = rstd * w * (dxh - mean(dxh) - xn * mean(dxh * xn))
+                            o0[k] = rs[k] * ww[k] * (dxh - m1[k] - xn * m2[k]);
+                        }
+                    }
+                    if (kMode == 1) {
+                        if (a.gb_mode == 0) {
+                            imx::stg_stream(reinterpret_cast<uint4*>(out1) + ob + (size_t)p * cg + c8, pack8(o0));
+                            imx::stg_stream(reinterpret_cast<uint4*>(out2) + ob + (size_t)p * cg + c8, pack8(o1));
+                        }
+                    } else {
+                        imx::stg_stream(out0 + ob + (size_t)p * cg + c8, pack8(o0));
+                    }
+                }
+            }
+        }
+        if (kMode == 1) {
+            // block-level reduction of r1, r2 (and adaptive dgamma/dbeta) over the row groups
+            for (int pass = 0; pass < (a.gb_mode == 1 ? 2 : 1); ++pass) {
+                __syncthreads();
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    sred[tid][k] = pass == 0 ? r1[k] : ag[k];
+                    sred[tid][8 + k] = pass == 0 ? r2[k] : ab[k];
+                }
+                __syncthreads();
+                if (r == 0) {
+                    float acc[16];
+#pragma unroll
+                    for (int k = 0; k < 16; ++k) acc[k] = sred[tid][k];
+                    for (int rr = 1; rr < rows; ++rr)
+#pragma unroll
+                        for (int k = 0; k < 16; ++k) acc[k] += sred[tid + rr * tpr][k];
+                    if (pass == 0) {
+                        const int G = a.per_instance ? a.N : 1;
+                        const int so = (a.per_instance ? n * a.C : 0) + c;
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) {
+                            atomicAdd(red + so + k, acc[k]);
+                            atomicAdd(red + (size_t)G * a.C + so + k, acc[8 + k]);
+                        }
+                    } else {
+                        float* dg = reinterpret_cast<float*>(out1) + (size_t)n * a.C + c;
+                        float* db = reinterpret_cast<float*>(out2) + (size_t)n * a.C + c;
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) { atomicAdd(dg + k, acc[k]); atomicAdd(db + k, acc[8 + k]); }
+                    }
+                }
+            }
+        }
+    }
+}
+
+int check_mod_args(const char* who, const void* x, const float* mean, const float* rstd,
+                   const void* gamma, const void* beta, int N, int H, int W, int C,
+                   int gb_mode, int act, int up2x) {
+    IMX_REQUIRE(x && mean && rstd, "%s: null pointer", who);
+    IMX_REQUIRE(N >= 0 && H >= 0 && W >= 0 && C >= 0, "%s: negative size", who);
+    IMX_REQUIRE(C % 8 == 0, "%s: C (%d) must be a multiple of 8", who, C);
+    IMX_REQUIRE(gb_mode >= 0 && gb_mode <= 2, "%s: bad gb_mode %d", who, gb_mode);
+    IMX_REQUIRE(gb_mode == 2 || (gamma && beta), "%s: gamma/beta missing", who);
+    IMX_REQUIRE(act >= 0 && act <= 2, "%s: bad act %d", who, act);
+    IMX_REQUIRE(!up2x || (H % 2 == 0 && W % 2 == 0), "%s: up2x needs even H, W", who);
+    IMX_REQUIRE(N <= 65535, "%s: batch too large", who);
+    return IMX_OK;
+}
+
+}  // namespace
+
+extern "C" int imx_bn_stats_nhwc_bf16(const imx_bf16* x, float* sum, float* sumsq,
+                                      int N, int HW, int C, int per_instance, imx_stream_t stream) {
+    IMX_REQUIRE(x && sum && sumsq, "bn_stats: null pointer");
+    IMX_REQUIRE(N >= 0 && HW >= 0 && C >= 0, "bn_stats: negative size");
+    IMX_REQUIRE(C % 8 == 0, "bn_stats: C (%d) must be a multiple of 8", C);
+    if ((long)N * HW * C == 0) return IMX_OK;
+    const RowMap m = make_rowmap(C);
+    const int groups = per_instance ? N : 1;
+    IMX_REQUIRE(groups <= 65535, "bn_stats: batch too large");
+    const long HWg = per_instance ? HW : (long)N * HW;
+    dim3 grid(pick_blocks(HWg, m.rows, groups), groups);
+    stats_kernel<true><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const uint4*>(x), sum, sumsq, HWg, C, m.cg, m.tpr, m.rows, m.cg);
+    return imx::check_launch("bn_stats");
+}
+
+extern "C" int imx_channel_sum_nhwc_bf16(const imx_bf16* x, float* out, int NP, int C, int Cp,
+                                         imx_stream_t stream) {
+    IMX_REQUIRE(x && out, "channel_sum: null pointer");
+    IMX_REQUIRE(NP >= 0 && C >= 0 && Cp >= C, "channel_sum: bad size");
+    IMX_REQUIRE(C % 8 == 0 && Cp % 8 == 0, "channel_sum: C and Cp must be multiples of 8");
+    if ((long)NP * C == 0) return IMX_OK;
+    const RowMap m = make_rowmap(C);
+    dim3 grid(pick_blocks(NP, m.rows, 1), 1);
+    stats_kernel<false><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const uint4*>(x), out, nullptr, NP, C, m.cg, m.tpr, m.rows, Cp / 8);
+    return imx::check_launch("channel_sum");
+}
+
+extern "C" int imx_bn_finalize(const float* sum, const float* sumsq, float count, float eps,
+                               float* mean, float* rstd, float* running_mean, float* running_var,
+                               float momentum, int G, int C, imx_stream_t stream) {
+    IMX_REQUIRE(sum && sumsq && mean && rstd, "bn_finalize: null pointer");
+    IMX_REQUIRE(G >= 0 && C >= 0, "bn_finalize: negative size");
+    IMX_REQUIRE(count > 0.0f, "bn_finalize: count must be positive");
+    IMX_REQUIRE((running_mean == nullptr) == (running_var == nullptr), "bn_finalize: running_mean/var must come together");
+    IMX_REQUIRE(running_mean == nullptr || G == 1, "bn_finalize: running stats need G == 1");
+    const int n = G * C;
+    if (n == 0) return IMX_OK;
+    finalize_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(sum, sumsq, count, eps, mean, rstd,
+                                                                      running_mean, running_var, momentum, n);
+    return imx::check_launch("bn_finalize");
+}
+
+extern "C" int imx_spade_modulate_fwd(const imx_bf16* x, const float* mean, const float* rstd,
+                                      const float* w, const float* b,
+                                      const void* gamma, const void* beta, imx_bf16* y,
+                                      int N, int H, int W, int C,
+                                      int stats_per_instance, int gb_mode, int act, int up2x,
+                                      imx_stream_t stream) {
+    int rc = check_mod_args("spade_modulate_fwd", x, mean, rstd, gamma, beta, N, H, W, C, gb_mode, act, up2x);
+    if (rc) return rc;
+    IMX_REQUIRE(y, "spade_modulate_fwd: null output");
+    if ((long)N * H * W * C == 0) return IMX_OK;
+    const RowMap m = make_rowmap(C);
+    ModArgs a{reinterpret_cast<const uint4*>(x), nullptr, mean, rstd, w, b, gamma, beta,
+              N, H, W, C, stats_per_instance, gb_mode, act, up2x};
+    dim3 grid(pick_blocks((long)H * W, m.rows, N), N);
+    modulate_kernel<0><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
+        a, reinterpret_cast<uint4*>(y), nullptr, nullptr, nullptr, 0.0f, 1, m.cg, m.tpr, m.rows);
+    return imx::check_launch("spade_modulate_fwd");
+}
+
+extern "C" int imx_spade_modulate_bwd_reduce(const imx_bf16* x, const imx_bf16* dy,
+                                             const float* mean, const float* rstd,
+                                             const float* w, const float* b,
+                                             const void* gamma, const void* beta,
+                                             void* dgamma, void* dbeta, float* red,
+                                             int N, int H, int W, int C,
+                                             int stats_per_instance, int gb_mode, int act,
+                                             imx_stream_t stream) {
+    int rc = check_mod_args("spade_modulate_bwd_reduce", x, mean, rstd, gamma, beta, N, H, W, C, gb_mode, act, 0);
+    if (rc) return rc;
+    IMX_REQUIRE(dy && red, "spade_modulate_bwd_reduce: null pointer");
+    IMX_REQUIRE(gb_mode == 2 || (dgamma && dbeta), "spade_modulate_bwd_reduce: dgamma/dbeta missing");
+    if ((long)N * H * W * C == 0) return IMX_OK;
+    const RowMap m = make_rowmap(C);
+    ModArgs a{reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(dy), mean, rstd, w, b, gamma, beta,
+              N, H, W, C, stats_per_instance, gb_mode, act, 0};
+    dim3 grid(pick_blocks((long)H * W, m.rows, N), N);
+    modulate_kernel<1><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
+        a, nullptr, dgamma, dbeta, red, 0.0f, 1, m.cg, m.tpr, m.rows);
+    return imx::check_launch("spade_modulate_bwd_reduce");
+}
+
+extern "C" int imx_spade_modulate_bwd_dx(const imx_bf16* x, const imx_bf16* dy,
+                                         const float* mean, const float* rstd,
+                                         const float* w, const float* b,
+                                         const void* gamma, const void* beta,
+                                         const float* red, float count, imx_bf16* dx,
+                                         int N, int H, int W, int C,
+                                         int stats_per_instance, int gb_mode, int act,
+                                         int use_batch_stats, imx_stream_t stream) {
+    int rc = check_mod_args("spade_modulate_bwd_dx", x, mean, rstd, gamma, beta, N, H, W, C, gb_mode, act, 0);
+    if (rc) return rc;
+    IMX_REQUIRE(dy && dx, "spade_modulate_bwd_dx: null pointer");
+    IMX_REQUIRE(!use_batch_stats || (red && count > 0.0f), "spade_modulate_bwd_dx: reductions/count missing");
+    if ((long)N * H * W * C == 0) return IMX_OK;
+    const RowMap m = make_rowmap(C);
+    ModArgs a{reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(dy), mean, rstd, w, b, gamma, beta,
+              N, H, W, C, stats_per_instance, gb_mode, act, 0};
+    dim3 grid(pick_blocks((long)H * W, m.rows, N), N);
+    modulate_kernel<2><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
+        a, reinterpret_cast<uint4*>(dx), nullptr, nullptr, const_cast<float*>(red),
+        use_batch_stats ? 1.0f / count : 0.0f, use_batch_stats, m.cg, m.tpr, m.rows);
+    return imx::check_launch("spade_modulate_bwd_dx");
+}

@@ -1,0 +1,334 @@
+"""Tensor-level wrappers over the C ABI (include/imx.h).
+
+PyTorch is plumbing here: it owns device memory and the current stream.  Every
+function checks device / dtype / layout, allocates the outputs, and calls the
+C entry point on ``torch.cuda.current_stream()``.  CPU tensors are rejected:
+there is no CPU or eager fallback.
+
+Activation layout: a logical N x C x H x W bf16 tensor in ``channels_last``
+memory format, i.e. NHWC in memory, which is what the kernels read.
+"""
+import torch
+
+from . import _C
+
+EPI_BIAS, EPI_RELU, EPI_LRELU, EPI_RESIDUAL, EPI_TANH, EPI_STATS, EPI_OUT_F32 = 1, 2, 4, 8, 16, 32, 64
+ACT_NONE, ACT_LRELU, ACT_RELU = 0, 1, 2
+ACT_CODES = {'': 0, 'none': 0, None: 0, 'leakyrelu': 1, 'relu': 2}
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _req_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError('imaginaire_b200 ops run on CUDA tensors only (no CPU fallback); got a %s tensor'
+                               % t.device.type)
+
+
+def _req_f32c(t, name):
+    if t.dtype != torch.float32 or not t.is_contiguous():
+        raise RuntimeError('%s must be a contiguous float32 tensor' % name)
+
+
+def round_up(v, m):
+    return (v + m - 1) // m * m
+
+
+def is_nhwc_bf16(t):
+    return t.dim() == 4 and t.dtype == torch.bfloat16 and t.permute(0, 2, 3, 1).is_contiguous()
+
+
+def _req_nhwc(t, name):
+    if not is_nhwc_bf16(t):
+        raise RuntimeError('%s must be a 4-D bfloat16 tensor in channels_last (NHWC) memory; got %s %s strides %s'
+                           % (name, t.dtype, tuple(t.shape), t.stride()))
+
+
+def empty_nhwc(n, c, h, w, device, dtype=torch.bfloat16):
+    """Logical (n, c, h, w) tensor with NHWC memory."""
+    return torch.empty((n, h, w, c), dtype=dtype, device=device).permute(0, 3, 1, 2)
+
+
+# --------------------------------------------------------------------- warp
+
+def resample2d_fwd(img, flow, kernel_size=1):
+    _req_cuda(img, flow)
+    _req_f32c(img, 'input1'); _req_f32c(flow, 'input2')
+    b, c, hi, wi = img.shape
+    b2, two, h, w = flow.shape
+    if two != 2 or b2 != b:
+        raise RuntimeError('flow must be B x 2 x H x W with the same batch as the image')
+    out = torch.empty((b, c, h, w), dtype=torch.float32, device=img.device)
+    _C.lib().call('imx_resample2d_fwd_f32', _ptr(img), _ptr(flow), _ptr(out), b, c, h, w, hi, wi,
+                  int(kernel_size), _stream())
+    return out
+
+
+def resample2d_bwd(img, flow, grad_out, kernel_size=1, trunc_alpha=True, need_img=True, need_flow=True):
+    _req_cuda(img, flow, grad_out)
+    _req_f32c(img, 'input1'); _req_f32c(flow, 'input2'); _req_f32c(grad_out, 'grad_output')
+    b, c, hi, wi = img.shape
+    _, _, h, w = flow.shape
+    gimg = torch.zeros_like(img) if need_img else None
+    gflow = torch.empty_like(flow) if need_flow else None
+    _C.lib().call('imx_resample2d_bwd_f32', _ptr(img), _ptr(flow), _ptr(grad_out), _ptr(gimg), _ptr(gflow),
+                  b, c, h, w, hi, wi, int(kernel_size), int(bool(trunc_alpha)), _stream())
+    return gimg, gflow
+
+
+def gridsample_warp_fwd(img, flow):
+    _req_cuda(img, flow)
+    _req_f32c(img, 'image'); _req_f32c(flow, 'flow')
+    b, c, h, w = img.shape
+    if tuple(flow.shape) != (b, 2, h, w):
+        raise RuntimeError('flow must be B x 2 x H x W matching the image')
+    out = torch.empty_like(img)
+    _C.lib().call('imx_gridsample_warp_fwd_f32', _ptr(img), _ptr(flow), _ptr(out), b, c, h, w, _stream())
+    return out
+
+
+def gridsample_warp_bwd(img, flow, grad_out, need_img=True, need_flow=True):
+    _req_cuda(img, flow, grad_out)
+    _req_f32c(img, 'image'); _req_f32c(flow, 'flow'); _req_f32c(grad_out, 'grad_output')
+    b, c, h, w = img.shape
+    gimg = torch.zeros_like(img) if need_img else None
+    gflow = torch.empty_like(flow) if need_flow else None
+    _C.lib().call('imx_gridsample_warp_bwd_f32', _ptr(img), _ptr(flow), _ptr(grad_out), _ptr(gimg), _ptr(gflow),
+                  b, c, h, w, _stream())
+    return gimg, gflow
+
+
+# ------------------------------------------------------------------- layout
+
+def nearest_resize_to_nhwc(label, h, w, cp=None):
+    """NCHW fp32 conditioning map -> nearest-resized NHWC bf16, channels padded to cp."""
+    _req_cuda(label)
+    label = label.float().contiguous()
+    n, l, H, W = label.shape
+    cp = round_up(l, 64) if cp is None else cp
+    out = empty_nhwc(n, cp, h, w, label.device)
+    _C.lib().call('imx_nearest_resize_nchw_f32_to_nhwc_bf16', _ptr(label), _ptr(out), n, l, H, W, h, w, cp, _stream())
+    return out
+
+
+def upsample2x(x):
+    _req_cuda(x); _req_nhwc(x, 'x')
+    n, c, h, w = x.shape
+    out = empty_nhwc(n, c, 2 * h, 2 * w, x.device)
+    _C.lib().call('imx_upsample2x_nhwc_bf16', _ptr(x), _ptr(out), n, h, w, c, _stream())
+    return out
+
+
+def upsample2x_bwd(g):
+    _req_cuda(g); _req_nhwc(g, 'grad')
+    n, c, h2, w2 = g.shape
+    out = empty_nhwc(n, c, h2 // 2, w2 // 2, g.device)
+    _C.lib().call('imx_upsample2x_bwd_nhwc_bf16', _ptr(g), _ptr(out), n, h2 // 2, w2 // 2, c, _stream())
+    return out
+
+
+def nchw_f32_to_nhwc_bf16(x, cp=None):
+    _req_cuda(x)
+    x = x.float().contiguous()
+    n, c, h, w = x.shape
+    cp = round_up(c, 8) if cp is None else cp
+    out = empty_nhwc(n, cp, h, w, x.device)
+    _C.lib().call('imx_nchw_f32_to_nhwc_bf16', _ptr(x), _ptr(out), n, c, h, w, cp, _stream())
+    return out
+
+
+def nhwc_bf16_to_nchw_f32(x, c=None, apply_tanh=False):
+    _req_cuda(x); _req_nhwc(x, 'x')
+    n, cp, h, w = x.shape
+    c = cp if c is None else c
+    out = torch.empty((n, c, h, w), dtype=torch.float32, device=x.device)
+    _C.lib().call('imx_nhwc_bf16_to_nchw_f32', _ptr(x), _ptr(out), n, c, h, w, cp, int(apply_tanh), _stream())
+    return out
+
+
+def pack_conv_weight(w, inv_sigma=None, cin_p=None, transpose_flip=False):
+    """fp32 [Cout, Cin, KH, KW] -> bf16 [Cout, KH, KW, Cin_p] (or the dgrad filter
+    [Cin, KH, KW, Cout_p] with transpose_flip)."""
+    _req_cuda(w)
+    w = w.detach().float().contiguous()
+    cout, cin, kh, kw = w.shape
+    inner = cout if transpose_flip else cin
+    cin_p = round_up(inner, 8) if cin_p is None else cin_p
+    rows = cin if transpose_flip else cout
+    out = torch.empty((rows, kh, kw, cin_p), dtype=torch.bfloat16, device=w.device)
+    if inv_sigma is not None:
+        inv_sigma = inv_sigma.detach().float().reshape(1).contiguous()
+    _C.lib().call('imx_pack_conv_weight_bf16', _ptr(w), _ptr(inv_sigma), _ptr(out), cout, cin, kh, kw, cin_p,
+                  int(transpose_flip), _stream())
+    return out
+
+
+def pack_spade_gb_weight(w_gamma, w_beta, inv_sigma_gamma=None, inv_sigma_beta=None, ch_p=None):
+    _req_cuda(w_gamma, w_beta)
+    w_gamma = w_gamma.detach().float().contiguous()
+    w_beta = w_beta.detach().float().contiguous()
+    c, ch, kh, kw = w_gamma.shape
+    ch_p = round_up(ch, 8) if ch_p is None else ch_p
+    rows = 2 * round_up(c, 64)
+    out = torch.empty((rows, kh, kw, ch_p), dtype=torch.bfloat16, device=w_gamma.device)
+    isg = None if inv_sigma_gamma is None else inv_sigma_gamma.detach().float().reshape(1).contiguous()
+    isb = None if inv_sigma_beta is None else inv_sigma_beta.detach().float().reshape(1).contiguous()
+    _C.lib().call('imx_pack_spade_gb_weight_bf16', _ptr(w_gamma), _ptr(w_beta), _ptr(isg), _ptr(isb), _ptr(out),
+                  c, ch, kh, kw, ch_p, _stream())
+    return out
+
+
+# ------------------------------------------------------------- statistics
+
+def bn_stats(x, per_instance=False):
+    """Per-channel (or per-sample-per-channel) sum and sum of squares, fp32."""
+    _req_cuda(x); _req_nhwc(x, 'x')
+    n, c, h, w = x.shape
+    g = n if per_instance else 1
+    buf = torch.zeros((2, g, c), dtype=torch.float32, device=x.device)
+    _C.lib().call('imx_bn_stats_nhwc_bf16', _ptr(x), _ptr(buf[0]), _ptr(buf[1]), n, h * w, c, int(per_instance),
+                  _stream())
+    return buf
+
+
+def bn_finalize(sums, count, eps, running_mean=None, running_var=None, momentum=0.1):
+    """sums: (2, G, C) from bn_stats (possibly all-reduced).  Returns (mean, rstd) as (G*C,)."""
+    _req_cuda(sums)
+    _, g, c = sums.shape
+    out = torch.empty((2, g * c), dtype=torch.float32, device=sums.device)
+    _C.lib().call('imx_bn_finalize', _ptr(sums[0]), _ptr(sums[1]), float(count), float(eps), _ptr(out[0]),
+                  _ptr(out[1]), _ptr(running_mean), _ptr(running_var), float(momentum), g, c, _stream())
+    return out[0], out[1]
+
+
+def channel_sum(x, c=None):
+    _req_cuda(x); _req_nhwc(x, 'x')
+    n, cp, h, w = x.shape
+    c = cp if c is None else c
+    out = torch.zeros((c,), dtype=torch.float32, device=x.device)
+    _C.lib().call('imx_channel_sum_nhwc_bf16', _ptr(x), _ptr(out), n * h * w, c, cp, _stream())
+    return out
+
+
+# -------------------------------------------------------------- modulation
+
+def _gb_mode(gamma):
+    if gamma is None:
+        return 2
+    return 0 if gamma.dim() == 4 else 1
+
+
+def spade_modulate_fwd(x, mean, rstd, w, b, gamma, beta, per_instance, act, up2x=False):
+    _req_cuda(x); _req_nhwc(x, 'x')
+    n, c, h, wd = x.shape
+    if up2x:
+        h, wd = 2 * h, 2 * wd
+    mode = _gb_mode(gamma)
+    if mode == 0:
+        _req_nhwc(gamma, 'gamma'); _req_nhwc(beta, 'beta')
+    elif mode == 1:
+        _req_f32c(gamma, 'gamma'); _req_f32c(beta, 'beta')
+    y = empty_nhwc(n, c, h, wd, x.device)
+    _C.lib().call('imx_spade_modulate_fwd', _ptr(x), _ptr(mean), _ptr(rstd), _ptr(w), _ptr(b), _ptr(gamma),
+                  _ptr(beta), _ptr(y), n, h, wd, c, int(per_instance), mode, int(act), int(up2x), _stream())
+    return y
+
+
+def spade_modulate_bwd(x, dy, mean, rstd, w, b, gamma, beta, per_instance, act, count, use_batch_stats=True,
+                       reduce_hook=None):
+    """Returns (dx, dgamma, dbeta, dweight, dbias).  ``reduce_hook(red)`` may all-reduce the
+    (2, G, C) reductions in place across ranks (SyncBatchNorm backward) and return the
+    global element count."""
+    _req_cuda(x, dy); _req_nhwc(x, 'x'); _req_nhwc(dy, 'dy')
+    n, c, h, wd = x.shape
+    mode = _gb_mode(gamma)
+    g = n if per_instance else 1
+    red = torch.zeros((2, g, c), dtype=torch.float32, device=x.device)
+    if mode == 0:
+        dgamma = empty_nhwc(n, c, h, wd, x.device)
+        dbeta = empty_nhwc(n, c, h, wd, x.device)
+    elif mode == 1:
+        dgamma = torch.zeros((n, c), dtype=torch.float32, device=x.device)
+        dbeta = torch.zeros((n, c), dtype=torch.float32, device=x.device)
+    else:
+        dgamma = dbeta = None
+    _C.lib().call('imx_spade_modulate_bwd_reduce', _ptr(x), _ptr(dy), _ptr(mean), _ptr(rstd), _ptr(w), _ptr(b),
+                  _ptr(gamma), _ptr(beta), _ptr(dgamma), _ptr(dbeta), _ptr(red), n, h, wd, c, int(per_instance),
+                  mode, int(act), _stream())
+    # dweight / dbias of the inner norm use the LOCAL reductions (DDP averages them later)
+    dweight = red[1].sum(0) if w is not None else None
+    dbias = red[0].sum(0) if b is not None else None
+    if reduce_hook is not None and use_batch_stats:
+        red = red.clone()
+        count = reduce_hook(red)
+    dx = empty_nhwc(n, c, h, wd, x.device)
+    _C.lib().call('imx_spade_modulate_bwd_dx', _ptr(x), _ptr(dy), _ptr(mean), _ptr(rstd), _ptr(w), _ptr(b),
+                  _ptr(gamma), _ptr(beta), _ptr(red), float(count), _ptr(dx), n, h, wd, c, int(per_instance),
+                  mode, int(act), int(use_batch_stats), _stream())
+    return dx, dgamma, dbeta, dweight, dbias
+
+
+# ------------------------------------------------------------ convolutions
+
+def conv2d_fprop(x, wpk, cout, kh, kw, stride=1, pad=0, bias=None, residual=None, flags=0, stats=None,
+                 cout_p=None, out_f32=False):
+    """x: NHWC bf16 (C = Cin_p), wpk: packed bf16 [Cout, KH, KW, Cin_p]."""
+    _req_cuda(x, wpk); _req_nhwc(x, 'x')
+    n, cin_p, h, w = x.shape
+    if wpk.dtype != torch.bfloat16 or not wpk.is_contiguous() or wpk.shape[-1] != cin_p:
+        raise RuntimeError('packed weight must be contiguous bf16 [rows, KH, KW, Cin_p=%d]; got %s' %
+                           (cin_p, tuple(wpk.shape)))
+    cout_p = round_up(cout, 8) if cout_p is None else cout_p
+    ho = (h + 2 * pad - kh) // stride + 1
+    wo = (w + 2 * pad - kw) // stride + 1
+    out = empty_nhwc(n, cout_p, ho, wo, x.device, torch.float32 if out_f32 else torch.bfloat16)
+    if bias is not None:
+        flags |= EPI_BIAS
+        _req_f32c(bias, 'bias')
+    if residual is not None:
+        flags |= EPI_RESIDUAL
+        _req_nhwc(residual, 'residual')
+        if tuple(residual.shape) != (n, cout_p, ho, wo):
+            raise RuntimeError('residual shape %s does not match the output %s' %
+                               (tuple(residual.shape), (n, cout_p, ho, wo)))
+    if stats is not None:
+        flags |= EPI_STATS
+    if out_f32:
+        flags |= EPI_OUT_F32
+    _C.lib().call('imx_conv2d_igemm_fprop_bf16', _ptr(x), _ptr(wpk), _ptr(bias), _ptr(residual), _ptr(out),
+                  _ptr(stats), n, h, w, cin_p, cout, cout_p, kh, kw, stride, pad, flags, _stream())
+    return out
+
+
+def spade_gb_conv_modulate(hidden, wgb, bias_gamma, bias_beta, x, mean, rstd, w, b, c, kh, kw, pad,
+                           per_instance, act, up2x=False):
+    _req_cuda(hidden, wgb, x); _req_nhwc(hidden, 'hidden'); _req_nhwc(x, 'x')
+    n, ch_p, h, wd = hidden.shape
+    y = empty_nhwc(n, c, h, wd, x.device)
+    _C.lib().call('imx_spade_gb_conv_modulate_bf16', _ptr(hidden), _ptr(wgb), _ptr(bias_gamma), _ptr(bias_beta),
+                  _ptr(x), _ptr(mean), _ptr(rstd), _ptr(w), _ptr(b), _ptr(y), n, h, wd, ch_p, c, kh, kw, pad,
+                  int(per_instance), int(act), int(up2x), _stream())
+    return y
+
+
+def conv2d_wgrad(x, dy, cin, cout, kh, kw, stride=1, pad=0):
+    """dW (fp32, [Cout, Cin, KH, KW]) from x (NHWC bf16, C = Cin_p) and dy (NHWC bf16, C = Cout_p)."""
+    _req_cuda(x, dy); _req_nhwc(x, 'x'); _req_nhwc(dy, 'dy')
+    n, cin_p, h, w = x.shape
+    cout_p = dy.shape[1]
+    lib = _C.lib()
+    nbytes = lib.raw('imx_conv2d_wgrad_workspace_bytes')(n, h, w, cin, cin_p, cout, cout_p, kh, kw, stride, pad)
+    if nbytes < 0:
+        raise _C.ImxError('imx_conv2d_wgrad_workspace_bytes: %s' % lib.last_error())
+    ws = torch.empty((max(int(nbytes), 16),), dtype=torch.uint8, device=x.device)
+    dw = torch.empty((cout, cin, kh, kw), dtype=torch.float32, device=x.device)
+    lib.call('imx_conv2d_igemm_wgrad_bf16', _ptr(x), _ptr(dy), _ptr(dw), _ptr(ws), int(nbytes), n, h, w, cin, cin_p,
+             cout, cout_p, kh, kw, stride, pad, _stream())
+    return dw

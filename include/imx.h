@@ -1,0 +1,250 @@
+/*
+ * imx.h — C ABI of libimx_kernels.so: the B200 (sm_100a) implementation of the
+ * SPADE generator hot path and the vid2vid flow warp of StephChabr/imaginaire.
+ *
+ * This is the drop-in boundary.  Every entry point
+ *   - takes plain device pointers, sizes and a cudaStream_t (passed as void*),
+ *   - launches asynchronously on that stream, never synchronises, never
+ *     allocates device memory, never touches the default stream,
+ *   - returns 0 on success, otherwise a cudaError_t value or an IMX_ERR_* code;
+ *     imx_last_error() returns the calling thread's last message.
+ * Activations are NHWC bf16 ("channels_last" memory of a logical NCHW tensor),
+ * statistics / biases / norm affine parameters are fp32, warp tensors are NCHW
+ * fp32 exactly as the reference's extension takes them.
+ *
+ * "ref:" lines cite the reference interface (path:line under the reference
+ * repository root) that each entry point replaces.
+ */
+#ifndef IMX_H_
+#define IMX_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define IMX_API __attribute__((visibility("default")))
+#else
+#define IMX_API
+#endif
+
+typedef void* imx_stream_t;   /* a cudaStream_t */
+typedef uint16_t imx_bf16;    /* raw bfloat16 bits */
+
+IMX_API int imx_version(void);
+IMX_API const char* imx_last_error(void);
+
+/* ------------------------------------------------------------------ warp -- */
+
+/* out[b,c,y,x] = bilinear sample of img[b,c] at (x+flow[b,0,y,x], y+flow[b,1,y,x]),
+ * tap indices clamped to the OUTPUT dims (H, W), weights not renormalised.
+ * img: B x C x Hi x Wi, flow: B x 2 x H x W, out: B x C x H x W; all contiguous fp32.
+ * kernel_size must be 1.
+ * ref: resample2d_cuda.forward(input1, input2, output, kernel_size)
+ *      imaginaire/third_party/resample2d/src/resample2d_cuda.cc:6-17,
+ *      kernel imaginaire/third_party/resample2d/src/resample2d_kernel.cu:15-75 */
+IMX_API int imx_resample2d_fwd_f32(const float* img, const float* flow, float* out,
+                           int B, int C, int H, int W, int Hi, int Wi,
+                           int kernel_size, imx_stream_t stream);
+
+/* Gradients of the above.  grad_img (B x C x Hi x Wi) MUST be zero-filled by the
+ * caller (scatter with atomics, like the reference); grad_flow (B x 2 x H x W) is
+ * overwritten.  trunc_alpha != 0 reproduces the reference's use of
+ * `xf - int(xf)` (truncation) for the scatter weights; 0 uses floor, which is the
+ * true derivative of the forward for negative coordinates.
+ * ref: resample2d_cuda.backward(...)
+ *      imaginaire/third_party/resample2d/src/resample2d_cuda.cc:19-33,
+ *      kernels resample2d_kernel.cu:78-129 and :131-203 */
+IMX_API int imx_resample2d_bwd_f32(const float* img, const float* flow, const float* grad_out,
+                           float* grad_img, float* grad_flow,
+                           int B, int C, int H, int W, int Hi, int Wi,
+                           int kernel_size, int trunc_alpha, imx_stream_t stream);
+
+/* The warp the vid2vid generators actually call: grid_sample(bilinear, border,
+ * align_corners=True) of img at linspace(-1,1)+flow/((size-1)/2), computed with
+ * the same fp32 operation order as torch (bit-exact against the CPU path) and
+ * without building the grid.  img, out: B x C x H x W fp32; flow: B x 2 x H x W fp32.
+ * ref: resample(image, flow) imaginaire/model_utils/fs_vid2vid.py:14-39,
+ *      get_grid :42-80 */
+IMX_API int imx_gridsample_warp_fwd_f32(const float* img, const float* flow, float* out,
+                                int B, int C, int H, int W, imx_stream_t stream);
+
+/* Gradients of imx_gridsample_warp_fwd_f32 (autograd of the reference's
+ * resample()).  grad_img must be zero-filled by the caller; grad_flow is
+ * overwritten; either may be NULL to skip it. */
+IMX_API int imx_gridsample_warp_bwd_f32(const float* img, const float* flow, const float* grad_out,
+                                float* grad_img, float* grad_flow,
+                                int B, int C, int H, int W, imx_stream_t stream);
+
+/* ------------------------------------------------------- layout helpers -- */
+
+/* Nearest-neighbour resize of an NCHW fp32 conditioning map to NHWC bf16 with
+ * the channel dimension zero-padded to Cp (Cp >= L, Cp % 8 == 0):
+ * dst[n,y,x,c] = src[n,c,floor(y*H/h),floor(x*W/w)].
+ * ref: F.interpolate(cond, size, mode='nearest')
+ *      imaginaire/layers/activation_norm.py:224-225 and
+ *      imaginaire/generators/spade.py:424 */
+IMX_API int imx_nearest_resize_nchw_f32_to_nhwc_bf16(const float* src, imx_bf16* dst,
+                                             int N, int L, int H, int W,
+                                             int h, int w, int Cp, imx_stream_t stream);
+
+/* Nearest x2 upsample, NHWC bf16.  ref: NearestUpsample(scale_factor=2)
+ * imaginaire/generators/spade.py:394-395 */
+IMX_API int imx_upsample2x_nhwc_bf16(const imx_bf16* src, imx_bf16* dst,
+                             int N, int H, int W, int C, imx_stream_t stream);
+/* Its gradient: dst[n,y,x,c] = sum of the 2x2 block of src (N x 2H x 2W x C). */
+IMX_API int imx_upsample2x_bwd_nhwc_bf16(const imx_bf16* src, imx_bf16* dst,
+                                 int N, int H, int W, int C, imx_stream_t stream);
+
+/* NCHW fp32 -> NHWC bf16 (channels zero-padded to Cp) and back (first C of Cp). */
+IMX_API int imx_nchw_f32_to_nhwc_bf16(const float* src, imx_bf16* dst, int N, int C, int H, int W,
+                              int Cp, imx_stream_t stream);
+IMX_API int imx_nhwc_bf16_to_nchw_f32(const imx_bf16* src, float* dst, int N, int C, int H, int W,
+                              int Cp, int apply_tanh, imx_stream_t stream);
+
+/* Conv weight preparation: W_packed[co][kh][kw][ci] (bf16, ci padded to Cin_p with
+ * zeros) = W[co][ci][kh][kw] * (*inv_sigma or 1 if NULL).  With transpose_flip != 0
+ * it instead writes the data-gradient filter Wt[ci][K-1-kh][K-1-kw][co] (co padded to
+ * Cin_p, which then means the padded Cout).
+ * ref: spectral_norm's W/sigma (imaginaire/layers/weight_norm.py:85) fused with the
+ * GEMM-layout repack. */
+IMX_API int imx_pack_conv_weight_bf16(const float* w, const float* inv_sigma, imx_bf16* packed,
+                              int Cout, int Cin, int KH, int KW, int Cin_p,
+                              int transpose_flip, imx_stream_t stream);
+
+/* ----------------------------------------------- normalisation + SPADE -- */
+
+/* Per-channel sums over an NHWC bf16 tensor: sum[g*C+c], sumsq[g*C+c] (fp32),
+ * g = 0 (per_instance == 0: batch statistics over N*HW) or g = n (instance
+ * statistics).  The caller zero-fills sum/sumsq (the kernel accumulates with
+ * atomics across CTAs).
+ * ref: the statistics half of torch.nn.{SyncBatchNorm,BatchNorm2d,InstanceNorm2d}
+ *      built by get_activation_norm_layer, imaginaire/layers/activation_norm.py:377-432 */
+IMX_API int imx_bn_stats_nhwc_bf16(const imx_bf16* x, float* sum, float* sumsq,
+                           int N, int HW, int C, int per_instance, imx_stream_t stream);
+
+/* mean = sum/count, rstd = 1/sqrt(max(sumsq/count - mean^2, 0) + eps) for G*C
+ * entries; if running_mean != NULL (G must be 1) also
+ * running = (1-momentum)*running + momentum*{mean, unbiased var}.
+ * `count` is the number of elements per entry (after any cross-rank all-reduce of
+ * sum/sumsq/count). */
+IMX_API int imx_bn_finalize(const float* sum, const float* sumsq, float count, float eps,
+                    float* mean, float* rstd, float* running_mean, float* running_var,
+                    float momentum, int G, int C, imx_stream_t stream);
+
+/* y = act( ((x-mean)*rstd*w + b) * (1+gamma) + beta ), NHWC bf16, fp32 math.
+ *   stats_per_instance: mean/rstd indexed [n*C+c] instead of [c]
+ *   gamma/beta: full-size NHWC bf16 (gb_mode 0: SPADE), per-sample fp32 vectors
+ *               [n*C+c] (gb_mode 1: AdaptiveNorm), or absent (gb_mode 2: plain norm)
+ *   w, b may be NULL (no affine);  act: 0 none, 1 LeakyReLU(0.2), 2 ReLU
+ *   up2x != 0: x is N x H/2 x W/2 x C and is read through a nearest x2 upsample.
+ * ref: SpatiallyAdaptiveNorm.forward imaginaire/layers/activation_norm.py:211-234,
+ *      AdaptiveNorm.forward :79-106, LeakyReLU(0.2) imaginaire/layers/nonlinearity.py:22 */
+IMX_API int imx_spade_modulate_fwd(const imx_bf16* x, const float* mean, const float* rstd,
+                           const float* w, const float* b,
+                           const void* gamma, const void* beta, imx_bf16* y,
+                           int N, int H, int W, int C,
+                           int stats_per_instance, int gb_mode, int act, int up2x,
+                           imx_stream_t stream);
+
+/* Backward of imx_spade_modulate_fwd, pass 1: given dy, recompute the forward and
+ * write dgamma, dbeta (gb_mode 0: NHWC bf16; gb_mode 1: accumulated into fp32
+ * [n*C+c], caller zero-fills) and accumulate the per-(group,channel) reductions
+ * red[0][g*C+c] = sum dxhat_affine, red[1][g*C+c] = sum dxhat_affine * xn
+ * (fp32, caller zero-fills; these are also dbias / dweight of the inner norm). */
+IMX_API int imx_spade_modulate_bwd_reduce(const imx_bf16* x, const imx_bf16* dy,
+                                  const float* mean, const float* rstd,
+                                  const float* w, const float* b,
+                                  const void* gamma, const void* beta,
+                                  void* dgamma, void* dbeta, float* red,
+                                  int N, int H, int W, int C,
+                                  int stats_per_instance, int gb_mode, int act,
+                                  imx_stream_t stream);
+
+/* Pass 2: dx = rstd*w*( g - mean(g) - xn*mean(g*xn) ), g = dy*act'*(1+gamma), using
+ * the (all-reduced) reductions of pass 1 divided by `count`.  With use_batch_stats
+ * == 0 (eval-mode BatchNorm: running statistics are constants) dx = rstd*w*g. */
+IMX_API int imx_spade_modulate_bwd_dx(const imx_bf16* x, const imx_bf16* dy,
+                              const float* mean, const float* rstd,
+                              const float* w, const float* b,
+                              const void* gamma, const void* beta,
+                              const float* red, float count, imx_bf16* dx,
+                              int N, int H, int W, int C,
+                              int stats_per_instance, int gb_mode, int act,
+                              int use_batch_stats, imx_stream_t stream);
+
+/* ------------------------------------------------- implicit-GEMM convs -- */
+
+/* Epilogue flags for imx_conv2d_igemm_fprop_bf16 */
+#define IMX_EPI_BIAS      1   /* + bias[co] (fp32) */
+#define IMX_EPI_RELU      2
+#define IMX_EPI_LRELU     4   /* LeakyReLU(0.2) */
+#define IMX_EPI_RESIDUAL  8   /* + residual[n,oy,ox,co] (NHWC bf16, same shape as out) */
+#define IMX_EPI_TANH      16
+#define IMX_EPI_STATS     32  /* accumulate per-channel sum / sumsq of the stored
+                                 (bf16-rounded) output into stats[0..Cout) / [Cout..2Cout)
+                                 (fp32 atomics; caller zero-fills) */
+#define IMX_EPI_OUT_F32   64  /* out is fp32 NHWC instead of bf16 */
+
+/* out[n,oy,ox,co] = epilogue( sum_{kh,kw,ci} x[n, oy*stride+kh-pad, ox*stride+kw-pad, ci]
+ *                                            * wpk[co][kh][kw][ci] ), zero padding.
+ * x: N x H x W x Cin_p bf16 (Cin_p % 8 == 0), wpk: Cout x KH x KW x Cin_p bf16 from
+ * imx_pack_conv_weight_bf16, out: N x Ho x Wo x Cout_p (Cout_p >= Cout; channels
+ * >= Cout are written as zero when Cout_p > Cout).  tcgen05 (M=128 pixel tile, N<=256
+ * channel tile, fp32 accumulators in TMEM), operands staged by TMA (128-byte swizzle);
+ * the zero padding is TMA out-of-bounds fill.
+ * The same entry point computes the data gradient of a stride-1 convolution when
+ * given dy as x, the transposed+flipped filter, and pad' = K-1-pad.
+ * ref: torch.nn.Conv2d inside Conv2dBlock, imaginaire/layers/conv.py:93-104, 262-327 */
+IMX_API int imx_conv2d_igemm_fprop_bf16(const imx_bf16* x, const imx_bf16* wpk, const float* bias,
+                                const imx_bf16* residual, void* out, float* stats,
+                                int N, int H, int W, int Cin_p,
+                                int Cout, int Cout_p, int KH, int KW,
+                                int stride, int pad, int flags, imx_stream_t stream);
+
+/* SPADE projection conv fused with the modulation (gamma/beta never reach HBM):
+ *   gb = conv(hidden; wgb) (+bias), wgb rows interleaved per 64-channel block as
+ *   [64 gamma rows | 64 beta rows] (imx_pack_spade_gb_weight_bf16),
+ *   y[n,p,c] = act( ((x-mean)*rstd*w+b) * (1+gamma) + beta ).
+ * hidden: N x H x W x Ch_p bf16; x, y: N x H x W x C bf16 (x at half resolution when
+ * up2x != 0).  Same tiling as the plain conv; the epilogue reads the x tile.
+ * ref: imaginaire/layers/activation_norm.py:226-233 */
+IMX_API int imx_spade_gb_conv_modulate_bf16(const imx_bf16* hidden, const imx_bf16* wgb,
+                                    const float* bias_gamma, const float* bias_beta,
+                                    const imx_bf16* x, const float* mean, const float* rstd,
+                                    const float* w, const float* b, imx_bf16* y,
+                                    int N, int H, int W, int Ch_p, int C, int KH, int KW, int pad,
+                                    int stats_per_instance, int act, int up2x,
+                                    imx_stream_t stream);
+
+IMX_API int imx_pack_spade_gb_weight_bf16(const float* w_gamma, const float* w_beta,
+                                  const float* inv_sigma_gamma, const float* inv_sigma_beta,
+                                  imx_bf16* packed, int C, int Ch, int KH, int KW, int Ch_p,
+                                  imx_stream_t stream);
+
+/* Weight gradient: dw[co][ci][kh][kw] (fp32, PyTorch layout, overwritten) =
+ * sum_{n,oy,ox} dy[n,oy,ox,co] * x[n, oy*stride+kh-pad, ox*stride+kw-pad, ci].
+ * x: N x H x W x Cin_p bf16, dy: N x Ho x Wo x Cout_p bf16.  `workspace` is caller-owned
+ * scratch of at least imx_conv2d_wgrad_workspace_bytes(...) bytes (split-K partial
+ * sums over the N*Ho*Wo reduction); it need not be initialised.
+ * ref: autograd of torch.nn.Conv2d (imaginaire/layers/conv.py:93-104) */
+IMX_API int imx_conv2d_igemm_wgrad_bf16(const imx_bf16* x, const imx_bf16* dy, float* dw,
+                                void* workspace, int64_t workspace_bytes,
+                                int N, int H, int W, int Cin, int Cin_p,
+                                int Cout, int Cout_p, int KH, int KW,
+                                int stride, int pad, imx_stream_t stream);
+IMX_API int64_t imx_conv2d_wgrad_workspace_bytes(int N, int H, int W, int Cin, int Cin_p,
+                                         int Cout, int Cout_p, int KH, int KW,
+                                         int stride, int pad);
+
+/* Per-channel sum over pixels of an NHWC bf16 tensor (bias gradient):
+ * out[c] = sum_{n,p} x[n,p,c]; fp32, caller zero-fills. */
+IMX_API int imx_channel_sum_nhwc_bf16(const imx_bf16* x, float* out, int NP, int C, int Cp,
+                              imx_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif  /* IMX_H_ */
