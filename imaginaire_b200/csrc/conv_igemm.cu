@@ -288,8 +288,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                             if (lane == j) { s_mine = s; q_mine = qq; }
                         }
                         if (nb + lane < p.Cout) {
-                            atomicAdd(p.stats + nb + lane, s_mine);
-                            atomicAdd(p.stats + p.Cout + nb + lane, q_mine);
+                            // layout (2, G, Cout): G = 1 (batch statistics) or N (instance statistics)
+                            const bool inst = (p.flags & IMX_EPI_STATS_INSTANCE) != 0;
+                            float* sdst = p.stats + (inst ? (size_t)img * p.Cout : 0) + nb + lane;
+                            atomicAdd(sdst, s_mine);
+                            atomicAdd(sdst + (size_t)(inst ? p.N : 1) * p.Cout, q_mine);
                         }
                     }
                 }

@@ -66,11 +66,13 @@ resample2d_fwd_kernel(const float* __restrict__ img, const float* __restrict__ f
     const float* fl = flow + (size_t)b * 2 * hw + (size_t)y * W + x;
     const float dx = __ldg(fl), dy = __ldg(fl + hw);
     const Taps t = r2d_taps(dx, dy, x, y, W, H);  // clamps against the OUTPUT dims (:31-34)
-    // The reference forms each weight in double ((1. - alpha) promotes) and rounds
-    // each product to float before the float accumulation (:59-62).
+    // The reference forms the three weights that contain the literal `1.` in double
+    // ((1. - alpha) promotes) and rounds each product to float before the float
+    // accumulation; `alpha * beta * I` has no double operand and stays in float (:59-62).
     const double a = t.alpha, be = t.beta;
     const double w00 = (1. - a) * (1. - be), w01 = a * (1. - be);
-    const double w10 = (1. - a) * be, w11 = a * be;
+    const double w10 = (1. - a) * be;
+    const float w11 = __fmul_rn(t.alpha, t.beta);
     const int oTL = t.yT * Wi + t.xL, oTR = t.yT * Wi + t.xR;
     const int oBL = t.yB * Wi + t.xL, oBR = t.yB * Wi + t.xR;
     const int c1 = min(C, c0 + cpb);
@@ -82,7 +84,7 @@ resample2d_fwd_kernel(const float* __restrict__ img, const float* __restrict__ f
         v += static_cast<float>(w00 * (double)__ldg(ip + oTL));
         v += static_cast<float>(w01 * (double)__ldg(ip + oTR));
         v += static_cast<float>(w10 * (double)__ldg(ip + oBL));
-        v += static_cast<float>(w11 * (double)__ldg(ip + oBR));
+        v += __fmul_rn(w11, __ldg(ip + oBR));
         __stcs(op, v);
     }
 }
@@ -275,6 +277,7 @@ gridsample_warp_bwd_kernel(const float* __restrict__ img, const float* __restric
 extern "C" int imx_resample2d_fwd_f32(const float* img, const float* flow, float* out,
                                       int B, int C, int H, int W, int Hi, int Wi,
                                       int kernel_size, imx_stream_t stream) {
+    if (B == 0 || C == 0 || H == 0 || W == 0) return IMX_OK;
     IMX_REQUIRE(img && flow && out, "resample2d_fwd: null pointer");
     IMX_REQUIRE(kernel_size == 1, "resample2d_fwd: kernel_size must be 1 (got %d)", kernel_size);
     IMX_REQUIRE(B >= 0 && C >= 0 && H >= 0 && W >= 0, "resample2d_fwd: negative size");
@@ -292,6 +295,7 @@ extern "C" int imx_resample2d_bwd_f32(const float* img, const float* flow, const
                                       float* grad_img, float* grad_flow,
                                       int B, int C, int H, int W, int Hi, int Wi,
                                       int kernel_size, int trunc_alpha, imx_stream_t stream) {
+    if (B == 0 || H == 0 || W == 0) return IMX_OK;
     IMX_REQUIRE(img && flow && grad_out, "resample2d_bwd: null pointer");
     IMX_REQUIRE(kernel_size == 1, "resample2d_bwd: kernel_size must be 1 (got %d)", kernel_size);
     IMX_REQUIRE(B >= 0 && C >= 0 && H >= 0 && W >= 0, "resample2d_bwd: negative size");
@@ -306,6 +310,7 @@ extern "C" int imx_resample2d_bwd_f32(const float* img, const float* flow, const
 
 extern "C" int imx_gridsample_warp_fwd_f32(const float* img, const float* flow, float* out,
                                            int B, int C, int H, int W, imx_stream_t stream) {
+    if (B == 0 || C == 0 || H == 0 || W == 0) return IMX_OK;
     IMX_REQUIRE(img && flow && out, "gridsample_warp_fwd: null pointer");
     IMX_REQUIRE(B >= 0 && C >= 0 && H >= 0 && W >= 0, "gridsample_warp_fwd: negative size");
     if ((long)B * C * H * W == 0) return IMX_OK;
@@ -321,6 +326,7 @@ extern "C" int imx_gridsample_warp_fwd_f32(const float* img, const float* flow, 
 extern "C" int imx_gridsample_warp_bwd_f32(const float* img, const float* flow, const float* grad_out,
                                            float* grad_img, float* grad_flow,
                                            int B, int C, int H, int W, imx_stream_t stream) {
+    if (B == 0 || H == 0 || W == 0) return IMX_OK;
     IMX_REQUIRE(img && flow && grad_out, "gridsample_warp_bwd: null pointer");
     IMX_REQUIRE(B >= 0 && C >= 0 && H >= 0 && W >= 0, "gridsample_warp_bwd: negative size");
     IMX_REQUIRE(B <= 65535, "gridsample_warp_bwd: batch too large");

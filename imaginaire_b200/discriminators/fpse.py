@@ -1,0 +1,63 @@
+"""Feature-pyramid semantics-embedding discriminator.
+ref: imaginaire/discriminators/fpse.py:15-132
+
+Convolutions run on the native kernels; the few glue operations between them (bilinear
+x2 upsample, 2x2 average pooling, the label-embedding inner product) are torch
+elementwise / pooling calls on the bf16 NHWC tensors.
+"""
+import functools
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+from torch import nn
+
+from ..layers import Conv2dBlock
+
+
+class FPSEDiscriminator(nn.Module):
+    def __init__(self, num_input_channels, num_labels, num_filters, kernel_size, weight_norm_type,
+                 activation_norm_type):
+        super().__init__()
+        padding = int(np.ceil((kernel_size - 1.0) / 2))
+        common = dict(weight_norm_type=weight_norm_type, activation_norm_type=activation_norm_type,
+                      nonlinearity='leakyrelu', order='CNA')
+        same = functools.partial(Conv2dBlock, kernel_size=kernel_size, stride=1, padding=padding, **common)
+        down = functools.partial(Conv2dBlock, kernel_size=kernel_size, stride=2, padding=padding, **common)
+        lat = functools.partial(Conv2dBlock, kernel_size=1, stride=1, **common)
+        f = num_filters
+        self.enc1 = down(num_input_channels, f)
+        self.enc2 = down(1 * f, 2 * f)
+        self.enc3 = down(2 * f, 4 * f)
+        self.enc4 = down(4 * f, 8 * f)
+        self.enc5 = down(8 * f, 8 * f)
+        self.lat2 = lat(2 * f, 4 * f)
+        self.lat3 = lat(4 * f, 4 * f)
+        self.lat4 = lat(8 * f, 4 * f)
+        self.lat5 = lat(8 * f, 4 * f)
+        self.upsample2x = nn.Upsample(scale_factor=2, mode='bilinear', align_corners=False)
+        self.final2 = same(4 * f, 2 * f)
+        self.final3 = same(4 * f, 2 * f)
+        self.final4 = same(4 * f, 2 * f)
+        self.output = Conv2dBlock(f * 2, 1, kernel_size=1)
+        self.seg = Conv2dBlock(f * 2, f * 2, kernel_size=1)
+        self.embedding = Conv2dBlock(num_labels, f * 2, kernel_size=1)
+
+    def forward(self, images, segmaps):
+        feat11 = self.enc1(images)
+        feat12 = self.enc2(feat11)
+        feat13 = self.enc3(feat12)
+        feat14 = self.enc4(feat13)
+        feat15 = self.enc5(feat14)
+        feat25 = self.lat5(feat15)
+        feat24 = self.upsample2x(feat25) + self.lat4(feat14)
+        feat23 = self.upsample2x(feat24) + self.lat3(feat13)
+        feat22 = self.upsample2x(feat23) + self.lat2(feat12)
+        feats = (self.final2(feat22), self.final3(feat23), self.final4(feat24))
+        segemb = F.avg_pool2d(self.embedding(segmaps), kernel_size=2, stride=2)
+        preds = []
+        for feat in feats:
+            segemb = F.avg_pool2d(segemb, kernel_size=2, stride=2)
+            pred = self.output(feat) + torch.mul(segemb, self.seg(feat)).sum(dim=1, keepdim=True)
+            preds.append(pred)
+        return tuple(preds)

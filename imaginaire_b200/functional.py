@@ -1,0 +1,317 @@
+"""Differentiable building blocks of the SPADE hot path on top of ops.py.
+
+Each class is a ``torch.autograd.Function`` whose forward AND backward run the
+hand-written kernels of libimx_kernels.so; PyTorch only keeps the graph.
+Activations are bf16 NHWC (channels_last) tensors with the channel count padded
+to a multiple of 8 (padding channels are zero).
+"""
+import torch
+import torch.distributed as dist
+
+from . import ops
+
+ACT_CODES = ops.ACT_CODES
+
+
+# ------------------------------------------------------------ layout glue
+
+class _ToNHWC(torch.autograd.Function):
+    """NCHW float -> NHWC bf16 (channels zero-padded to a multiple of 8)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        ctx.c = x.shape[1]
+        ctx.in_dtype = x.dtype
+        return ops.nchw_f32_to_nhwc_bf16(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        return ops.nhwc_bf16_to_nchw_f32(_as_nhwc(g), ctx.c).to(ctx.in_dtype)
+
+
+class _ToNCHW(torch.autograd.Function):
+    """NHWC bf16 -> contiguous NCHW fp32 (first c channels), optional tanh."""
+
+    @staticmethod
+    def forward(ctx, x, c, apply_tanh):
+        y = ops.nhwc_bf16_to_nchw_f32(x, c, apply_tanh)
+        ctx.cp = x.shape[1]
+        ctx.apply_tanh = apply_tanh
+        if apply_tanh:
+            ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        if ctx.apply_tanh:
+            (y,) = ctx.saved_tensors
+            g = g * (1.0 - y * y)
+        return ops.nchw_f32_to_nhwc_bf16(g.contiguous(), ctx.cp), None, None
+
+
+def _as_nhwc(t):
+    """Makes a gradient tensor NHWC bf16 (autograd may hand back other layouts)."""
+    if ops.is_nhwc_bf16(t):
+        return t
+    return t.to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+
+
+def to_nhwc(x):
+    """Any 4-D CUDA float tensor -> the internal activation layout."""
+    if ops.is_nhwc_bf16(x) and x.shape[1] % 8 == 0:
+        return x
+    if x.dtype == torch.bfloat16 and x.shape[1] % 8 == 0:
+        return x.contiguous(memory_format=torch.channels_last)
+    return _ToNHWC.apply(x)
+
+
+def to_nchw(x, channels=None, apply_tanh=False):
+    return _ToNCHW.apply(x, x.shape[1] if channels is None else channels, apply_tanh)
+
+
+class _Upsample2x(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        return ops.upsample2x(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        return ops.upsample2x_bwd(_as_nhwc(g))
+
+
+def upsample2x(x):
+    y = _Upsample2x.apply(x)
+    st = getattr(x, '_imx_stats', None)
+    if st is not None:
+        # every element is replicated 4 times: sums and count scale by 4, mean/var do not change
+        sums, per_instance, count = st
+        y._imx_stats = (sums * 4.0, per_instance, count * 4)
+    return y
+
+
+# ------------------------------------------------------------ convolution
+
+def _act_backward(dy, y, act):
+    """Gradient through an activation that was fused into a conv epilogue (y = act(pre))."""
+    if act == ops.ACT_LRELU:
+        return torch.where(y > 0, dy, dy * 0.2)
+    if act == ops.ACT_RELU:
+        return torch.where(y > 0, dy, torch.zeros_like(dy))
+    return dy
+
+
+class _Conv2d(torch.autograd.Function):
+    """y = act(conv(x, w) + bias) (+ residual); x, y NHWC bf16; w fp32 [Cout, Cin, KH, KW]."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, residual, stride, pad, act, stats):
+        cout, cin, kh, kw = weight.shape
+        cin_p = x.shape[1]
+        wpk = ops.pack_conv_weight(weight, None, cin_p=cin_p)
+        flags = {ops.ACT_NONE: 0, ops.ACT_LRELU: ops.EPI_LRELU, ops.ACT_RELU: ops.EPI_RELU}[act]
+        y = ops.conv2d_fprop(x, wpk, cout, kh, kw, stride, pad, bias=bias, residual=residual, flags=flags,
+                             stats=stats)
+        ctx.stride, ctx.pad, ctx.act = stride, pad, act
+        ctx.geom = (cout, cin, kh, kw, x.shape[2], x.shape[3])
+        ctx.has_bias = bias is not None
+        ctx.has_res = residual is not None
+        needs_y = act != ops.ACT_NONE
+        ctx.save_for_backward(x, weight, y if needs_y else None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight, y = ctx.saved_tensors
+        cout, cin, kh, kw, h, w = ctx.geom
+        dy = _as_nhwc(dy)
+        if y is not None:
+            dy = _act_backward(dy, y, ctx.act)
+        dx = dw = db = dres = None
+        if ctx.needs_input_grad[0]:
+            dx = conv2d_dgrad(dy, weight, ctx.stride, ctx.pad, h, w, x.shape[1])
+        if ctx.needs_input_grad[1]:
+            dw = ops.conv2d_wgrad(x, dy, cin, cout, kh, kw, ctx.stride, ctx.pad)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            db = ops.channel_sum(dy, cout)
+        if ctx.has_res and ctx.needs_input_grad[3]:
+            dres = dy
+        return dx, dw, db, dres, None, None, None, None
+
+
+def conv2d_dgrad(dy, weight, stride, pad, h, w, cin_p):
+    """Data gradient of conv2d as a stride-1 convolution of dy with the transposed,
+    spatially flipped filter.  A stride-2 forward is handled by zero-insertion."""
+    cout, cin, kh, kw = weight.shape
+    cout_p = dy.shape[1]
+    wt = ops.pack_conv_weight(weight, None, cin_p=cout_p, transpose_flip=True)   # [Cin, KH, KW, Cout_p]
+    if stride != 1:
+        n, _, ho, wo = dy.shape
+        dh = (ho - 1) * stride + 1 + (h + 2 * pad - kh) % stride
+        dw_ = (wo - 1) * stride + 1 + (w + 2 * pad - kw) % stride
+        z = torch.zeros((n, dh, dw_, cout_p), dtype=torch.bfloat16, device=dy.device).permute(0, 3, 1, 2)
+        z[:, :, 0:(ho - 1) * stride + 1:stride, 0:(wo - 1) * stride + 1:stride] = dy
+        dy = z
+    if kh != kw:
+        raise RuntimeError('conv2d_dgrad: only square kernels are supported')
+    return ops.conv2d_fprop(dy, wt, cin, kh, kw, 1, kh - 1 - pad, cout_p=cin_p)
+
+
+def conv2d(x, weight, bias=None, residual=None, stride=1, pad=0, act=ops.ACT_NONE, stats_mode=None):
+    """stats_mode='batch' | 'instance': the epilogue also accumulates the per-channel sum / sum of squares
+    of the stored output, attached to the result for the consuming norm layer."""
+    stats = None
+    if stats_mode in ('batch', 'instance'):
+        g = x.shape[0] if stats_mode == 'instance' else 1
+        stats = torch.zeros((2, g, weight.shape[0]), dtype=torch.float32, device=x.device)
+    y = _Conv2d.apply(x, weight, bias, residual, stride, pad, act, stats)
+    if stats is not None:
+        n, _, ho, wo = y.shape
+        y._imx_stats = (stats, stats_mode == 'instance', ho * wo if stats_mode == 'instance' else n * ho * wo)
+    return y
+
+
+# ---------------------------------------------------- normalisation + SPADE
+
+class NormState:
+    """What the fused kernels need from the inner norm module (parameters stay owned by
+    the torch.nn norm module so state-dict keys are the reference's)."""
+
+    def __init__(self, kind, weight, bias, running_mean, running_var, momentum, eps, training,
+                 track_running_stats, num_batches_tracked=None, process_group=None):
+        self.kind = kind                      # 'batch' | 'sync_batch' | 'instance'
+        self.weight, self.bias = weight, bias
+        self.running_mean, self.running_var = running_mean, running_var
+        self.momentum, self.eps = momentum, eps
+        self.training = training
+        self.track_running_stats = track_running_stats
+        self.num_batches_tracked = num_batches_tracked
+        self.process_group = process_group
+
+    @property
+    def per_instance(self):
+        return self.kind == 'instance'
+
+    @property
+    def use_batch_stats(self):
+        return self.kind == 'instance' or self.training or self.running_mean is None
+
+
+def _world(ns):
+    if ns.kind != 'sync_batch' or not ns.training:
+        return 1
+    if not (dist.is_available() and dist.is_initialized()):
+        return 1
+    return dist.get_world_size(ns.process_group)
+
+
+def compute_norm_stats(x, ns, up2x=False):
+    """mean / rstd of x for the given inner norm (and the running-stat update).
+
+    Statistics attached to x by the producing kernel's epilogue are used when present;
+    otherwise the standalone statistics kernel runs.  SyncBatchNorm all-reduces
+    [sum, sumsq, count] over the process group (NCCL on the compute stream).
+    Returns (mean, rstd, count) with mean/rstd shaped (G*C,).
+    """
+    n, c, h, w = x.shape
+    if not ns.use_batch_stats:
+        rstd = torch.rsqrt(ns.running_var.float() + ns.eps)
+        return ns.running_mean.float().contiguous(), rstd.contiguous(), n * h * w
+    st = getattr(x, '_imx_stats', None)
+    if st is not None and st[1] == ns.per_instance and st[0].shape[-1] == c:
+        sums, _, count = st
+    else:
+        sums = ops.bn_stats(x, ns.per_instance)
+        count = h * w if ns.per_instance else n * h * w
+    world = _world(ns)
+    if world > 1:
+        # one message of 2C+1 floats: [sum, sumsq, count]; everything stays on the device
+        packed = torch.cat([sums.reshape(-1), sums.new_tensor([float(count)])])
+        dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=ns.process_group)
+        gsums = packed[:-1].view_as(sums)
+        count_t = packed[-1]
+        mean = (gsums[0] / count_t).reshape(-1)
+        var = (gsums[1].reshape(-1) / count_t - mean * mean).clamp_min_(0.0)
+        rstd = torch.rsqrt(var + ns.eps)
+        if ns.track_running_stats and ns.running_mean is not None:
+            _update_running(ns, mean, var * (count_t / (count_t - 1.0)))
+        # the backward kernels take the global element count as a host scalar: equal
+        # per-rank batches (DistributedSampler) are assumed there
+        return mean.contiguous(), rstd.contiguous(), count * world
+    update = ns.training and ns.track_running_stats and ns.running_mean is not None and not ns.per_instance
+    momentum = _momentum(ns) if update else 0.0
+    mean, rstd = ops.bn_finalize(sums, count, ns.eps, ns.running_mean if update else None,
+                                 ns.running_var if update else None, momentum)
+    return mean, rstd, count
+
+
+def _momentum(ns):
+    if ns.num_batches_tracked is not None:
+        ns.num_batches_tracked.add_(1)
+    if ns.momentum is None:   # cumulative moving average (calibrate_batch_norm_momentum)
+        return 1.0 / float(ns.num_batches_tracked.item())
+    return ns.momentum
+
+
+def _update_running(ns, mean, unbiased_var):
+    m = _momentum(ns)
+    ns.running_mean.mul_(1.0 - m).add_(mean, alpha=m)
+    ns.running_var.mul_(1.0 - m).add_(unbiased_var, alpha=m)
+
+
+class _SpadeNormAct(torch.autograd.Function):
+    """y = act(norm(x) * (1 + gamma) + beta) with materialised gamma/beta (NHWC bf16),
+    per-sample gamma/beta vectors (AdaptiveNorm) or none (plain norm)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, gamma, beta, mean, rstd, count, per_instance, act, use_batch_stats, sync):
+        y = ops.spade_modulate_fwd(x, mean, rstd, weight, bias, gamma, beta, per_instance, act)
+        ctx.save_for_backward(x, weight, bias, gamma, beta, mean, rstd)
+        ctx.cfg = (count, per_instance, act, use_batch_stats, sync)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight, bias, gamma, beta, mean, rstd = ctx.saved_tensors
+        count, per_instance, act, use_batch_stats, sync = ctx.cfg
+        hook = None
+        if sync is not None:
+            group, world = sync
+
+            def hook(red):
+                # SyncBatchNorm backward: all-reduce [sum dy', sum dy'*xn] (2C floats)
+                dist.all_reduce(red, op=dist.ReduceOp.SUM, group=group)
+                return count
+        dx, dg, db, dwt, dbs = ops.spade_modulate_bwd(x, _as_nhwc(dy), mean, rstd, weight, bias, gamma, beta,
+                                                      per_instance, act, count, use_batch_stats, hook)
+        if not ctx.needs_input_grad[1]:
+            dwt = None
+        if not ctx.needs_input_grad[2]:
+            dbs = None
+        return dx, dwt, dbs, dg, db, None, None, None, None, None, None, None
+
+
+def spade_norm_act(x, ns, gamma, beta, act):
+    """Fused inner norm + modulation + activation (differentiable)."""
+    mean, rstd, count = compute_norm_stats(x, ns)
+    sync = None
+    world = _world(ns)
+    if world > 1:
+        sync = (ns.process_group, world)
+    w = ns.weight.float() if ns.weight is not None else None
+    b = ns.bias.float() if ns.bias is not None else None
+    return _SpadeNormAct.apply(x, w, b, gamma, beta, mean, rstd, count, ns.per_instance, act,
+                               ns.use_batch_stats, sync)
+
+
+def spade_gb_fused(hidden, w_gamma, w_beta, b_gamma, b_beta, x, ns, act, pad):
+    """No-grad fast path: the gamma/beta projection conv applies the modulation in its
+    epilogue, so gamma and beta never reach HBM."""
+    mean, rstd, _ = compute_norm_stats(x, ns)
+    c, ch, kh, kw = w_gamma.shape
+    wgb = ops.pack_spade_gb_weight(w_gamma, w_beta, ch_p=hidden.shape[1])
+    w = ns.weight.float() if ns.weight is not None else None
+    b = ns.bias.float() if ns.bias is not None else None
+    if w is None and b is not None:
+        w = torch.ones_like(b)
+    return ops.spade_gb_conv_modulate(hidden, wgb, b_gamma, b_beta, x, mean, rstd, w, b, c, kh, kw, pad,
+                                      ns.per_instance, act)

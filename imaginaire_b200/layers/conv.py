@@ -1,0 +1,218 @@
+"""Convolution / linear blocks with the reference's module API, running on the native
+sm_100a kernels.
+
+ref: imaginaire/layers/conv.py:14-135 (_BaseConvBlock), :138-191 (LinearBlock),
+     :262-327 (Conv2dBlock)
+
+Same constructor arguments, same ``layers`` ModuleDict (keys ``conv`` / ``noise`` /
+``norm`` / ``nonlinearity`` in ``order``), same ``conditional`` attribute and the same
+parameter names, so a reference ``state_dict`` loads with ``strict=True``.  What
+differs is how ``forward`` executes: a 2-D block converts its input once to the
+internal activation layout (NHWC bf16) and runs
+
+  * 'C'  -> the tcgen05 implicit-GEMM convolution (bias, a following LeakyReLU/ReLU,
+            a residual add and the next norm's statistics fused into its epilogue),
+  * 'N'(+'A') -> one fused normalise * (1+gamma) + beta -> activation kernel,
+
+instead of one cuDNN / ATen launch per operation.  There is no cuDNN dispatch and
+no CPU path: CPU tensors raise.
+"""
+from types import SimpleNamespace
+
+import torch
+from torch import nn
+from torch.nn import functional as F
+
+from .. import functional as NF
+from .. import ops
+from .misc import ApplyNoise
+
+
+class Conv2d(nn.Conv2d):
+    """nn.Conv2d as the parameter owner (identical init, keys and spectral-norm hooks);
+    the computation is ops.conv2d_fprop."""
+
+    def effective_weight(self):
+        """Runs the weight-norm forward pre-hooks (spectral norm's power iteration and
+        W / sigma) without calling the module, and returns the weight to convolve with."""
+        for hook in self._forward_pre_hooks.values():
+            hook(self, None)
+        return self.weight
+
+    def _check_supported(self):
+        if self.groups != 1 or tuple(self.dilation) != (1, 1) or self.padding_mode != 'zeros':
+            raise NotImplementedError('native Conv2d supports groups=1, dilation=1, zero padding only')
+        if self.kernel_size[0] != self.kernel_size[1] or self.stride[0] != self.stride[1] or \
+                self.padding[0] != self.padding[1] or self.stride[0] not in (1, 2):
+            raise NotImplementedError('native Conv2d supports square kernels, stride 1 or 2, symmetric padding')
+
+    def native_forward(self, x, act=ops.ACT_NONE, residual=None, stats_mode=None):
+        self._check_supported()
+        weight = self.effective_weight()
+        return NF.conv2d(x, weight, self.bias, residual, self.stride[0], self.padding[0], act, stats_mode)
+
+    def forward(self, x):
+        return self.native_forward(NF.to_nhwc(x))
+
+
+_FUSABLE_ACT = {nn.LeakyReLU: ops.ACT_LRELU, nn.ReLU: ops.ACT_RELU}
+
+
+def _act_code(layer):
+    """ACT_* code if the activation module can be folded into a native kernel, else None."""
+    code = _FUSABLE_ACT.get(type(layer))
+    if code == ops.ACT_LRELU and abs(layer.negative_slope - 0.2) > 1e-12:
+        return None
+    return code
+
+
+class _BaseConvBlock(nn.Module):
+    def __init__(self, in_channels, out_channels, kernel_size, stride,
+                 padding, dilation, groups, bias, padding_mode,
+                 weight_norm_type, weight_norm_params,
+                 activation_norm_type, activation_norm_params,
+                 nonlinearity, inplace_nonlinearity,
+                 apply_noise, order, input_dim):
+        super().__init__()
+        from .activation_norm import get_activation_norm_layer
+        from .nonlinearity import get_nonlinearity_layer
+        from .weight_norm import get_weight_norm_layer
+        self.weight_norm_type = weight_norm_type
+        self.input_dim = input_dim
+        self._out_channels = out_channels
+
+        # Construction order (conv -> noise -> norm -> nonlinearity) follows the reference so
+        # that a seeded build draws the same random numbers (conv.py:32-57).
+        wn_params = vars(weight_norm_params) if weight_norm_params is not None else {}
+        conv_layer = get_weight_norm_layer(weight_norm_type, **wn_params)(
+            self._get_conv_layer(in_channels, out_channels, kernel_size, stride, padding, dilation,
+                                 groups, bias, padding_mode, input_dim))
+        noise_layer = ApplyNoise() if apply_noise else None
+        conv_first = order.find('C') < order.find('N')
+        an_params = vars(activation_norm_params) if activation_norm_params is not None else {}
+        norm_layer = get_activation_norm_layer(out_channels if conv_first else in_channels,
+                                               activation_norm_type, input_dim, **an_params)
+        act_layer = get_nonlinearity_layer(nonlinearity, inplace=inplace_nonlinearity)
+
+        self.layers = nn.ModuleDict()
+        for op in order:
+            name, layer = {'C': ('conv', conv_layer), 'N': ('norm', norm_layer),
+                           'A': ('nonlinearity', act_layer)}[op]
+            if layer is None:
+                continue
+            self.layers[name] = layer
+            if op == 'C' and noise_layer is not None:
+                self.layers['noise'] = noise_layer
+
+        self.conditional = getattr(conv_layer, 'conditional', False) or \
+            getattr(norm_layer, 'conditional', False)
+
+    def _get_conv_layer(self, in_channels, out_channels, kernel_size, stride, padding, dilation,
+                        groups, bias, padding_mode, input_dim):
+        if input_dim == 0:
+            return nn.Linear(in_channels, out_channels, bias)
+        if input_dim == 2:
+            return Conv2d(in_channels, out_channels, kernel_size, stride, padding, dilation, groups,
+                          bias, padding_mode)
+        raise NotImplementedError('Conv%dd blocks are outside the SPADE hot path' % input_dim)
+
+    # ---------------------------------------------------------------- forward
+    def forward(self, x, *cond_inputs, **kw_cond_inputs):
+        if self.input_dim == 2:
+            y = self.forward_native(x, cond_inputs, kw_cond_inputs)
+            # internal tensors carry channels padded to a multiple of 8 (zeros); callers of the
+            # public API see the logical channel count
+            return y if y.shape[1] == self._out_channels else y[:, :self._out_channels]
+        # Linear blocks (style code MLPs): tiny GEMMs, plain torch (cuBLAS) calls.
+        for layer in self.layers.values():
+            if getattr(layer, 'conditional', False):
+                x = layer(x, *cond_inputs, **kw_cond_inputs)
+            else:
+                x = layer(x)
+        return x
+
+    def forward_native(self, x, cond_inputs=(), kw_cond_inputs=None, residual=None, stats_mode=None):
+        """2-D forward on the native kernels.
+
+        residual: NHWC bf16 tensor added in the epilogue of the block's convolution.
+        stats_mode: 'batch' / 'instance' -> the convolution's epilogue also produces the
+            statistics that the next normalisation layer needs (only honoured when the
+            convolution is the last operation of the block).
+        """
+        kw_cond_inputs = kw_cond_inputs or {}
+        x = NF.to_nhwc(x)
+        items = list(self.layers.items())
+        i = 0
+        while i < len(items):
+            name, layer = items[i]
+            nxt = items[i + 1] if i + 1 < len(items) else None
+            fused_act = ops.ACT_NONE
+            if name in ('conv', 'norm') and nxt is not None and nxt[0] == 'nonlinearity' and \
+                    _act_code(nxt[1]) is not None:
+                fused_act = _act_code(nxt[1])
+            if name == 'conv':
+                last = (i + (2 if fused_act else 1)) >= len(items)
+                x = layer.native_forward(x, act=fused_act, residual=residual if last else None,
+                                         stats_mode=stats_mode if last else None)
+                if last:
+                    residual = None
+            elif name == 'norm':
+                from .activation_norm import apply_norm_layer
+                x = apply_norm_layer(layer, x, cond_inputs, kw_cond_inputs, fused_act)
+            elif name == 'nonlinearity':
+                x = self._standalone_act(layer, x)
+            else:   # noise
+                x = layer(x)
+            i += 2 if fused_act else 1
+        if residual is not None:
+            x = x + residual
+        return x
+
+    @staticmethod
+    def _standalone_act(layer, x):
+        # An activation with no producer in this block (order 'A..'): elementwise torch op
+        # on the bf16 NHWC tensor (layout preserved).
+        if isinstance(layer, nn.LeakyReLU):
+            return F.leaky_relu(x, layer.negative_slope)
+        if isinstance(layer, nn.ReLU):
+            return F.relu(x)
+        return layer(x)
+
+    def __repr__(self):
+        lines = []
+        for name, layer in self.layers.items():
+            text = repr(layer)
+            if name == 'conv' and self.weight_norm_type not in ('none', ''):
+                text = text[:-1] + ', weight_norm={})'.format(self.weight_norm_type)
+            lines.append('  ' + text.replace('\n', '\n  '))
+        return self._get_name() + '(\n' + '\n'.join(lines) + '\n)'
+
+
+class LinearBlock(_BaseConvBlock):
+    """ref: imaginaire/layers/conv.py:138-191"""
+
+    def __init__(self, in_features, out_features, bias=True,
+                 weight_norm_type='none', weight_norm_params=None,
+                 activation_norm_type='none', activation_norm_params=None,
+                 nonlinearity='none', inplace_nonlinearity=False,
+                 apply_noise=False, order='CNA'):
+        super().__init__(in_features, out_features, None, None, None, None, None, bias, None,
+                         weight_norm_type, weight_norm_params,
+                         activation_norm_type, activation_norm_params,
+                         nonlinearity, inplace_nonlinearity, apply_noise, order, 0)
+
+
+class Conv2dBlock(_BaseConvBlock):
+    """ref: imaginaire/layers/conv.py:262-327"""
+
+    def __init__(self, in_channels, out_channels, kernel_size, stride=1,
+                 padding=0, dilation=1, groups=1, bias=True,
+                 padding_mode='zeros',
+                 weight_norm_type='none', weight_norm_params=None,
+                 activation_norm_type='none', activation_norm_params=None,
+                 nonlinearity='none', inplace_nonlinearity=False,
+                 apply_noise=False, order='CNA'):
+        super().__init__(in_channels, out_channels, kernel_size, stride, padding, dilation, groups, bias,
+                         padding_mode, weight_norm_type, weight_norm_params,
+                         activation_norm_type, activation_norm_params,
+                         nonlinearity, inplace_nonlinearity, apply_noise, order, 2)

@@ -13,6 +13,7 @@ import torch
 from . import _C
 
 EPI_BIAS, EPI_RELU, EPI_LRELU, EPI_RESIDUAL, EPI_TANH, EPI_STATS, EPI_OUT_F32 = 1, 2, 4, 8, 16, 32, 64
+EPI_STATS_INSTANCE = 128
 ACT_NONE, ACT_LRELU, ACT_RELU = 0, 1, 2
 ACT_CODES = {'': 0, 'none': 0, None: 0, 'leakyrelu': 1, 'relu': 2}
 
@@ -299,7 +300,12 @@ def conv2d_fprop(x, wpk, cout, kh, kw, stride=1, pad=0, bias=None, residual=None
             raise RuntimeError('residual shape %s does not match the output %s' %
                                (tuple(residual.shape), (n, cout_p, ho, wo)))
     if stats is not None:
+        # stats: zero-filled fp32 (2, G, Cout); G == N selects per-sample statistics
         flags |= EPI_STATS
+        if stats.shape[1] != 1:
+            if stats.shape[1] != n:
+                raise RuntimeError('stats must be (2, 1, Cout) or (2, N, Cout)')
+            flags |= EPI_STATS_INSTANCE
     if out_f32:
         flags |= EPI_OUT_F32
     _C.lib().call('imx_conv2d_igemm_fprop_bf16', _ptr(x), _ptr(wpk), _ptr(bias), _ptr(residual), _ptr(out),

@@ -184,8 +184,10 @@ IMX_API int imx_spade_modulate_bwd_dx(const imx_bf16* x, const imx_bf16* dy,
 #define IMX_EPI_RESIDUAL  8   /* + residual[n,oy,ox,co] (NHWC bf16, same shape as out) */
 #define IMX_EPI_TANH      16
 #define IMX_EPI_STATS     32  /* accumulate per-channel sum / sumsq of the stored
-                                 (bf16-rounded) output into stats[0..Cout) / [Cout..2Cout)
-                                 (fp32 atomics; caller zero-fills) */
+                                 (bf16-rounded) output into stats, laid out (2, G, Cout)
+                                 like imx_bn_stats_nhwc_bf16 (fp32 atomics; caller
+                                 zero-fills); G = 1 unless IMX_EPI_STATS_INSTANCE */
+#define IMX_EPI_STATS_INSTANCE 128 /* with IMX_EPI_STATS: per-sample statistics, G = N */
 #define IMX_EPI_OUT_F32   64  /* out is fp32 NHWC instead of bf16 */
 
 /* out[n,oy,ox,co] = epilogue( sum_{kh,kw,ci} x[n, oy*stride+kh-pad, ox*stride+kw-pad, ci]

@@ -1,0 +1,111 @@
+"""CPU checks of the drop-in boundary: the C-ABI library loads and exports every symbol that
+include/imx.h declares, argument validation works without a GPU, the host-side modules keep
+the reference's names / keys, and CPU tensors are rejected (no fallback)."""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+from tests import helpers as H
+
+ROOT = H.ROOT
+
+
+def test_library_exports_every_declared_symbol():
+    from imaginaire_b200 import _C
+    decls = _C.parse_header()
+    header = open(os.path.join(ROOT, 'include', 'imx.h')).read()
+    declared = set(re.findall(r'IMX_API[^;(]*?\b(imx_\w+)\s*\(', header))
+    assert declared == set(decls) and len(declared) >= 20
+    dll = ctypes.CDLL(_C.LIB_PATH)
+    for name in declared:
+        assert hasattr(dll, name), name
+    assert _C.lib().raw('imx_version')() >= 100
+
+
+def test_argument_validation_needs_no_gpu():
+    from imaginaire_b200 import _C
+    lib = _C.lib()
+    # kernel_size != 1 is rejected before anything touches the device
+    rc = lib.raw('imx_resample2d_fwd_f32')(1, 1, 1, 1, 3, 8, 8, 8, 8, 3, None)
+    assert rc != 0 and 'kernel_size' in lib.last_error()
+    rc = lib.raw('imx_bn_stats_nhwc_bf16')(1, 1, 1, 1, 16, 12, 0, None)
+    assert rc != 0 and 'multiple of 8' in lib.last_error()
+    assert lib.raw('imx_conv2d_wgrad_workspace_bytes')(8, 128, 256, 128, 128, 512, 512, 5, 5, 1, 2) > 0
+    with pytest.raises(_C.ImxError):
+        lib.call('imx_conv2d_igemm_fprop_bf16', 1, 1, None, None, 1, None, 1, 8, 8, 12, 8, 8, 3, 3, 1, 1, 0, None)
+
+
+def test_cpu_tensors_are_rejected():
+    from imaginaire_b200 import ops
+    from imaginaire_b200.model_utils.fs_vid2vid import resample
+    with pytest.raises(RuntimeError, match='no CPU fallback'):
+        ops.resample2d_fwd(torch.zeros(1, 1, 4, 4), torch.zeros(1, 2, 4, 4))
+    with pytest.raises(RuntimeError, match='no CPU fallback'):
+        resample(torch.zeros(1, 1, 4, 4), torch.zeros(1, 2, 4, 4))
+    from imaginaire_b200.layers import Conv2dBlock
+    with pytest.raises(RuntimeError, match='no CPU fallback'):
+        Conv2dBlock(8, 8, 3, padding=1)(torch.zeros(1, 8, 4, 4))
+
+
+def test_generator_state_dict_keys_match_reference():
+    d = H.load_golden('generator_unit_test.npz')
+    _, net = H.build_generator('spade_unit_test.yaml')
+    sd = net.state_dict()
+    assert list(sd.keys()) == [str(k) for k in d['keys']]
+    assert len(sd) == 263
+    assert H.state_dict_digest(sd) == str(d['state_dict_sha256'])
+
+
+def test_block_api_surface():
+    import types
+    from imaginaire_b200.layers import Conv2dBlock, Res2dBlock, SpatiallyAdaptiveNorm
+    an = types.SimpleNamespace(num_filters=8, kernel_size=3, separate_projection=True, cond_dims=5,
+                               weight_norm_type='spectral', activation_norm_type='sync_batch',
+                               activation_norm_params=types.SimpleNamespace(affine=False))
+    blk = Res2dBlock(16, 8, activation_norm_type='spatially_adaptive', activation_norm_params=an,
+                     weight_norm_type='spectral', bias=[True, True, False], order='NACNAC')
+    assert blk.learn_shortcut and blk.conditional
+    assert list(blk.conv_block_0.layers.keys()) == ['norm', 'nonlinearity', 'conv']
+    assert list(blk.conv_block_s.layers.keys()) == ['norm', 'conv']
+    keys = set(blk.state_dict().keys())
+    for k in ('conv_block_0.layers.conv.weight_orig', 'conv_block_0.layers.conv.weight_u',
+              'conv_block_0.layers.conv.weight_v', 'conv_block_0.layers.conv.bias',
+              'conv_block_0.layers.norm.norm.running_mean', 'conv_block_0.layers.norm.norm.weight',
+              'conv_block_0.layers.norm.mlps.0.0.layers.conv.weight_orig',
+              'conv_block_0.layers.norm.gammas.0.layers.conv.bias',
+              'conv_block_0.layers.norm.betas.0.layers.conv.weight_v'):
+        assert k in keys, k
+    assert 'conv_block_s.layers.conv.bias' not in keys
+    norm = blk.conv_block_0.layers['norm']
+    assert isinstance(norm, SpatiallyAdaptiveNorm) and norm.conditional
+    # sync_batch always owns weight / bias; `affine` only decides whether they train
+    assert not norm.norm.weight.requires_grad
+    blk2 = Conv2dBlock(4, 4, 3, padding=1, nonlinearity='leakyrelu', order='CNA')
+    assert list(blk2.layers.keys()) == ['conv', 'nonlinearity'] and not blk2.conditional
+
+
+def test_config_loader():
+    from imaginaire_b200.config import Config
+    from imaginaire_b200.utils.data import (get_crop_h_w, get_paired_input_image_channel_number,
+                                            get_paired_input_label_channel_number)
+    cfg = Config(os.path.join(ROOT, 'configs', 'spade_c3_256x512.yaml'))
+    assert get_paired_input_label_channel_number(cfg.data) == 35
+    assert get_paired_input_image_channel_number(cfg.data) == 3
+    assert get_crop_h_w(cfg.data.train.augmentations) == (256, 512)
+    assert cfg.gen.activation_norm_params.separate_projection is True
+    assert cfg.gen_opt.lr == 1e-4 and cfg.trainer.model_average is True
+
+
+@pytest.mark.skipif(not os.path.isdir('/root/reference/configs'), reason='reference tree not mounted')
+def test_reference_yaml_files_load_unchanged():
+    from imaginaire_b200.config import Config
+    from imaginaire_b200.generators.spade import Generator
+    for rel in ('configs/unit_test/spade.yaml', 'configs/projects/spade/cocostuff/base128_bs4.yaml'):
+        cfg = Config(os.path.join('/root/reference', rel))
+        assert cfg.gen.type == 'imaginaire.generators.spade'
+    cfg = Config('/root/reference/configs/unit_test/spade.yaml')
+    net = Generator(cfg.gen, cfg.data)
+    assert sum(p.numel() for p in net.parameters()) == 109247811

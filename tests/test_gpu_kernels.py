@@ -1,0 +1,282 @@
+"""GPU parity of the C-ABI kernels against the CPU oracle (oracle/) and the golden vectors.
+Bit-exact where the arithmetic is reproducible (warp forwards, resizes, packs), stated
+tolerances elsewhere."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import spade_oracle as so
+from oracle import warp_oracle as wo
+from tests import helpers as H
+
+pytestmark = pytest.mark.gpu
+DEV = 'cuda:0'
+
+
+def nhwc(t):
+    return t.to(DEV).bfloat16().contiguous(memory_format=torch.channels_last)
+
+
+# ------------------------------------------------------------------ warps
+
+@pytest.mark.parametrize('tag', ['a', 'b'])
+def test_gridsample_warp_bit_exact_vs_reference_golden(tag):
+    from imaginaire_b200.model_utils.fs_vid2vid import resample
+    d = H.load_golden('warp_%s.npz' % tag)
+    out = resample(torch.from_numpy(d['img']).to(DEV), torch.from_numpy(d['flow']).to(DEV))
+    assert np.array_equal(out.cpu().numpy(), d['out'])
+
+
+def test_gridsample_warp_full_size_512x1024():
+    """BASELINE.json configs[3] shape: 512 x 1024 frames; 1e-5 relative bound (measured: bit-exact)."""
+    from imaginaire_b200 import ops
+    g = torch.Generator().manual_seed(7)
+    img = torch.randn(2, 3, 512, 1024, generator=g)
+    flow = H.synthetic_flow(8, 2, 512, 1024)
+    out = ops.gridsample_warp_fwd(img.to(DEV), flow.to(DEV)).cpu().numpy()
+    ref = wo.gridsample_warp_forward(img.numpy(), flow.numpy())
+    assert np.abs(out - ref).max() <= 1e-5 * np.abs(ref).max()
+    assert np.array_equal(out, ref)
+
+
+@pytest.mark.parametrize('shape', [(2, 3, 64, 128), (1, 5, 33, 47), (2, 3, 512, 1024), (1, 1, 1, 1), (3, 2, 1, 9)])
+def test_resample2d_forward_bit_exact_vs_oracle(shape):
+    from imaginaire_b200.third_party.resample2d import Resample2d
+    b, c, h, w = shape
+    g = torch.Generator().manual_seed(11)
+    img = torch.randn(b, c, h, w, generator=g)
+    flow = H.synthetic_flow(12, b, h, w) if h > 4 else torch.randn(b, 2, h, w, generator=g) * 3
+    out = Resample2d()(img.to(DEV), flow.to(DEV)).cpu().numpy()
+    ref = wo.resample2d_forward(img.numpy(), flow.numpy())
+    assert np.abs(out - ref).max() <= 1e-5 * max(np.abs(ref).max(), 1e-30)   # the stated tolerance
+    assert np.array_equal(out, ref)                                          # and in fact bit-exact
+
+
+def test_resample2d_empty_and_invalid():
+    from imaginaire_b200 import ops, _C
+    out = ops.resample2d_fwd(torch.zeros(0, 3, 8, 8, device=DEV), torch.zeros(0, 2, 8, 8, device=DEV))
+    assert out.shape == (0, 3, 8, 8)
+    with pytest.raises(_C.ImxError, match='kernel_size'):
+        ops.resample2d_fwd(torch.zeros(1, 3, 8, 8, device=DEV), torch.zeros(1, 2, 8, 8, device=DEV), kernel_size=3)
+    with pytest.raises(RuntimeError):
+        ops.resample2d_fwd(torch.zeros(1, 3, 8, 8, device=DEV).half(), torch.zeros(1, 2, 8, 8, device=DEV))
+
+
+@pytest.mark.parametrize('trunc', [True, False])
+def test_resample2d_backward_vs_oracle(trunc):
+    from imaginaire_b200 import ops
+    g = torch.Generator().manual_seed(13)
+    img = torch.randn(2, 4, 40, 56, generator=g)
+    flow = H.synthetic_flow(14, 2, 40, 56, scale=4.0)
+    gout = torch.randn(2, 4, 40, 56, generator=g)
+    gi, gf = ops.resample2d_bwd(img.to(DEV), flow.to(DEV), gout.to(DEV), trunc_alpha=trunc)
+    ri, rf = wo.resample2d_backward(img.numpy(), flow.numpy(), gout.numpy(), trunc_alpha=trunc)
+    assert np.array_equal(gf.cpu().numpy(), rf)                 # per-pixel, same op order: bit-exact
+    assert H.rel_err(gi.cpu(), ri) < 1e-5                        # atomics: summation order differs
+
+
+def test_resample2d_autograd_function():
+    from imaginaire_b200.third_party.resample2d import Resample2dFunction
+    g = torch.Generator().manual_seed(15)
+    img = torch.randn(1, 3, 16, 20, generator=g).to(DEV).requires_grad_(True)
+    flow = (torch.rand(1, 2, 16, 20, generator=g) * 2).to(DEV).requires_grad_(True)
+    out = Resample2dFunction.apply(img, flow, 1)
+    gout = torch.randn(1, 3, 16, 20, generator=g)
+    out.backward(gout.to(DEV))
+    ri, rf = wo.resample2d_backward(img.detach().cpu().numpy(), flow.detach().cpu().numpy(), gout.numpy(), True)
+    assert H.rel_err(img.grad.cpu(), ri) < 1e-5 and np.array_equal(flow.grad.cpu().numpy(), rf)
+
+
+def test_gridsample_warp_backward_vs_torch_autograd():
+    from imaginaire_b200.model_utils.fs_vid2vid import resample
+    g = torch.Generator().manual_seed(16)
+    img = torch.randn(2, 3, 48, 64, generator=g)
+    flow = H.synthetic_flow(17, 2, 48, 64, scale=5.0)
+    gout = torch.randn(2, 3, 48, 64, generator=g)
+    a = img.to(DEV).requires_grad_(True); f = flow.to(DEV).requires_grad_(True)
+    resample(a, f).backward(gout.to(DEV))
+    # the reference's resample() written out with torch CPU ops (fs_vid2vid.py:14-39)
+    ic = img.clone().requires_grad_(True); fc = flow.clone().requires_grad_(True)
+    h, w = 48, 64
+    gx = torch.linspace(-1, 1, w).view(1, 1, 1, w).expand(2, 1, h, w)
+    gy = torch.linspace(-1, 1, h).view(1, 1, h, 1).expand(2, 1, h, w)
+    fl = torch.cat([fc[:, 0:1] / ((w - 1.0) / 2.0), fc[:, 1:2] / ((h - 1.0) / 2.0)], 1)
+    F.grid_sample(ic, (torch.cat([gx, gy], 1) + fl).permute(0, 2, 3, 1), mode='bilinear', padding_mode='border',
+                  align_corners=True).backward(gout)
+    assert H.rel_err(a.grad.cpu(), ic.grad) < 1e-5
+    assert H.rel_err(f.grad.cpu(), fc.grad) < 1e-4
+
+
+# ------------------------------------------------------- layout / resize
+
+@pytest.mark.parametrize('size', [(64, 96), (16, 24), (5, 7), (1, 1)])
+def test_nearest_resize_exact_vs_oracle(size):
+    from imaginaire_b200 import ops
+    label = H.onehot_label(21, 2, 35, 64, 96, extra_uniform=1)
+    out = ops.nearest_resize_to_nhwc(label.to(DEV), *size)
+    ref = so.nearest_resize(label, size).bfloat16().float()
+    assert out.shape[1] == 64
+    assert torch.equal(out[:, :36].float().cpu(), ref)
+    assert float(out[:, 36:].float().abs().max()) == 0.0
+
+
+def test_upsample2x_exact_and_backward():
+    from imaginaire_b200 import functional as NF
+    x = nhwc(torch.randn(2, 64, 6, 10)).requires_grad_(True)
+    y = NF.upsample2x(x)
+    assert torch.equal(y.float().cpu(), so.upsample2x(x.detach().float().cpu()))
+    g = nhwc(torch.randn(2, 64, 12, 20))
+    y.backward(g)
+    ref = F.avg_pool2d(g.float(), 2) * 4
+    assert H.rel_err(x.grad.float(), ref) < 8e-3   # bf16 rounding of the 4-sum
+
+
+# ------------------------------------------------------------ convolution
+
+CONV_CASES = [
+    # N, Cin, Cout, H, W, k, stride, pad
+    (1, 64, 32, 8, 16, 1, 1, 0),
+    (2, 64, 64, 20, 24, 3, 1, 1),          # ragged tiles
+    (1, 40, 72, 13, 11, 5, 1, 2),          # channel counts that are not multiples of 64
+    (2, 192, 64, 16, 16, 5, 1, 2),         # label -> hidden
+    (2, 256, 512, 16, 32, 3, 1, 1),
+    (1, 256, 3, 64, 64, 5, 1, 2),          # to-RGB
+    (4, 512, 1024, 32, 64, 3, 1, 1),       # > 148 tiles: persistent loop, both TMEM stages
+    (2, 64, 64, 32, 32, 3, 2, 1),          # stride 2 (style encoder)
+    (2, 64, 128, 33, 47, 4, 2, 1),         # discriminator-style k4 s2, odd size
+    (1, 8, 16, 7, 5, 3, 1, 1),             # smallest
+]
+
+
+@pytest.mark.parametrize('case', CONV_CASES)
+def test_conv2d_fprop_vs_oracle(case):
+    """fp32 CPU convolution of the bf16-rounded operands is the oracle; the kernel accumulates
+    in fp32 and rounds the output to bf16 once: |err| <= 2^-8 relative to the output scale."""
+    from imaginaire_b200 import ops
+    n, cin, cout, h, w, k, s, p = case
+    g = torch.Generator().manual_seed(31)
+    x = torch.randn(n, cin, h, w, generator=g).bfloat16().float()
+    wt = (torch.randn(cout, cin, k, k, generator=g) / (cin * k * k) ** 0.5).bfloat16().float()
+    b = torch.randn(cout, generator=g)
+    cin_p = ops.round_up(cin, 8)
+    xp = torch.zeros(n, cin_p, h, w); xp[:, :cin] = x
+    y = ops.conv2d_fprop(nhwc(xp), ops.pack_conv_weight(wt.to(DEV), cin_p=cin_p), cout, k, k, s, p, bias=b.to(DEV))
+    ref = F.conv2d(x, wt, b, stride=s, padding=p)
+    assert y.shape[1] == ops.round_up(cout, 8)
+    assert H.rel_err(y[:, :cout].float().cpu(), ref) < 4e-3
+    assert float(y[:, cout:].float().abs().max() if y.shape[1] > cout else 0.0) == 0.0
+
+
+def test_conv2d_epilogues_vs_oracle():
+    from imaginaire_b200 import ops
+    g = torch.Generator().manual_seed(32)
+    n, cin, cout, h, w = 2, 128, 128, 16, 32
+    x = torch.randn(n, cin, h, w, generator=g).bfloat16().float()
+    wt = (torch.randn(cout, cin, 3, 3, generator=g) / (cin * 9) ** 0.5).bfloat16().float()
+    b = torch.randn(cout, generator=g)
+    res = torch.randn(n, cout, h, w, generator=g).bfloat16().float()
+    wpk = ops.pack_conv_weight(wt.to(DEV))
+    base = F.conv2d(x, wt, b, padding=1)
+    y = ops.conv2d_fprop(nhwc(x), wpk, cout, 3, 3, 1, 1, bias=b.to(DEV), flags=ops.EPI_LRELU)
+    assert H.rel_err(y.float().cpu(), so.leaky_relu(base)) < 4e-3
+    y = ops.conv2d_fprop(nhwc(x), wpk, cout, 3, 3, 1, 1, bias=b.to(DEV), flags=ops.EPI_RELU)
+    assert H.rel_err(y.float().cpu(), F.relu(base)) < 4e-3
+    y = ops.conv2d_fprop(nhwc(x), wpk, cout, 3, 3, 1, 1, bias=b.to(DEV), residual=nhwc(res))
+    assert H.rel_err(y.float().cpu(), base + res) < 4e-3
+    y = ops.conv2d_fprop(nhwc(x), wpk, cout, 3, 3, 1, 1, bias=b.to(DEV), flags=ops.EPI_TANH)
+    assert H.rel_err(y.float().cpu(), torch.tanh(base)) < 4e-3
+    y = ops.conv2d_fprop(nhwc(x), wpk, cout, 3, 3, 1, 1, bias=b.to(DEV), out_f32=True)
+    assert H.rel_err(y.float().cpu(), base) < 1e-5
+    for inst in (False, True):
+        st = torch.zeros(2, n if inst else 1, cout, device=DEV)
+        y = ops.conv2d_fprop(nhwc(x), wpk, cout, 3, 3, 1, 1, bias=b.to(DEV), stats=st)
+        yq = y.float().cpu()
+        dims = (2, 3) if inst else (0, 2, 3)
+        assert H.rel_err(st[0].cpu().flatten(), yq.sum(dims).flatten()) < 1e-4
+        assert H.rel_err(st[1].cpu().flatten(), (yq * yq).sum(dims).flatten()) < 1e-4
+
+
+@pytest.mark.parametrize('case', [(1, 64, 128, 8, 8, 1, 1, 0), (2, 64, 64, 16, 32, 3, 1, 1), (1, 40, 72, 13, 11, 5, 1, 2),
+                                  (2, 64, 512, 32, 64, 5, 1, 2), (2, 64, 128, 32, 32, 4, 2, 1),
+                                  (4, 256, 256, 32, 64, 3, 1, 1)])
+def test_conv2d_wgrad_vs_oracle(case):
+    from imaginaire_b200 import ops
+    n, cin, cout, h, w, k, s, p = case
+    g = torch.Generator().manual_seed(33)
+    ho, wo_ = (h + 2 * p - k) // s + 1, (w + 2 * p - k) // s + 1
+    x = torch.randn(n, cin, h, w, generator=g).bfloat16().float()
+    dy = torch.randn(n, cout, ho, wo_, generator=g).bfloat16().float()
+    cin_p, cout_p = ops.round_up(cin, 8), ops.round_up(cout, 8)
+    xp = torch.zeros(n, cin_p, h, w); xp[:, :cin] = x
+    dp = torch.zeros(n, cout_p, ho, wo_); dp[:, :cout] = dy
+    dw = ops.conv2d_wgrad(nhwc(xp), nhwc(dp), cin, cout, k, k, s, p)
+    ref = torch.nn.grad.conv2d_weight(x, (cout, cin, k, k), dy, stride=s, padding=p)
+    assert H.rel_err(dw.cpu(), ref) < 1e-4      # exact bf16 products, fp32 accumulation both sides
+
+
+@pytest.mark.parametrize('case', [(2, 64, 64, 16, 32, 3, 1, 1), (1, 40, 72, 13, 11, 5, 1, 2), (2, 64, 128, 32, 32, 3, 2, 1),
+                                  (2, 32, 64, 33, 47, 4, 2, 1)])
+def test_conv2d_dgrad_vs_oracle(case):
+    from imaginaire_b200 import ops, functional as NF
+    n, cin, cout, h, w, k, s, p = case
+    g = torch.Generator().manual_seed(34)
+    ho, wo_ = (h + 2 * p - k) // s + 1, (w + 2 * p - k) // s + 1
+    wt = (torch.randn(cout, cin, k, k, generator=g) / (cout * k * k) ** 0.5).bfloat16().float()
+    dy = torch.randn(n, cout, ho, wo_, generator=g).bfloat16().float()
+    cin_p, cout_p = ops.round_up(cin, 8), ops.round_up(cout, 8)
+    dp = torch.zeros(n, cout_p, ho, wo_); dp[:, :cout] = dy
+    dx = NF.conv2d_dgrad(nhwc(dp), wt.to(DEV), s, p, h, w, cin_p)
+    ref = torch.nn.grad.conv2d_input((n, cin, h, w), wt, dy, stride=s, padding=p)
+    assert dx.shape == (n, cin_p, h, w)
+    assert H.rel_err(dx[:, :cin].float().cpu(), ref) < 4e-3
+
+
+# ------------------------------------------------- statistics / modulation
+
+@pytest.mark.parametrize('shape', [(2, 64, 16, 32), (3, 512, 8, 8), (2, 2048, 4, 8), (1, 40, 5, 7), (2, 4096, 2, 2)])
+@pytest.mark.parametrize('inst', [False, True])
+def test_bn_stats_and_finalize_vs_oracle(shape, inst):
+    from imaginaire_b200 import ops
+    n, c, h, w = shape
+    g = torch.Generator().manual_seed(41)
+    x = (torch.randn(n, c, h, w, generator=g) * 1.7 + 0.3).bfloat16().float()
+    sums = ops.bn_stats(nhwc(x), inst)
+    dims = (2, 3) if inst else (0, 2, 3)
+    assert H.rel_err(sums[0].cpu().flatten(), x.sum(dims).flatten()) < 1e-5
+    assert H.rel_err(sums[1].cpu().flatten(), (x * x).sum(dims).flatten()) < 1e-5
+    rm, rv = torch.zeros(c, device=DEV), torch.ones(c, device=DEV)
+    cnt = h * w if inst else n * h * w
+    mean, rstd = ops.bn_finalize(sums, cnt, 1e-5, None if inst else rm, None if inst else rv, 0.1)
+    assert H.rel_err(mean.cpu(), x.mean(dims).flatten()) < 1e-5
+    assert H.rel_err(rstd.cpu(), (x.var(dims, unbiased=False) + 1e-5).rsqrt().flatten()) < 1e-4
+    if not inst and cnt > 1:
+        # oracle: running = 0.9 * running + 0.1 * {mean, unbiased var}  (spade_oracle.inner_norm)
+        assert H.rel_err(rv.cpu(), 0.9 + 0.1 * x.var(dims, unbiased=True)) < 1e-4
+        assert H.rel_err(rm.cpu(), 0.1 * x.mean(dims)) < 1e-4
+
+
+def test_spade_gb_fused_equals_materialised():
+    """The projection-conv-applies-the-modulation path and the materialised gamma/beta path
+    are the same function (bf16 rounding of gamma/beta aside)."""
+    from imaginaire_b200 import ops
+    g = torch.Generator().manual_seed(42)
+    n, ch, c, h, w, k = 2, 128, 512, 16, 32, 5
+    hid = F.relu(torch.randn(n, ch, h, w, generator=g)).bfloat16().float()
+    wg = (torch.randn(c, ch, k, k, generator=g) / (ch * k * k) ** 0.5)
+    wb = (torch.randn(c, ch, k, k, generator=g) / (ch * k * k) ** 0.5)
+    bg, bb = torch.randn(c, generator=g) * 0.1, torch.randn(c, generator=g) * 0.1
+    x = (torch.randn(n, c, h, w, generator=g) * 1.5 + 0.2).bfloat16().float()
+    nw, nb = torch.rand(c, generator=g) + 0.5, torch.randn(c, generator=g) * 0.3
+    xn = nhwc(x)
+    sums = ops.bn_stats(xn, False)
+    mean, rstd = ops.bn_finalize(sums, n * h * w, 1e-5)
+    y = ops.spade_gb_conv_modulate(nhwc(hid), ops.pack_spade_gb_weight(wg.to(DEV), wb.to(DEV)), bg.to(DEV), bb.to(DEV),
+                                   xn, mean, rstd, nw.to(DEV), nb.to(DEV), c, k, k, k // 2, False, ops.ACT_LRELU)
+    # oracle: the same formula on CPU in fp32
+    gamma = F.conv2d(hid, wg.bfloat16().float(), bg, padding=k // 2)
+    beta = F.conv2d(hid, wb.bfloat16().float(), bb, padding=k // 2)
+    m = x.mean((0, 2, 3), keepdim=True); v = x.var((0, 2, 3), unbiased=False, keepdim=True)
+    xh = (x - m) / torch.sqrt(v + 1e-5) * nw.view(1, -1, 1, 1) + nb.view(1, -1, 1, 1)
+    ref = so.leaky_relu(xh * (1 + gamma) + beta)
+    assert H.rel_err(y.float().cpu(), ref) < 6e-3
