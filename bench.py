@@ -1,0 +1,371 @@
+"""Benchmark of the SPADE hot path on B200 (driver contract: see the task description).
+
+    python bench.py --gpus 1 --steps K --warmup W            # our arm
+    python bench.py --impl reference --steps K --warmup W    # reference arm: CPU path on host cores
+    torchrun ... bench.py --gpus N ...                       # one rank per GPU, NCCL
+
+Workload (BASELINE.json configs[2], SURVEY.md section 8(d) "config 3"): one SPADE G+D
+training iteration of the base128 generator (configs/spade_c3_256x512.yaml) at 256x512,
+35-class synthetic one-hot labels, batch 8 per GPU, bf16 storage / fp32 accumulate:
+discriminator update (no-grad generator pass + D forward/backward + Adam) then generator
+update (G forward, D forward, GAN + feature-matching + KL + VGG perceptual losses, backward,
+Adam, EMA).  Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = 'spade_gd_train_images_per_sec_256x512'
+UNIT = 'img/s'
+CONFIG_NAME = 'spade_c3_256x512.yaml'
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--config', default=CONFIG_NAME)
+    ap.add_argument('--batch', type=int, default=None, help='per-GPU batch override (debugging only)')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    return ap.parse_args()
+
+
+def load_peaks():
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return dict(hbm=p['hbm_gbs'], tf_burst=p['bf16_tflops'], tf_sustained=p['bf16_tflops_sustained'],
+                    source='MEASURED_PEAKS.json')
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, source='fallback (B200_PROFILING.md)')
+
+
+# --------------------------------------------------------------------- synthetic data
+
+def synthetic_batch(cfg, batch, seed, pinned=False):
+    """Labels: one-hot of a blocky randint class map (what real label maps look like,
+    SURVEY 8(d)); images: U(-1, 1).  Host tensors, fp32, like the reference's data loader."""
+    import torch
+    from imaginaire_b200.utils.data import get_crop_h_w, get_paired_input_label_channel_number
+    h, w = get_crop_h_w(cfg.data.train.augmentations)
+    classes = get_paired_input_label_channel_number(cfg.data)
+    g = torch.Generator().manual_seed(seed)
+    idx = torch.randint(0, classes, (batch, 1, h // 8, w // 8), generator=g)
+    idx = idx.repeat_interleave(8, 2).repeat_interleave(8, 3)
+    label = torch.zeros(batch, classes, h, w).scatter_(1, idx, 1.0)
+    images = torch.rand(batch, 3, h, w, generator=g) * 2 - 1
+    if pinned:
+        label, images = label.pin_memory(), images.pin_memory()
+    return {'label': label, 'images': images}
+
+
+# ------------------------------------------------------------------------- clocks
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+    FIELDS = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+              'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.index, self.samples, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.FIELDS, '--format=csv,noheader,nounits',
+                 '-lms', '200'], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            parts = [p.strip() for p in line.split(',')]
+            if len(parts) >= 6:
+                self.samples.append(parts)
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+        sm = sorted(int(s[0]) for s in self.samples if s[0].isdigit())
+        mx = [int(s[1]) for s in self.samples if s[1].isdigit()]
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        reasons = sorted({names[i] for s in self.samples for i in range(4) if s[2 + i].lower().startswith('active')})
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': max(mx) if mx else None,
+                'reasons': reasons, 'samples': len(self.samples)}
+
+
+# ------------------------------------------------------------- conv roofline probe
+
+class ConvProbe:
+    """Times every implicit-GEMM convolution launch of one training iteration with CUDA events
+    on the launching stream and adds up its algorithmic FLOPs (2*N*Ho*Wo*Cout*Cin*kh*kw)."""
+
+    def __init__(self):
+        self.records = []
+
+    def install(self):
+        import torch
+        from imaginaire_b200 import ops
+        self._orig = (ops.conv2d_fprop, ops.conv2d_wgrad, ops.spade_gb_conv_modulate)
+        probe = self
+
+        def timed(fn, flops_fn, tag):
+            def wrapper(*a, **k):
+                s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                s.record()
+                out = fn(*a, **k)
+                e.record()
+                probe.records.append((tag, flops_fn(out, *a, **k), s, e))
+                return out
+            return wrapper
+
+        def fprop_flops(out, x, wpk, cout, kh, kw, *a, **k):
+            n, _, ho, wo = out.shape
+            return 2.0 * n * ho * wo * cout * x.shape[1] * kh * kw
+
+        def wgrad_flops(out, x, dy, cin, cout, kh, kw, *a, **k):
+            n, _, ho, wo = dy.shape
+            return 2.0 * n * ho * wo * cout * cin * kh * kw
+
+        def gb_flops(out, hidden, wgb, bg, bb, x, mean, rstd, w, b, c, kh, kw, *a, **k):
+            n, chp, h, wd = hidden.shape
+            return 2.0 * n * h * wd * (2 * c) * chp * kh * kw
+
+        ops.conv2d_fprop = timed(self._orig[0], fprop_flops, 'fprop')
+        ops.conv2d_wgrad = timed(self._orig[1], wgrad_flops, 'wgrad')
+        ops.spade_gb_conv_modulate = timed(self._orig[2], gb_flops, 'spade_gb')
+
+    def remove(self):
+        from imaginaire_b200 import ops
+        ops.conv2d_fprop, ops.conv2d_wgrad, ops.spade_gb_conv_modulate = self._orig
+
+    def summary(self):
+        by = {}
+        for tag, fl, s, e in self.records:
+            ms = s.elapsed_time(e)
+            a = by.setdefault(tag, [0.0, 0.0, 0])
+            a[0] += fl; a[1] += ms; a[2] += 1
+        tot_fl = sum(v[0] for v in by.values())
+        tot_ms = sum(v[1] for v in by.values())
+        return by, tot_fl, tot_ms
+
+
+# ---------------------------------------------------------------------- CPU baseline
+
+def cpu_reference_step(cfg, batch=1, seed=0):
+    """One bounded sample of the reference's CPU path: the SPADE generator forward (training
+    mode, fp32, all host cores) through the CPU oracle port of the reference's PyTorch code.
+    Returns (seconds, images)."""
+    import torch
+    from oracle import spade_oracle as so
+    from imaginaire_b200.generators.spade import Generator
+    from imaginaire_b200.utils.data import get_crop_h_w
+    from imaginaire_b200.utils.init_weight import weights_init
+    state = cpu_reference_step.__dict__
+    if 'sd' not in state:
+        torch.manual_seed(seed)
+        net = Generator(cfg.gen, cfg.data)
+        net.apply(weights_init('xavier', 0.02))
+        state['sd'] = net.state_dict()
+        state['spec'] = so.generator_spec_from_cfg(cfg.gen, get_crop_h_w(cfg.data.train.augmentations))
+    data = synthetic_batch(cfg, batch, seed)
+    eps = torch.randn(batch, cfg.gen.style_dims)
+    t0 = time.perf_counter()
+    with torch.no_grad():
+        so.generator(state['sd'], data, state['spec'], True, eps)
+    return time.perf_counter() - t0, batch
+
+
+# Algorithmic FLOPs per image (SURVEY.md section 3.1 / BASELINE.md section 3): one training
+# iteration = 4 F_G + 4.5 F_D + 3 F_VGG; the generator forward alone is F_G.
+F_G, F_D, F_VGG = 2883.0, 172.0, 102.0
+STEP_FLOP_SHARE_OF_G_FWD = F_G / (4 * F_G + 4.5 * F_D + 3 * F_VGG)
+
+
+def run_reference(args):
+    """Reference arm: the reference's own (CPU, PyTorch) implementation of the path, as ported in
+    oracle/, timed on this box's host cores.  /root/reference is Python and does not travel;
+    the oracle is pinned to it by tests/golden.  Each step is a bounded sample: one generator
+    forward at batch 1 of the same config; img/s for the training step is the sample's
+    throughput times the generator forward's share of the step's algorithmic FLOPs."""
+    import torch
+    from imaginaire_b200.config import Config
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    cfg = Config(os.path.join(ROOT, 'configs', args.config))
+    steps, warmup = args.steps, max(args.warmup, 1)
+    if steps + warmup > 8:   # keep the whole run within a few minutes
+        warmup = 1
+        steps = min(steps, 6)
+    for _ in range(warmup):
+        cpu_reference_step(cfg)
+    t = 0.0
+    for _ in range(steps):
+        dt, _ = cpu_reference_step(cfg)
+        t += dt
+    fwd_img_s = steps / t
+    value = fwd_img_s * STEP_FLOP_SHARE_OF_G_FWD
+    sample = ('generator forward (train mode, fp32), batch 1, 256x512, CPU oracle port of the reference; '
+              'train img/s = forward img/s (%.4f) x F_G/(4F_G+4.5F_D+3F_VGG) (%.4f)' % (fwd_img_s, STEP_FLOP_SHARE_OF_G_FWD))
+    line = {
+        'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': steps,
+        'warmup': warmup, 'ms_per_step': 1000.0 * t / steps, 'higher_is_better': True, 'scaling': 'weak',
+        'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': {'workload': 'SPADE G+D training step, base128 generator, 256x512, 35 labels (CPU sample: generator forward)',
+                   'config_file': 'configs/' + args.config},
+        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
+        'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------- our arm
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from imaginaire_b200 import _C
+    from imaginaire_b200.config import Config
+    from imaginaire_b200.trainers.spade import Trainer
+    from imaginaire_b200.utils.trainer import get_model_optimizer_and_scheduler
+
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    if not torch.cuda.is_available():
+        raise RuntimeError('bench.py needs a CUDA device: the product path has no CPU fallback')
+    torch.cuda.set_device(local_rank)
+    dev = torch.device('cuda', local_rank)
+    if world > 1:
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        dist.init_process_group('nccl', init_method='env://')
+    _C.lib()   # fails loudly if the CUDA library is missing
+
+    cfg = Config(os.path.join(ROOT, 'configs', args.config))
+    batch = args.batch or cfg.data.train.batch_size
+    net_G, net_D, opt_G, opt_D = get_model_optimizer_and_scheduler(cfg, seed=0, device=dev)
+    trainer = Trainer(cfg, net_G, net_D, opt_G, opt_D)
+    net_G.train(); net_D.train()
+
+    host = synthetic_batch(cfg, batch, seed=100 + rank, pinned=True)
+    resident = {k: v.to(dev) for k, v in host.items()}
+    h2d_bytes = sum(v.numel() * v.element_size() for v in host.values())
+
+    def one_step(data):
+        return trainer.step(dict(data))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        one_step(resident)
+
+    lib = _C.lib()
+    sampler = ClockSampler(local_rank)
+    # ---- timed region 1: inputs resident in HBM ----
+    barrier()
+    sampler.start()
+    lib.launches = 0
+    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    start.record()
+    for _ in range(args.steps):
+        one_step(resident)
+    end.record()
+    barrier()
+    launches = lib.launches
+    ms = start.elapsed_time(end)
+    # ---- timed region 2: end to end (pinned host -> device copies + loss read-back each step) ----
+    barrier()
+    start.record()
+    d2h = 0
+    for _ in range(args.steps):
+        data = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+        g_loss, d_loss = one_step(data)
+        losses = torch.stack([g_loss.reshape(()), d_loss.reshape(())]).cpu()   # device -> host read of the step's result
+        d2h = losses.numel() * losses.element_size()
+    end.record()
+    barrier()
+    ms_e2e = start.elapsed_time(end)
+    clocks = sampler.stop()
+    if world > 1:
+        t = torch.tensor([ms, ms_e2e], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, ms_e2e = float(t[0]), float(t[1])
+
+    # ---- roofline of the dominant kernel family: one more iteration with per-launch CUDA events ----
+    probe = ConvProbe()
+    probe.install()
+    one_step(resident)
+    torch.cuda.synchronize()
+    probe.remove()
+    by, conv_flops, conv_ms = probe.summary()
+    peaks = load_peaks()
+    achieved = conv_flops / (conv_ms * 1e-3) / 1e12 if conv_ms > 0 else 0.0
+    ms_per_step = ms / args.steps
+    roofline = {
+        'bound': 'tensor', 'kernel': 'conv_igemm_kernel / conv_wgrad_kernel (tcgen05 implicit GEMM), all launches of one iteration',
+        'achieved': achieved, 'peak': peaks['tf_sustained'], 'unit': 'TFLOP/s', 'frac': achieved / peaks['tf_sustained'],
+        'traffic': None, 'peak_source': peaks['source'] + ' bf16_tflops_sustained (kernel timed inside a long step)',
+        'conv_share_of_step': conv_ms / ms_per_step if ms_per_step > 0 else None,
+        'by_kind': {k: {'tflops': v[0] / (v[1] * 1e-3) / 1e12 if v[1] > 0 else 0.0, 'ms': v[1], 'launches': v[2]}
+                    for k, v in by.items()},
+    }
+
+    value = world * batch * args.steps / (ms * 1e-3)
+    e2e_value = world * batch * args.steps / (ms_e2e * 1e-3)
+    line = {
+        'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
+        'ms_per_step': ms_per_step, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+        'dtype': 'bf16', 'data': 'synthetic',
+        'config': {'workload': 'SPADE G+D training step (BASELINE configs[2]): base128 generator + SPADE discriminator, '
+                               '256x512, 35-class one-hot labels, batch %d/GPU, SyncBN, Adam, EMA' % batch,
+                   'config_file': 'configs/' + args.config, 'global_batch': world * batch,
+                   'parallelism': 'dp%d' % world, 'l2': 'working set (GBs of activations per step) is far larger than the 126 MB L2; no explicit flush'},
+        'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d_bytes, 'd2h_bytes_per_step': d2h,
+                'ms_per_step': ms_e2e / args.steps},
+        'gpu_launches': launches,
+        'roofline': roofline,
+        'clocks': clocks,
+        'step_tflops': world * batch * (4 * F_G + 4.5 * F_D + 3 * F_VGG) / 1e3 / (ms_per_step * 1e-3) / max(world, 1),
+    }
+    if rank == 0:
+        if world == 1 and not args.no_cpu_baseline:
+            cores = os.cpu_count() or 1
+            torch.set_num_threads(cores)
+            cpu_reference_step(cfg)            # warm-up (weight build, thread pool)
+            dt, n = cpu_reference_step(cfg)
+            fwd = n / dt
+            line['cpu_baseline'] = {
+                'value': fwd * STEP_FLOP_SHARE_OF_G_FWD, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+                'sample': 'one generator forward (train mode, fp32), batch 1, 256x512 through the CPU oracle port '
+                          '(%.2f s); train img/s = forward img/s x F_G/(4F_G+4.5F_D+3F_VGG) = %.4f x %.4f'
+                          % (dt, fwd, STEP_FLOP_SHARE_OF_G_FWD)}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    a = parse_args()
+    if a.impl == 'reference':
+        run_reference(a)
+    else:
+        run_ours(a)

@@ -55,6 +55,7 @@ class _Lib:
                 'libimx_kernels.so is not built (%s). Run `python -m imaginaire_b200.build` '
                 '(or __graft_entry__.build()); there is no fallback path.' % LIB_PATH)
         self._dll = ctypes.CDLL(LIB_PATH)
+        self.launches = 0   # kernel launches issued through call(); bench.py reads it
         self.decls = parse_header()
         for name, (ret, argtypes, _) in self.decls.items():
             fn = getattr(self._dll, name)   # AttributeError if the symbol is missing
@@ -67,11 +68,15 @@ class _Lib:
     def last_error(self):
         return self._dll.imx_last_error().decode('utf-8', 'replace')
 
+    # kernels launched per successful call (everything else launches exactly one)
+    _LAUNCHES = {'imx_conv2d_igemm_wgrad_bf16': 2}
+
     def call(self, name, *args):
         """Calls an int-returning entry point and raises ImxError on a nonzero code."""
         rc = getattr(self._dll, name)(*args)
         if rc != 0:
             raise ImxError('%s failed with code %d: %s' % (name, rc, self.last_error()))
+        self.launches += self._LAUNCHES.get(name, 1)
 
 
 _lib = None

@@ -132,7 +132,7 @@ class _Conv2d(torch.autograd.Function):
         if ctx.needs_input_grad[1]:
             dw = ops.conv2d_wgrad(x, dy, cin, cout, kh, kw, ctx.stride, ctx.pad)
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = ops.channel_sum(dy, cout)
+            db = ops.channel_sum(dy)[:cout]   # over the padded channels, then the logical ones
         if ctx.has_res and ctx.needs_input_grad[3]:
             dres = dy
         return dx, dw, db, dres, None, None, None, None

@@ -1,0 +1,101 @@
+"""VGG-19 perceptual loss.  ref: imaginaire/losses/perceptual.py:15-191
+
+The feature extractor is VGG-19 up to relu_5_1 built from the native Conv2dBlock (3x3
+tcgen05 convolutions with the ReLU in the epilogue; 2x2 max-pools are torch calls).  The
+reference loads ImageNet weights from the network; there is no network here, so the
+weights are randomly initialised (throughput is unaffected).
+"""
+import torch
+import torch.nn.functional as F
+from torch import nn
+
+from ..layers import Conv2dBlock
+
+_VGG19 = [('relu_1_1', 3, 64), ('relu_1_2', 64, 64), 'pool',
+          ('relu_2_1', 64, 128), ('relu_2_2', 128, 128), 'pool',
+          ('relu_3_1', 128, 256), ('relu_3_2', 256, 256), ('relu_3_3', 256, 256), ('relu_3_4', 256, 256), 'pool',
+          ('relu_4_1', 256, 512), ('relu_4_2', 512, 512), ('relu_4_3', 512, 512), ('relu_4_4', 512, 512), 'pool',
+          ('relu_5_1', 512, 512)]
+
+
+class _VGG19Features(nn.Module):
+    def __init__(self, layers):
+        super().__init__()
+        self.wanted = list(layers)
+        self.names = []
+        self.blocks = nn.ModuleList()
+        for item in _VGG19:
+            if item == 'pool':
+                self.names.append('pool')
+                self.blocks.append(nn.Identity())
+            else:
+                name, cin, cout = item
+                self.names.append(name)
+                self.blocks.append(Conv2dBlock(cin, cout, 3, padding=1, nonlinearity='relu'))
+        last = max(self.names.index(n) for n in self.wanted)
+        self.names, self.blocks = self.names[:last + 1], self.blocks[:last + 1]
+        for p in self.parameters():
+            p.requires_grad = False
+
+    def forward(self, x):
+        out = {}
+        for name, block in zip(self.names, self.blocks):
+            if name == 'pool':
+                x = F.max_pool2d(x, kernel_size=2, stride=2)
+            else:
+                x = block.forward_native(x)
+                if name in self.wanted:
+                    out[name] = x
+        return out
+
+
+def apply_imagenet_normalization(x):
+    """[-1, 1] images -> ImageNet-normalised.  ref: imaginaire/utils/misc.py:221-240"""
+    x = (x[:, :3] + 1) / 2
+    mean = x.new_tensor([0.485, 0.456, 0.406]).view(1, 3, 1, 1)
+    std = x.new_tensor([0.229, 0.224, 0.225]).view(1, 3, 1, 1)
+    return (x - mean) / std
+
+
+class PerceptualLoss(nn.Module):
+    def __init__(self, cfg=None, network='vgg19', layers='relu_4_1', weights=None, criterion='l1',
+                 resize=False, resize_mode='bilinear', instance_normalized=False, num_scales=1):
+        super().__init__()
+        if isinstance(layers, str):
+            layers = [layers]
+        if weights is None:
+            weights = [1.0] * len(layers)
+        elif isinstance(weights, (float, int)):
+            weights = [weights]
+        assert len(layers) == len(weights)
+        if network != 'vgg19':
+            raise NotImplementedError('only the vgg19 perceptual network is provided')
+        self.model = _VGG19Features(layers)
+        self.layers, self.weights = list(layers), list(weights)
+        self.criterion = nn.L1Loss() if criterion == 'l1' else nn.MSELoss()
+        self.resize, self.resize_mode = resize, resize_mode
+        self.instance_normalized = instance_normalized
+        self.num_scales = num_scales
+
+    def forward(self, inp, target):
+        self.model.eval()
+        inp, target = apply_imagenet_normalization(inp), apply_imagenet_normalization(target)
+        if self.resize:
+            inp = F.interpolate(inp, mode=self.resize_mode, size=(224, 224), align_corners=False)
+            target = F.interpolate(target, mode=self.resize_mode, size=(224, 224), align_corners=False)
+        loss = 0
+        for scale in range(self.num_scales):
+            feat_in = self.model(inp)
+            with torch.no_grad():
+                feat_tg = self.model(target)
+            for layer, weight in zip(self.layers, self.weights):
+                a, b = feat_in[layer].float(), feat_tg[layer].detach().float()
+                if self.instance_normalized:
+                    a, b = F.instance_norm(a), F.instance_norm(b)
+                loss = loss + weight * self.criterion(a, b)
+            if scale != self.num_scales - 1:
+                inp = F.interpolate(inp, mode=self.resize_mode, scale_factor=0.5, align_corners=False,
+                                    recompute_scale_factor=True)
+                target = F.interpolate(target, mode=self.resize_mode, scale_factor=0.5, align_corners=False,
+                                       recompute_scale_factor=True)
+        return loss.float()

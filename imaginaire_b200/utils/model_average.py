@@ -1,0 +1,79 @@
+"""Exponential moving average of the generator.  ref: imaginaire/utils/model_average.py:35-197
+
+Same wrapper shape (``.module`` / ``.averaged_model`` / ``num_updates_tracked``, so the
+checkpoint prefixes match) and the same update rule, including ``remove_sn``: the averaged
+copy stores W / sigma under ``weight`` instead of (weight_orig, weight_u, weight_v).  The
+update itself is batched with torch._foreach ops instead of one small kernel per tensor.
+"""
+import copy
+
+import torch
+from torch import nn
+from torch.nn.utils import remove_spectral_norm
+
+
+def requires_grad(model, flag=True):
+    for p in model.parameters():
+        p.requires_grad = flag
+
+
+class ModelAverage(nn.Module):
+    def __init__(self, module, beta=0.9999, start_iteration=1000, remove_sn=True):
+        super().__init__()
+        self.module = module
+        self.averaged_model = copy.deepcopy(self.module)
+        self.beta = beta
+        self.remove_sn = remove_sn
+        self.start_iteration = start_iteration
+        self.register_buffer('num_updates_tracked', torch.tensor(0, dtype=torch.long))
+        self._steps = 0
+        requires_grad(self.averaged_model, False)
+        if remove_sn:
+            def strip(m):
+                if hasattr(m, 'weight_orig'):
+                    remove_spectral_norm(m)
+            self.averaged_model.apply(strip)
+        else:
+            self.averaged_model.eval()
+        self._pairs = None
+
+    def forward(self, *inputs, **kwargs):
+        return self.module(*inputs, **kwargs)
+
+    @staticmethod
+    def sn_compute_weight(weight, u, v):
+        """W / sigma with the current u, v.  ref: model_average.py:183-197"""
+        mat = weight.reshape(weight.shape[0], -1)
+        sigma = torch.sum(u * torch.mv(mat, v))
+        return weight / sigma
+
+    def _build_pairs(self):
+        src = self.module.state_dict()
+        tgt = self.averaged_model.state_dict()
+        plain_t, plain_s, sn = [], [], []
+        for key, t in tgt.items():
+            if key.endswith('weight') and key + '_orig' in src:
+                sn.append((t, src[key + '_orig'], src[key + '_u'], src[key + '_v']))
+            elif t.is_floating_point():
+                plain_t.append(t)
+                plain_s.append(src[key])
+            else:
+                sn.append((t, src[key], None, None))   # integer buffers: plain copy
+        self._pairs = (plain_t, plain_s, sn)
+
+    @torch.no_grad()
+    def update_average(self):
+        self.num_updates_tracked += 1
+        self._steps += 1
+        beta = 0.0 if self._steps <= self.start_iteration else self.beta
+        if self._pairs is None:
+            self._build_pairs()
+        plain_t, plain_s, sn = self._pairs
+        # target = beta * target + (1 - beta) * source
+        torch._foreach_mul_(plain_t, beta)
+        torch._foreach_add_(plain_t, plain_s, alpha=1.0 - beta)
+        for t, w, u, v in sn:
+            if u is None:
+                t.copy_(w)
+            else:
+                t.mul_(beta).add_(self.sn_compute_weight(w, u, v), alpha=1.0 - beta)

@@ -1,0 +1,80 @@
+"""Builds networks, optimisers and the data-parallel wrapping.
+ref: imaginaire/utils/trainer.py:24-37 (seeds), :69-125 (get_model_optimizer_and_scheduler),
+     :128-216 (wrap / DDP), :242-306 (optimisers)
+
+apex is replaced as SURVEY.md Appendix C prescribes: mixed precision is the kernels' own
+bf16-storage / fp32-accumulate arithmetic (no loss scaling), FusedAdam becomes
+torch.optim.Adam(fused=True), apex DDP becomes torch DDP over NCCL.
+"""
+import random
+
+import numpy as np
+import torch
+from torch.nn.parallel import DistributedDataParallel
+
+from ..discriminators.spade import Discriminator
+from ..generators.spade import Generator
+from .distributed import get_rank, get_world_size
+from .init_weight import weights_init
+from .model_average import ModelAverage
+
+
+def set_random_seed(seed, by_rank=False):
+    if by_rank:
+        seed += get_rank()
+    random.seed(seed)
+    np.random.seed(seed)
+    torch.manual_seed(seed)
+    torch.cuda.manual_seed_all(seed)
+
+
+def get_optimizer(opt_cfg, params):
+    if opt_cfg.type != 'adam':
+        raise NotImplementedError('only adam is wired up for the SPADE step')
+    return torch.optim.Adam(params, lr=opt_cfg.lr, eps=getattr(opt_cfg, 'eps', 1e-8),
+                            betas=(opt_cfg.adam_beta1, opt_cfg.adam_beta2), fused=True)
+
+
+def get_model_optimizer_and_scheduler(cfg, seed=0, device='cuda'):
+    """Returns (net_G, net_D, opt_G, opt_D).  Networks are built and initialised with the same
+    seed on every rank, then the seed is offset by rank like the reference."""
+    set_random_seed(seed, by_rank=False)
+    net_G = Generator(cfg.gen, cfg.data)
+    net_D = Discriminator(cfg.dis, cfg.data)
+    init = getattr(cfg.trainer, 'init', None)
+    if init is not None:
+        fn = weights_init(init.type, init.gain, getattr(init, 'bias', None))
+        net_G.apply(fn)
+        net_D.apply(fn)
+    net_G, net_D = net_G.to(device), net_D.to(device)
+    set_random_seed(seed, by_rank=True)
+    opt_G = get_optimizer(cfg.gen_opt, [p for p in net_G.parameters() if p.requires_grad])
+    opt_D = get_optimizer(cfg.dis_opt, [p for p in net_D.parameters() if p.requires_grad])
+    return wrap_model_and_optimizer(cfg, net_G, net_D, opt_G, opt_D)
+
+
+def wrap_model_and_optimizer(cfg, net_G, net_D, opt_G, opt_D):
+    if cfg.trainer.model_average:
+        net_G = ModelAverage(net_G, cfg.trainer.model_average_beta,
+                             cfg.trainer.model_average_start_iteration,
+                             getattr(cfg.trainer, 'model_average_remove_sn', True))
+    return _wrap_model(net_G), _wrap_model(net_D), opt_G, opt_D
+
+
+class WrappedModel(torch.nn.Module):
+    """Single-process stand-in for DDP so that ``.module`` exists either way (trainer.py:168-190)."""
+
+    def __init__(self, module):
+        super().__init__()
+        self.module = module
+
+    def forward(self, *args, **kwargs):
+        return self.module(*args, **kwargs)
+
+
+def _wrap_model(model):
+    if get_world_size() > 1:
+        return DistributedDataParallel(model, device_ids=[torch.cuda.current_device()],
+                                       output_device=torch.cuda.current_device(),
+                                       find_unused_parameters=True, broadcast_buffers=False)
+    return WrappedModel(model)
