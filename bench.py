@@ -125,7 +125,7 @@ class ConvProbe:
                 s.record()
                 out = fn(*a, **k)
                 e.record()
-                probe.records.append((tag, flops_fn(out, *a, **k), s, e))
+                probe.records.append((tag, flops_fn(out, *a, **k), s, e, probe.describe(tag, out, a, k)))
                 return out
             return wrapper
 
@@ -145,13 +145,32 @@ class ConvProbe:
         ops.conv2d_wgrad = timed(self._orig[1], wgrad_flops, 'wgrad')
         ops.spade_gb_conv_modulate = timed(self._orig[2], gb_flops, 'spade_gb')
 
+    @staticmethod
+    def describe(tag, out, a, k):
+        if tag == 'fprop':
+            return 'x%s k%dx%d s%d -> %s' % (tuple(a[0].shape), a[3], a[4], a[5] if len(a) > 5 else k.get('stride', 1),
+                                              tuple(out.shape))
+        if tag == 'wgrad':
+            return 'x%s dy%s k%dx%d' % (tuple(a[0].shape), tuple(a[1].shape), a[4], a[5])
+        return 'hidden%s C%d k%d' % (tuple(a[0].shape), a[9], a[10])
+
+    def table(self, top=40):
+        rows = {}
+        for tag, fl, s, e, desc in self.records:
+            r = rows.setdefault((tag, desc), [0.0, 0.0, 0])
+            r[0] += fl; r[1] += s.elapsed_time(e); r[2] += 1
+        out = []
+        for (tag, desc), (fl, ms, n) in sorted(rows.items(), key=lambda kv: -kv[1][1])[:top]:
+            out.append('%7.3f ms x%-3d %7.1f TF/s  %-8s %s' % (ms, n, fl / (ms * 1e-3) / 1e12 if ms > 0 else 0, tag, desc))
+        return '\n'.join(out)
+
     def remove(self):
         from imaginaire_b200 import ops
         ops.conv2d_fprop, ops.conv2d_wgrad, ops.spade_gb_conv_modulate = self._orig
 
     def summary(self):
         by = {}
-        for tag, fl, s, e in self.records:
+        for tag, fl, s, e, _ in self.records:
             ms = s.elapsed_time(e)
             a = by.setdefault(tag, [0.0, 0.0, 0])
             a[0] += fl; a[1] += ms; a[2] += 1
@@ -316,6 +335,8 @@ def run_ours(args):
     torch.cuda.synchronize()
     probe.remove()
     by, conv_flops, conv_ms = probe.summary()
+    if os.environ.get('IMX_BENCH_VERBOSE') and rank == 0:
+        print(probe.table(), file=sys.stderr, flush=True)
     peaks = load_peaks()
     achieved = conv_flops / (conv_ms * 1e-3) / 1e12 if conv_ms > 0 else 0.0
     ms_per_step = ms / args.steps

@@ -45,7 +45,9 @@ template <int BN> struct Cfg {
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
     static constexpr int TMEM_COLS = (2 * BN < 32) ? 32 : 2 * BN;
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+    static constexpr int STATS_SMEM_CH = 2048;   // per-CTA statistics accumulators for up to this many channels
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ +
+                                      2 * STATS_SMEM_CH * 4;
 };
 
 struct ConvArgs {
@@ -95,6 +97,14 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     uint64_t* tmem_full = bars + 2 * C::STAGES;
     uint64_t* tmem_empty = bars + 2 * C::STAGES + 2;
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * C::STAGES + 4);
+    // Batch statistics are accumulated per CTA in shared memory over all of its tiles and flushed
+    // once at the end: 2*Cout global atomics per CTA instead of per tile (the per-tile version
+    // serialises on the few L2 slices that hold the 2*Cout accumulators).
+    float* s_stats = reinterpret_cast<float*>(smem + C::STAGES * C::STAGE_BYTES + 256);
+    const bool stats_in_smem = kMode == 0 && (p.flags & IMX_EPI_STATS) && !(p.flags & IMX_EPI_STATS_INSTANCE) &&
+                               p.Cout <= C::STATS_SMEM_CH;
+    if (stats_in_smem)
+        for (int i = threadIdx.x; i < 2 * p.Cout; i += kThreads) s_stats[i] = 0.0f;
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -287,7 +297,12 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                             const float qq = imx::warp_sum(f[j] * f[j]);
                             if (lane == j) { s_mine = s; q_mine = qq; }
                         }
-                        if (nb + lane < p.Cout) {
+                        if (stats_in_smem) {
+                            if (nb + lane < p.Cout) {
+                                atomicAdd(s_stats + nb + lane, s_mine);
+                                atomicAdd(s_stats + p.Cout + nb + lane, q_mine);
+                            }
+                        } else if (nb + lane < p.Cout) {
                             // layout (2, G, Cout): G = 1 (batch statistics) or N (instance statistics)
                             const bool inst = (p.flags & IMX_EPI_STATS_INSTANCE) != 0;
                             float* sdst = p.stats + (inst ? (size_t)img * p.Cout : 0) + nb + lane;
@@ -361,6 +376,12 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 
     tc_fence_before_sync();
     __syncthreads();
+    if (stats_in_smem) {
+        for (int i = threadIdx.x; i < 2 * p.Cout; i += kThreads) {
+            const float v = s_stats[i];
+            if (v != 0.0f) atomicAdd(p.stats + i, v);
+        }
+    }
     if (warp == 2) {
         tc_fence_after_sync();
         tmem_dealloc(tmem_base, C::TMEM_COLS);

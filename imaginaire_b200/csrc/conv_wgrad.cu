@@ -35,11 +35,18 @@ constexpr int kEpiWarp0 = 4;
 constexpr int BOX_BYTES = BKP * 64 * 2;   // one {64 ch x 64 px} box
 constexpr int A_BYTES = 2 * BOX_BYTES;
 
+// T = filter taps accumulated per work unit.  The dY tile (A operand) of a pixel step is the
+// same for every tap, so a unit that owns T taps loads it once and issues T MMAs into T TMEM
+// accumulators: with narrow Cin tiles (BN <= 128) a single tap would need more shared-memory
+// fill bandwidth (A + B bytes per MMA cycle) than L2 can deliver.  T * BN = 256 columns per
+// accumulator stage, two stages.
 template <int BN> struct WCfg {
-    static constexpr int B_BYTES = (BN / 64) * BOX_BYTES;
+    static constexpr int T = 256 / BN;
+    static constexpr int TAP_BYTES = (BN / 64) * BOX_BYTES;      // X boxes of one tap
+    static constexpr int B_BYTES = T * TAP_BYTES;                  // = 32 KB for every BN
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
-    static constexpr int TMEM_COLS = 2 * BN;
+    static constexpr int STAGES = 4;
+    static constexpr int TMEM_COLS = 2 * T * BN;                   // = 512
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
 };
 
@@ -52,13 +59,17 @@ struct WgradArgs {
     float* ws;
 };
 
-struct Unit { int co_t, ci_t, tap, split; };
+struct Unit { int co_t, ci_t, tap0, ntaps, split; };
 
+template <int T>
 __device__ __forceinline__ Unit decode_unit(int u, const WgradArgs& p) {
     Unit r;
     const int taps = p.KH * p.KW;
+    const int groups = (taps + T - 1) / T;
     r.split = u % p.splits; u /= p.splits;
-    r.tap = u % taps; u /= taps;
+    const int g = u % groups; u /= groups;
+    r.tap0 = g * T;
+    r.ntaps = taps - r.tap0 < T ? taps - r.tap0 : T;
     r.ci_t = u % p.ci_tiles;
     r.co_t = u / p.ci_tiles;
     return r;
@@ -118,8 +129,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
             int stage = 0;
             uint32_t phase = 0;
             for (int u = blockIdx.x; u < p.total_units; u += gridDim.x) {
-                const Unit un = decode_unit(u, p);
-                const int kh = un.tap / p.KW, kw = un.tap - kh * p.KW;
+                const Unit un = decode_unit<C::T>(u, p);
                 int kb, ke;
                 k_range(un.split, kb, ke);
                 for (int k = kb; k < ke; ++k) {
@@ -128,15 +138,20 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
                     const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
                     const int oy0 = ty * p.th, ox0 = tx * p.tw;
                     mbar_wait(&empty_bar[stage], phase ^ 1);
-                    mbar_arrive_expect_tx(&full_bar[stage], C::STAGE_BYTES);
+                    mbar_arrive_expect_tx(&full_bar[stage], A_BYTES + un.ntaps * C::TAP_BYTES);
                     uint8_t* sa = smem_a + stage * A_BYTES;
                     tma_load_4d(sa, &tmap_dy, &full_bar[stage], un.co_t * BM, ox0, oy0, img);
                     tma_load_4d(sa + BOX_BYTES, &tmap_dy, &full_bar[stage], un.co_t * BM + 64, ox0, oy0, img);
                     uint8_t* sb = smem_b + stage * C::B_BYTES;
+                    for (int t = 0; t < un.ntaps; ++t) {
+                        const int tap = un.tap0 + t;
+                        const int kh = tap / p.KW, kw = tap - kh * p.KW;
 #pragma unroll
-                    for (int j = 0; j < BN / 64; ++j)
-                        tma_load_4d(sb + j * BOX_BYTES, &tmap_x, &full_bar[stage], un.ci_t * BN + j * 64,
-                                    ox0 * p.stride + kw - p.pad, oy0 * p.stride + kh - p.pad, img);
+                        for (int j = 0; j < BN / 64; ++j)
+                            tma_load_4d(sb + t * C::TAP_BYTES + j * BOX_BYTES, &tmap_x, &full_bar[stage],
+                                        un.ci_t * BN + j * 64, ox0 * p.stride + kw - p.pad,
+                                        oy0 * p.stride + kh - p.pad, img);
+                    }
                     if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                 }
             }
@@ -148,25 +163,28 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
             uint32_t phase = 0;
             int iter = 0;
             for (int u = blockIdx.x; u < p.total_units; u += gridDim.x, ++iter) {
-                const Unit un = decode_unit(u, p);
+                const Unit un = decode_unit<C::T>(u, p);
                 int kb, ke;
                 k_range(un.split, kb, ke);
                 const int as = iter & 1;
                 const uint32_t aphase = (iter >> 1) & 1;
                 mbar_wait(&tmem_empty[as], aphase ^ 1);
                 tc_fence_after_sync();
-                const uint32_t d_tmem = tmem_base + as * BN;
+                const uint32_t d_tmem = tmem_base + as * (C::T * BN);
                 for (int k = kb; k < ke; ++k) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after_sync();
                     const uint32_t a0 = smem_u32(smem_a + stage * A_BYTES);
                     const uint32_t b0 = smem_u32(smem_b + stage * C::B_BYTES);
+                    for (int t = 0; t < un.ntaps; ++t) {
 #pragma unroll
-                    for (int j = 0; j < BKP / UMMA_K; ++j) {
-                        // 16 pixels = 16 rows of 128 B inside every 64-channel box
-                        const uint64_t da = make_mnmajor_sw128_desc(a0 + j * UMMA_K * 128, 1024, BOX_BYTES);
-                        const uint64_t db = make_mnmajor_sw128_desc(b0 + j * UMMA_K * 128, 1024, BOX_BYTES);
-                        umma_bf16_ss(d_tmem, da, db, idesc, (k > kb) || (j > 0));
+                        for (int j = 0; j < BKP / UMMA_K; ++j) {
+                            // 16 pixels = 16 rows of 128 B inside every 64-channel box
+                            const uint64_t da = make_mnmajor_sw128_desc(a0 + j * UMMA_K * 128, 1024, BOX_BYTES);
+                            const uint64_t db = make_mnmajor_sw128_desc(b0 + t * C::TAP_BYTES + j * UMMA_K * 128, 1024,
+                                                                        BOX_BYTES);
+                            umma_bf16_ss(d_tmem + t * BN, da, db, idesc, (k > kb) || (j > 0));
+                        }
                     }
                     umma_commit(&empty_bar[stage]);
                     if (k == ke - 1) umma_commit(&tmem_full[as]);
@@ -185,21 +203,23 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
         const int taps = p.KH * p.KW;
         int iter = 0;
         for (int u = blockIdx.x; u < p.total_units; u += gridDim.x, ++iter) {
-            const Unit un = decode_unit(u, p);
+            const Unit un = decode_unit<C::T>(u, p);
             int kb, ke;
             k_range(un.split, kb, ke);
             const int as = iter & 1;
             const uint32_t aphase = (iter >> 1) & 1;
             mbar_wait(&tmem_full[as], aphase);
             tc_fence_after_sync();
-            const uint32_t t_acc = tmem_base + as * BN + (static_cast<uint32_t>(q * 32) << 16);
-            float* dst = p.ws + ((((size_t)un.split * taps + un.tap) * p.co_r + un.co_t * BM + row) * p.ci_r) + un.ci_t * BN;
+            const uint32_t t_acc = tmem_base + as * (C::T * BN) + (static_cast<uint32_t>(q * 32) << 16);
 #pragma unroll 1
-            for (int ch = 0; ch < BN / 32; ++ch) {
+            for (int cc = 0; cc < un.ntaps * (BN / 32); ++cc) {
+                const int t = cc / (BN / 32), ch = cc - t * (BN / 32);
+                float* dst = p.ws + ((((size_t)un.split * taps + un.tap0 + t) * p.co_r + un.co_t * BM + row) * p.ci_r) +
+                             un.ci_t * BN;
                 uint32_t v[32];
-                tmem_ld_32x32(t_acc + ch * 32, v);
+                tmem_ld_32x32(t_acc + t * BN + ch * 32, v);
                 tmem_ld_wait();
-                if (ch == BN / 32 - 1) {
+                if (cc == un.ntaps * (BN / 32) - 1) {
                     tc_fence_before_sync();
                     mbar_arrive(&tmem_empty[as]);
                 }
@@ -263,7 +283,8 @@ int make_plan(Plan& pl, int N, int H, int W, int Cin_p, int Cout_p, int KH, int 
     pl.ptiles = (int)ptiles;
     pl.co_tiles = (Cout_p + BM - 1) / BM;
     pl.ci_tiles = (Cin_p + pl.BN - 1) / pl.BN;
-    const long base_units = (long)pl.co_tiles * pl.ci_tiles * KH * KW;
+    const int T = 256 / pl.BN;
+    const long base_units = (long)pl.co_tiles * pl.ci_tiles * ((KH * KW + T - 1) / T);
     // enough units for ~2 waves, but keep at least 8 K steps per unit
     long splits = (2L * imx::kNumSMs + base_units - 1) / base_units;
     long max_splits = ptiles / 8 > 1 ? ptiles / 8 : 1;
@@ -339,7 +360,8 @@ extern "C" int imx_conv2d_igemm_wgrad_bf16(const imx_bf16* x, const imx_bf16* dy
     a.tw = pl.tw; a.th = pl.th; a.tw_log2 = pl.tw_log2;
     a.tiles_x = pl.tiles_x; a.tiles_y = pl.tiles_y; a.ptiles = pl.ptiles;
     a.co_tiles = pl.co_tiles; a.ci_tiles = pl.ci_tiles; a.splits = pl.splits;
-    a.total_units = pl.co_tiles * pl.ci_tiles * KH * KW * pl.splits;
+    const int T = 256 / pl.BN;
+    a.total_units = pl.co_tiles * pl.ci_tiles * ((KH * KW + T - 1) / T) * pl.splits;
     a.co_r = pl.co_tiles * BM; a.ci_r = pl.ci_tiles * pl.BN;
     a.ws = reinterpret_cast<float*>(workspace);
 

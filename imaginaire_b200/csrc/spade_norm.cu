@@ -36,10 +36,12 @@ inline RowMap make_rowmap(int C) {
     return m;
 }
 
-// Split `np` pixels of one group over blocks: a few CTAs per SM, whole rows-per-iteration.
-inline int pick_blocks(long np, int rows, int groups) {
+// Split `np` pixels of one group over blocks.  `per_sm` CTAs per SM in total: the reducing
+// kernels end with 2C atomics per CTA onto the same few L2 slices, so they want few, long-lived
+// CTAs (2 per SM, 8 loads in flight per thread); the pure streaming kernels take more.
+inline int pick_blocks(long np, int rows, int groups, int per_sm = 2) {
     long iters = (np + rows - 1) / rows;
-    long want = (8L * imx::kNumSMs + groups - 1) / groups;
+    long want = ((long)per_sm * imx::kNumSMs + groups - 1) / groups;
     long b = iters < want ? iters : want;
     return (int)(b < 1 ? 1 : b);
 }
@@ -78,13 +80,13 @@ stats_kernel(const uint4* __restrict__ x, float* __restrict__ sum, float* __rest
         float s[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         if (active) {
             long p = p0 + r;
-            // 4 independent 128-bit loads in flight per thread
-            for (; p + 3L * rows < p1; p += 4L * rows) {
-                uint4 v[4];
+            // 8 independent 128-bit loads in flight per thread
+            for (; p + 7L * rows < p1; p += 8L * rows) {
+                uint4 v[8];
 #pragma unroll
-                for (int u = 0; u < 4; ++u) v[u] = imx::ldg_stream(base + (size_t)(p + (long)u * rows) * row_stride_c8 + c8);
+                for (int u = 0; u < 8; ++u) v[u] = imx::ldg_stream(base + (size_t)(p + (long)u * rows) * row_stride_c8 + c8);
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
+                for (int u = 0; u < 8; ++u) {
                     float f[8];
                     unpack8(v[u], f);
 #pragma unroll
@@ -395,7 +397,7 @@ extern "C" int imx_spade_modulate_fwd(const imx_bf16* x, const float* mean, cons
     const RowMap m = make_rowmap(C);
     ModArgs a{reinterpret_cast<const uint4*>(x), nullptr, mean, rstd, w, b, gamma, beta,
               N, H, W, C, stats_per_instance, gb_mode, act, up2x};
-    dim3 grid(pick_blocks((long)H * W, m.rows, N), N);
+    dim3 grid(pick_blocks((long)H * W, m.rows, N, 6), N);
     modulate_kernel<0><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
         a, reinterpret_cast<uint4*>(y), nullptr, nullptr, nullptr, 0.0f, 1, m.cg, m.tpr, m.rows);
     return imx::check_launch("spade_modulate_fwd");
@@ -439,7 +441,7 @@ extern "C" int imx_spade_modulate_bwd_dx(const imx_bf16* x, const imx_bf16* dy,
     const RowMap m = make_rowmap(C);
     ModArgs a{reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(dy), mean, rstd, w, b, gamma, beta,
               N, H, W, C, stats_per_instance, gb_mode, act, 0};
-    dim3 grid(pick_blocks((long)H * W, m.rows, N), N);
+    dim3 grid(pick_blocks((long)H * W, m.rows, N, 6), N);
     modulate_kernel<2><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
         a, reinterpret_cast<uint4*>(dx), nullptr, nullptr, const_cast<float*>(red),
         use_batch_stats ? 1.0f / count : 0.0f, use_batch_stats, m.cg, m.tpr, m.rows);

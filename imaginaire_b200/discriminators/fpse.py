@@ -12,6 +12,7 @@ import torch
 import torch.nn.functional as F
 from torch import nn
 
+from .. import functional as NF
 from ..layers import Conv2dBlock
 
 
@@ -54,10 +55,18 @@ class FPSEDiscriminator(nn.Module):
         feat23 = self.upsample2x(feat24) + self.lat3(feat13)
         feat22 = self.upsample2x(feat23) + self.lat2(feat12)
         feats = (self.final2(feat22), self.final3(feat23), self.final4(feat24))
-        segemb = F.avg_pool2d(self.embedding(segmaps), kernel_size=2, stride=2)
+        # The reference embeds the full-resolution label map (1x1 conv to 2F channels) and then
+        # average-pools the embedding 4 times.  A 1x1 convolution commutes with average pooling,
+        # so the same embeddings are computed from the pooled label maps: a 2F-channel tensor is
+        # never materialised at full resolution.  The embedding filter (and its spectral-norm
+        # power iteration) is evaluated once per forward, as in the reference.
+        conv = self.embedding.layers['conv']
+        weight = conv.effective_weight()
+        pooled = F.avg_pool2d(segmaps.float(), kernel_size=2, stride=2)
         preds = []
         for feat in feats:
-            segemb = F.avg_pool2d(segemb, kernel_size=2, stride=2)
+            pooled = F.avg_pool2d(pooled, kernel_size=2, stride=2)
+            segemb = NF.conv2d(NF.to_nhwc(pooled), weight, conv.bias, None, 1, 0)
             pred = self.output(feat) + torch.mul(segemb, self.seg(feat)).sum(dim=1, keepdim=True)
             preds.append(pred)
         return tuple(preds)

@@ -1,0 +1,33 @@
+"""Kernel-time breakdown of one training iteration with torch.profiler (developer tool)."""
+import os, sys, json
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from torch.profiler import profile, ProfilerActivity
+import bench
+from imaginaire_b200.config import Config
+from imaginaire_b200.trainers.spade import Trainer
+from imaginaire_b200.utils.trainer import get_model_optimizer_and_scheduler
+
+cfg = Config(os.path.join(bench.ROOT, 'configs', bench.CONFIG_NAME))
+dev = torch.device('cuda:0')
+net_G, net_D, opt_G, opt_D = get_model_optimizer_and_scheduler(cfg, seed=0, device=dev)
+trainer = Trainer(cfg, net_G, net_D, opt_G, opt_D)
+data = {k: v.to(dev) for k, v in bench.synthetic_batch(cfg, int(sys.argv[1]) if len(sys.argv) > 1 else 8, 100).items()}
+for _ in range(2):
+    trainer.step(dict(data))
+torch.cuda.synchronize()
+with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+    trainer.step(dict(data))
+    torch.cuda.synchronize()
+rows = []
+for e in prof.key_averages():
+    t = getattr(e, 'device_time_total', None)
+    if t is None:
+        t = getattr(e, 'cuda_time_total', 0)
+    if e.device_type == torch.autograd.DeviceType.CUDA and t > 0:
+        rows.append((t, e.count, e.key))
+rows.sort(reverse=True)
+tot = sum(r[0] for r in rows)
+print('total device kernel time %.1f ms over %d kernel names' % (tot / 1e3, len(rows)))
+for t, c, k in rows[:45]:
+    print('%8.2f ms %5.1f%% x%-5d %s' % (t / 1e3, 100.0 * t / tot, c, k[:110]))
