@@ -224,24 +224,35 @@ def compute_norm_stats(x, ns, up2x=False):
         count = h * w if ns.per_instance else n * h * w
     world = _world(ns)
     if world > 1:
-        # one message of 2C+1 floats: [sum, sumsq, count]; everything stays on the device
-        packed = torch.cat([sums.reshape(-1), sums.new_tensor([float(count)])])
-        dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=ns.process_group)
-        gsums = packed[:-1].view_as(sums)
-        count_t = packed[-1]
-        mean = (gsums[0] / count_t).reshape(-1)
-        var = (gsums[1].reshape(-1) / count_t - mean * mean).clamp_min_(0.0)
-        rstd = torch.rsqrt(var + ns.eps)
+        mean, rstd, unbiased = sync_batch_stats(sums, count, ns.eps, ns.process_group)
         if ns.track_running_stats and ns.running_mean is not None:
-            _update_running(ns, mean, var * (count_t / (count_t - 1.0)))
+            _update_running(ns, mean, unbiased)
         # the backward kernels take the global element count as a host scalar: equal
         # per-rank batches (DistributedSampler) are assumed there
-        return mean.contiguous(), rstd.contiguous(), count * world
+        return mean, rstd, count * world
     update = ns.training and ns.track_running_stats and ns.running_mean is not None and not ns.per_instance
     momentum = _momentum(ns) if update else 0.0
     mean, rstd = ops.bn_finalize(sums, count, ns.eps, ns.running_mean if update else None,
                                  ns.running_var if update else None, momentum)
     return mean, rstd, count
+
+
+def sync_batch_stats(sums, count, eps, group=None):
+    """Cross-rank batch statistics from per-rank partial sums (works on any device / backend).
+
+    sums: (2, 1, C) = [sum x, sum x^2] of this rank; count: this rank's elements per channel.
+    One all-reduce of 2C+1 floats [sum, sumsq, count] replaces torch SyncBatchNorm's all-gather
+    of [mean, invstd, count] + batch_norm_gather_stats_with_counts (torch
+    nn/modules/_functions.py:49-86): same global mean / biased variance, also for unequal
+    per-rank counts.  Returns (mean, rstd, unbiased_var), each (C,); nothing leaves the device."""
+    packed = torch.cat([sums.reshape(-1), sums.new_tensor([float(count)])])
+    dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=group)
+    gsums = packed[:-1].view_as(sums)
+    count_t = packed[-1]
+    mean = (gsums[0] / count_t).reshape(-1)
+    var = (gsums[1].reshape(-1) / count_t - mean * mean).clamp_min_(0.0)
+    rstd = torch.rsqrt(var + eps)
+    return mean.contiguous(), rstd.contiguous(), var * (count_t / (count_t - 1.0))
 
 
 def _momentum(ns):
