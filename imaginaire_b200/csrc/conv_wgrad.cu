@@ -391,3 +391,70 @@ extern "C" int imx_conv2d_igemm_wgrad_bf16(const imx_bf16* x, const imx_bf16* dy
     wgrad_reduce_kernel<<<(int)blocks, 256, 0, s>>>(a.ws, dw, Cout, Cin, KH * KW, pl.splits, a.co_r, a.ci_r);
     return imx::check_launch("conv2d_wgrad_reduce");
 }
+
+// ---------------------------------------------------------------------------------------------
+// Weight gradient for callers that must not allocate.
+//
+// imx_conv2d_igemm_wgrad_bf16 needs a split-K workspace that the caller allocates.  Some hosts
+// cannot do that at the point where they need the gradient: a training server that reserves all
+// of its device memory once at start-up and then forbids every later cudaMalloc (a late
+// allocation can fail, or stall the whole device while the driver maps memory), or a plugin
+// that runs on a thread which simply has no allocator to call.  For them the workspace lives in
+// this translation unit as a fixed-size device array that is part of the loaded library image:
+// every GPU that loads the library carries IMX_WGRAD_NOALLOC_SCRATCH_BYTES of it until the
+// process exits, and no call ever allocates or frees anything.
+//
+// `g_wgrad_noalloc_scratch` is a device symbol.  In host code its name is only a stand-in, not a
+// device address, so the host asks the runtime for the real address once per device
+// (cudaGetSymbolAddress, with that device current) and hands that pointer to the kernels.
+static __device__ __align__(256) unsigned char g_wgrad_noalloc_scratch[IMX_WGRAD_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mu;
+void* g_noalloc_ptr[kMaxDevices] = {nullptr};
+
+// Device address of the scratch array on the CURRENT device (looked up on first use per device).
+int noalloc_scratch_for_current_device(void** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return imx::set_error((int)e, "conv2d_wgrad_noalloc: cudaGetDevice: %s", cudaGetErrorString(e));
+    if (dev < 0 || dev >= kMaxDevices)
+        return imx::set_error(IMX_ERR_UNSUPPORTED, "conv2d_wgrad_noalloc: device index %d outside [0, %d)", dev, kMaxDevices);
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (g_noalloc_ptr[dev] == nullptr) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_wgrad_noalloc_scratch);
+        if (e != cudaSuccess || p == nullptr)
+            return imx::set_error((int)e, "conv2d_wgrad_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev,
+                                  cudaGetErrorString(e));
+        g_noalloc_ptr[dev] = p;
+    }
+    *out = g_noalloc_ptr[dev];
+    return IMX_OK;
+}
+
+}  // namespace
+
+extern "C" int imx_conv2d_igemm_wgrad_bf16_noalloc(const imx_bf16* x, const imx_bf16* dy, float* dw,
+                                                   int N, int H, int W, int Cin, int Cin_p,
+                                                   int Cout, int Cout_p, int KH, int KW,
+                                                   int stride, int pad, imx_stream_t stream) {
+    // Size first: a layer whose split-K partials do not fit is refused before anything runs.
+    const int64_t need = imx_conv2d_wgrad_workspace_bytes(N, H, W, Cin, Cin_p, Cout, Cout_p, KH, KW, stride, pad);
+    if (need < 0) return IMX_ERR_INVALID_ARG;   // message already set by the size query
+    if (need > (int64_t)IMX_WGRAD_NOALLOC_SCRATCH_BYTES)
+        return imx::set_error(IMX_ERR_TOO_LARGE,
+                              "conv2d_wgrad_noalloc: this layer needs %lld bytes of split-K scratch but the built-in "
+                              "array holds %lld; use imx_conv2d_igemm_wgrad_bf16 with a caller-owned workspace",
+                              (long long)need, (long long)IMX_WGRAD_NOALLOC_SCRATCH_BYTES);
+    void* scratch = nullptr;
+    int rc = noalloc_scratch_for_current_device(&scratch);
+    if (rc) return rc;
+    // Nothing in the scratch has to start at zero: every (split, tap, Cout, Cin) slot that the
+    // reduction kernel reads is overwritten by this call's GEMM units first, so whatever the
+    // previous call left behind is never observed.
+    return imx_conv2d_igemm_wgrad_bf16(x, dy, dw, scratch, (int64_t)IMX_WGRAD_NOALLOC_SCRATCH_BYTES, N, H, W, Cin, Cin_p,
+                                       Cout, Cout_p, KH, KW, stride, pad, stream);
+}

@@ -338,3 +338,21 @@ def conv2d_wgrad(x, dy, cin, cout, kh, kw, stride=1, pad=0):
     lib.call('imx_conv2d_igemm_wgrad_bf16', _ptr(x), _ptr(dy), _ptr(dw), _ptr(ws), int(nbytes), n, h, w, cin, cin_p,
              cout, cout_p, kh, kw, stride, pad, _stream())
     return dw
+
+
+def conv2d_wgrad_noalloc(x, dy, cin, cout, kh, kw, stride=1, pad=0, out=None):
+    """conv2d_wgrad through the entry point that needs no workspace from the caller.
+
+    For hosts that may not allocate device memory when the gradient is due (all memory
+    reserved at start-up, allocation forbidden afterwards): the split-K scratch is a fixed
+    array inside the library, so only the caller's own x, dy and the result buffer `out`
+    (fp32 [Cout, Cin, KH, KW]; allocated here when not given) are involved.  Layers whose
+    partial sums exceed the built-in array raise; calls must not overlap on the GPU."""
+    _req_cuda(x, dy); _req_nhwc(x, 'x'); _req_nhwc(dy, 'dy')
+    n, cin_p, h, w = x.shape
+    cout_p = dy.shape[1]
+    if out is None:
+        out = torch.empty((cout, cin, kh, kw), dtype=torch.float32, device=x.device)
+    _C.lib().call('imx_conv2d_igemm_wgrad_bf16_noalloc', _ptr(x), _ptr(dy), _ptr(out), n, h, w, cin, cin_p,
+                  cout, cout_p, kh, kw, stride, pad, _stream())
+    return out

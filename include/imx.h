@@ -241,6 +241,30 @@ IMX_API int64_t imx_conv2d_wgrad_workspace_bytes(int N, int H, int W, int Cin, i
                                          int Cout, int Cout_p, int KH, int KW,
                                          int stride, int pad);
 
+/* The weight gradient again, for callers that are not able to allocate device memory (no
+ * counterpart in the reference: its extensions always let torch allocate).  Think of a host
+ * that reserves its whole device-memory budget at start-up and forbids cudaMalloc afterwards,
+ * or a plugin thread that has no allocator: they cannot provide the split-K workspace that
+ * imx_conv2d_igemm_wgrad_bf16 asks for.  Here the workspace is a device array of
+ * IMX_WGRAD_NOALLOC_SCRATCH_BYTES built into the library (each GPU that loads the library
+ * holds that much until the process exits); the call allocates and frees nothing.
+ *   - Same arguments and result as imx_conv2d_igemm_wgrad_bf16 minus the workspace; x, dy and
+ *     dw are still the caller's buffers.
+ *   - A layer whose partial sums need more than the built-in array is rejected with
+ *     IMX_ERR_TOO_LARGE (10004) and a message naming both sizes; nothing is launched.
+ *   - The first call on each device looks up the array's device address (one
+ *     cudaGetSymbolAddress with that device current).  Make that first call during set-up,
+ *     before any stream capture begins.
+ *   - All calls share the one array.  Its contents survive from call to call but never have to
+ *     be cleared: each call overwrites every slot it later reads.  Two calls that overlap on
+ *     the GPU (different streams, or another thread) would write the same scratch and race;
+ *     run them one after the other. */
+#define IMX_WGRAD_NOALLOC_SCRATCH_BYTES (64 * 1024 * 1024)
+IMX_API int imx_conv2d_igemm_wgrad_bf16_noalloc(const imx_bf16* x, const imx_bf16* dy, float* dw,
+                                                int N, int H, int W, int Cin, int Cin_p,
+                                                int Cout, int Cout_p, int KH, int KW,
+                                                int stride, int pad, imx_stream_t stream);
+
 /* Per-channel sum over pixels of an NHWC bf16 tensor (bias gradient):
  * out[c] = sum_{n,p} x[n,p,c]; fp32, caller zero-fills. */
 IMX_API int imx_channel_sum_nhwc_bf16(const imx_bf16* x, float* out, int NP, int C, int Cp,
