@@ -36,6 +36,9 @@ def parse_args():
     ap.add_argument('--config', default=CONFIG_NAME)
     ap.add_argument('--batch', type=int, default=None, help='per-GPU batch override (debugging only)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--one-step', action='store_true',
+                    help='profiling aid: run exactly one training iteration (after --warmup) and exit, '
+                         'so that an ncu launch list covers one step and nothing else')
     return ap.parse_args()
 
 
@@ -295,6 +298,12 @@ def run_ours(args):
 
     for _ in range(args.warmup):
         one_step(resident)
+    if args.one_step:
+        torch.cuda.synchronize()
+        one_step(resident)
+        torch.cuda.synchronize()
+        print(json.dumps({'one_step': True, 'note': 'profiling run, no metric'}), flush=True)
+        return
 
     lib = _C.lib()
     sampler = ClockSampler(local_rank)

@@ -91,6 +91,25 @@ def upsample2x(x):
 
 # ------------------------------------------------------------ convolution
 
+_PACK_CACHE = {}
+
+
+def _packed_weight(weight, inner_p, transpose_flip, inv_sigma=None):
+    """bf16 GEMM-layout copy of a filter.  Parameters that are convolved with directly (no
+    weight norm: frozen VGG filters, un-normalised SPADE projections) keep their packed copy
+    until the optimizer changes them (tensor version counter); spectrally normalised filters
+    are new tensors every forward and are packed each time."""
+    if inv_sigma is not None or not isinstance(weight, torch.nn.Parameter):
+        return ops.pack_conv_weight(weight, inv_sigma, cin_p=inner_p, transpose_flip=transpose_flip)
+    key = (id(weight), inner_p, transpose_flip)
+    hit = _PACK_CACHE.get(key)
+    if hit is not None and hit[0] == weight._version and hit[1] == weight.data_ptr():
+        return hit[2]
+    packed = ops.pack_conv_weight(weight, None, cin_p=inner_p, transpose_flip=transpose_flip)
+    _PACK_CACHE[key] = (weight._version, weight.data_ptr(), packed)
+    return packed
+
+
 def _act_backward(dy, y, act):
     """Gradient through an activation that was fused into a conv epilogue (y = act(pre))."""
     if act == ops.ACT_LRELU:
@@ -100,14 +119,38 @@ def _act_backward(dy, y, act):
     return dy
 
 
+def spectral_sigma(weight_orig, u_buf, v_buf, training, n_power_iterations=1, eps=1e-12):
+    """Spectral norm of a filter with torch.nn.utils.spectral_norm's semantics (the reference's
+    weight norm, imaginaire/layers/weight_norm.py:85): in training mode run the power iteration
+    in place on the module's u / v buffers (no autograd), then sigma = u^T W v.  Returns
+    (1/sigma as a 1-element tensor, u copy, v copy); the copies are what autograd may keep,
+    because the buffers change again on the next forward.  W v of the last iteration is reused
+    for sigma (torch recomputes the identical product), so the filter is read twice, not three
+    times, and W / sigma is never materialised: the division happens inside the repack kernel."""
+    mat = weight_orig.detach().reshape(weight_orig.shape[0], -1)
+    with torch.no_grad():
+        wv = None
+        if training:
+            for _ in range(n_power_iterations):
+                v_buf.copy_(torch.nn.functional.normalize(torch.mv(mat.t(), u_buf), dim=0, eps=eps))
+                wv = torch.mv(mat, v_buf)
+                u_buf.copy_(torch.nn.functional.normalize(wv, dim=0, eps=eps))
+        if wv is None:
+            wv = torch.mv(mat, v_buf)
+        sigma = torch.dot(u_buf, wv)
+        return (1.0 / sigma).reshape(1), u_buf.clone(), v_buf.clone()
+
+
 class _Conv2d(torch.autograd.Function):
-    """y = act(conv(x, w) + bias) (+ residual); x, y NHWC bf16; w fp32 [Cout, Cin, KH, KW]."""
+    """y = act(conv(x, w * inv_sigma) + bias) (+ residual); x, y NHWC bf16; w fp32
+    [Cout, Cin, KH, KW].  With spectral norm (inv_sigma, u, v given) `w` is weight_orig and
+    the backward returns the gradient for weight_orig, including the path through sigma."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, residual, stride, pad, act, stats):
+    def forward(ctx, x, weight, bias, residual, stride, pad, act, stats, inv_sigma, u, v):
         cout, cin, kh, kw = weight.shape
         cin_p = x.shape[1]
-        wpk = ops.pack_conv_weight(weight, None, cin_p=cin_p)
+        wpk = _packed_weight(weight, cin_p, False, inv_sigma)
         flags = {ops.ACT_NONE: 0, ops.ACT_LRELU: ops.EPI_LRELU, ops.ACT_RELU: ops.EPI_RELU}[act]
         y = ops.conv2d_fprop(x, wpk, cout, kh, kw, stride, pad, bias=bias, residual=residual, flags=flags,
                              stats=stats)
@@ -116,34 +159,40 @@ class _Conv2d(torch.autograd.Function):
         ctx.has_bias = bias is not None
         ctx.has_res = residual is not None
         needs_y = act != ops.ACT_NONE
-        ctx.save_for_backward(x, weight, y if needs_y else None)
+        ctx.save_for_backward(x, weight, y if needs_y else None, inv_sigma, u, v)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        x, weight, y = ctx.saved_tensors
+        x, weight, y, inv_sigma, u, v = ctx.saved_tensors
         cout, cin, kh, kw, h, w = ctx.geom
         dy = _as_nhwc(dy)
         if y is not None:
             dy = _act_backward(dy, y, ctx.act)
         dx = dw = db = dres = None
         if ctx.needs_input_grad[0]:
-            dx = conv2d_dgrad(dy, weight, ctx.stride, ctx.pad, h, w, x.shape[1])
+            dx = conv2d_dgrad(dy, weight, ctx.stride, ctx.pad, h, w, x.shape[1], inv_sigma)
         if ctx.needs_input_grad[1]:
-            dw = ops.conv2d_wgrad(x, dy, cin, cout, kh, kw, ctx.stride, ctx.pad)
+            dw = ops.conv2d_wgrad(x, dy, cin, cout, kh, kw, ctx.stride, ctx.pad)   # d/d(w * inv_sigma)
+            if inv_sigma is not None:
+                # W_eff = W / sigma, sigma = u^T W v (u, v constants):
+                # dL/dW = G / sigma - (<G, W> / sigma^2) u v^T
+                c = (dw * weight).sum() * inv_sigma * inv_sigma
+                dw.mul_(inv_sigma)
+                dw.view(cout, -1).addr_(u * (-c), v)
         if ctx.has_bias and ctx.needs_input_grad[2]:
             db = ops.channel_sum(dy)[:cout]   # over the padded channels, then the logical ones
         if ctx.has_res and ctx.needs_input_grad[3]:
             dres = dy
-        return dx, dw, db, dres, None, None, None, None
+        return dx, dw, db, dres, None, None, None, None, None, None, None
 
 
-def conv2d_dgrad(dy, weight, stride, pad, h, w, cin_p):
+def conv2d_dgrad(dy, weight, stride, pad, h, w, cin_p, inv_sigma=None):
     """Data gradient of conv2d as a stride-1 convolution of dy with the transposed,
     spatially flipped filter.  A stride-2 forward is handled by zero-insertion."""
     cout, cin, kh, kw = weight.shape
     cout_p = dy.shape[1]
-    wt = ops.pack_conv_weight(weight, None, cin_p=cout_p, transpose_flip=True)   # [Cin, KH, KW, Cout_p]
+    wt = _packed_weight(weight, cout_p, True, inv_sigma)   # [Cin, KH, KW, Cout_p]
     if stride != 1:
         n, _, ho, wo = dy.shape
         dh = (ho - 1) * stride + 1 + (h + 2 * pad - kh) % stride
@@ -156,14 +205,16 @@ def conv2d_dgrad(dy, weight, stride, pad, h, w, cin_p):
     return ops.conv2d_fprop(dy, wt, cin, kh, kw, 1, kh - 1 - pad, cout_p=cin_p)
 
 
-def conv2d(x, weight, bias=None, residual=None, stride=1, pad=0, act=ops.ACT_NONE, stats_mode=None):
-    """stats_mode='batch' | 'instance': the epilogue also accumulates the per-channel sum / sum of squares
+def conv2d(x, weight, bias=None, residual=None, stride=1, pad=0, act=ops.ACT_NONE, stats_mode=None, sn=None):
+    """sn = (inv_sigma, u, v) from spectral_sigma() when `weight` is a spectrally normalised
+    layer's weight_orig.  stats_mode='batch' | 'instance': the epilogue also accumulates the per-channel sum / sum of squares
     of the stored output, attached to the result for the consuming norm layer."""
     stats = None
     if stats_mode in ('batch', 'instance'):
         g = x.shape[0] if stats_mode == 'instance' else 1
         stats = torch.zeros((2, g, weight.shape[0]), dtype=torch.float32, device=x.device)
-    y = _Conv2d.apply(x, weight, bias, residual, stride, pad, act, stats)
+    inv_sigma, u, v = sn if sn is not None else (None, None, None)
+    y = _Conv2d.apply(x, weight, bias, residual, stride, pad, act, stats, inv_sigma, u, v)
     if stats is not None:
         n, _, ho, wo = y.shape
         y._imx_stats = (stats, stats_mode == 'instance', ho * wo if stats_mode == 'instance' else n * ho * wo)
@@ -314,12 +365,13 @@ def spade_norm_act(x, ns, gamma, beta, act):
                                ns.use_batch_stats, sync)
 
 
-def spade_gb_fused(hidden, w_gamma, w_beta, b_gamma, b_beta, x, ns, act, pad):
+def spade_gb_fused(hidden, w_gamma, w_beta, b_gamma, b_beta, x, ns, act, pad, inv_sigma_gamma=None,
+                   inv_sigma_beta=None):
     """No-grad fast path: the gamma/beta projection conv applies the modulation in its
     epilogue, so gamma and beta never reach HBM."""
     mean, rstd, _ = compute_norm_stats(x, ns)
     c, ch, kh, kw = w_gamma.shape
-    wgb = ops.pack_spade_gb_weight(w_gamma, w_beta, ch_p=hidden.shape[1])
+    wgb = ops.pack_spade_gb_weight(w_gamma, w_beta, inv_sigma_gamma, inv_sigma_beta, ch_p=hidden.shape[1])
     w = ns.weight.float() if ns.weight is not None else None
     b = ns.bias.float() if ns.bias is not None else None
     if w is None and b is not None:

@@ -198,14 +198,19 @@ class SpatiallyAdaptiveNorm(nn.Module):
         return hidden, mlp[-1].layers['conv'], None
 
     def _gamma_beta_weights(self, i):
-        """fp32 filters / biases of gamma and beta (joint projection: the two halves)."""
+        """Filters / biases of gamma and beta: (wg, wb, bg, bb, sng, snb, conv).  Separate
+        projections go through the fused spectral-norm path (weight_orig + 1/sigma); a joint
+        projection is split into its two halves of the effective weight."""
         _, conv_g, conv_b = self._projection(i)
         c = self.num_features
         if conv_b is not None:
-            return conv_g.effective_weight(), conv_b.effective_weight(), conv_g.bias, conv_b.bias, conv_g
+            wg, sng = conv_g.weight_for_kernel()
+            wb, snb = conv_b.weight_for_kernel()
+            return wg, wb, conv_g.bias, conv_b.bias, sng, snb, conv_g
         w = conv_g.effective_weight()
         bias = conv_g.bias
-        return w[:c], w[c:], (None if bias is None else bias[:c]), (None if bias is None else bias[c:]), conv_g
+        return (w[:c], w[c:], (None if bias is None else bias[:c]), (None if bias is None else bias[c:]),
+                None, None, conv_g)
 
     def forward_fused(self, x, *cond_inputs, act=ops.ACT_NONE, **kwargs):
         x = NF.to_nhwc(x)
@@ -223,7 +228,7 @@ class SpatiallyAdaptiveNorm(nn.Module):
             label = self._resized_cond(cond_inputs[i], h, w)
             hidden_block, _, _ = self._projection(i)
             hidden = hidden_block(label) if hidden_block is not None else NF.to_nhwc(label)
-            wg, wb, bg, bb, conv = self._gamma_beta_weights(i)
+            wg, wb, bg, bb, sng, snb, conv = self._gamma_beta_weights(i)
             conv._check_supported()
             pad = conv.padding[0]
             fuse = (not torch.is_grad_enabled()) and conv.stride[0] == 1 and \
@@ -234,10 +239,11 @@ class SpatiallyAdaptiveNorm(nn.Module):
                     mean, rstd = _IdentityStats.get(c, x.device)
                     step_ns = NF.NormState('batch', None, None, mean, torch.ones_like(rstd) - 1e-5, 0.1, 1e-5,
                                            False, True)
-                out = NF.spade_gb_fused(hidden, wg, wb, bg, bb, out, step_ns, step_act, pad)
+                out = NF.spade_gb_fused(hidden, wg, wb, bg, bb, out, step_ns, step_act, pad,
+                                        None if sng is None else sng[0], None if snb is None else snb[0])
             else:
-                gamma = NF.conv2d(hidden, wg, bg, None, 1, pad)
-                beta = NF.conv2d(hidden, wb, bb, None, 1, pad)
+                gamma = NF.conv2d(hidden, wg, bg, None, 1, pad, sn=sng)
+                beta = NF.conv2d(hidden, wb, bb, None, 1, pad, sn=snb)
                 if step_ns is None:
                     out = _modulate_only(out, gamma, beta, step_act)
                 else:

@@ -22,6 +22,7 @@ from types import SimpleNamespace
 import torch
 from torch import nn
 from torch.nn import functional as F
+from torch.nn.utils.spectral_norm import SpectralNorm
 
 from .. import functional as NF
 from .. import ops
@@ -46,10 +47,27 @@ class Conv2d(nn.Conv2d):
                 self.padding[0] != self.padding[1] or self.stride[0] not in (1, 2):
             raise NotImplementedError('native Conv2d supports square kernels, stride 1 or 2, symmetric padding')
 
+    def spectral_hook(self):
+        """torch's SpectralNorm hook on `weight` (dim 0), if this layer has one."""
+        for hook in self._forward_pre_hooks.values():
+            if isinstance(hook, SpectralNorm) and hook.name == 'weight' and hook.dim == 0:
+                return hook
+        return None
+
+    def weight_for_kernel(self):
+        """(filter to pack, sn): for a spectrally normalised layer the filter is weight_orig and
+        sn = (1/sigma, u, v) after this forward's power iteration (the division is folded into the
+        repack kernel and the backward handles sigma); otherwise (effective weight, None)."""
+        hook = self.spectral_hook()
+        if hook is None:
+            return self.effective_weight(), None
+        return self.weight_orig, NF.spectral_sigma(self.weight_orig, self.weight_u, self.weight_v, self.training,
+                                                   hook.n_power_iterations, hook.eps)
+
     def native_forward(self, x, act=ops.ACT_NONE, residual=None, stats_mode=None):
         self._check_supported()
-        weight = self.effective_weight()
-        return NF.conv2d(x, weight, self.bias, residual, self.stride[0], self.padding[0], act, stats_mode)
+        weight, sn = self.weight_for_kernel()
+        return NF.conv2d(x, weight, self.bias, residual, self.stride[0], self.padding[0], act, stats_mode, sn)
 
     def forward(self, x):
         return self.native_forward(NF.to_nhwc(x))
