@@ -36,6 +36,7 @@ def parse_args():
     ap.add_argument('--config', default=CONFIG_NAME)
     ap.add_argument('--batch', type=int, default=None, help='per-GPU batch override (debugging only)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-clocks', action='store_true', help='do not spawn the nvidia-smi clock sampler (ncu runs)')
     ap.add_argument('--one-step', action='store_true',
                     help='profiling aid: run exactly one training iteration (after --warmup) and exit, '
                          'so that an ncu launch list covers one step and nothing else')
@@ -309,7 +310,8 @@ def run_ours(args):
     sampler = ClockSampler(local_rank)
     # ---- timed region 1: inputs resident in HBM ----
     barrier()
-    sampler.start()
+    if not args.no_clocks:
+        sampler.start()
     lib.launches = 0
     start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     start.record()

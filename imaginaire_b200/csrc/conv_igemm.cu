@@ -290,13 +290,12 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 #pragma unroll
                             for (int j = 0; j < 32; ++j) f[j] = valid ? f[j] : 0.0f;
                         }
-                        float s_mine = 0.0f, q_mine = 0.0f;
+                        // Column sums over the warp's 32 rows: lane L ends up with channel nb + L.
+                        float q2[32];
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            const float s = imx::warp_sum(f[j]);
-                            const float qq = imx::warp_sum(f[j] * f[j]);
-                            if (lane == j) { s_mine = s; q_mine = qq; }
-                        }
+                        for (int j = 0; j < 32; ++j) q2[j] = f[j] * f[j];
+                        const float s_mine = imx::warp_transpose_sum32(f, lane);
+                        const float q_mine = imx::warp_transpose_sum32(q2, lane);
                         if (stats_in_smem) {
                             if (nb + lane < p.Cout) {
                                 atomicAdd(s_stats + nb + lane, s_mine);

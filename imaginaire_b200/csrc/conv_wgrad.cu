@@ -285,13 +285,22 @@ int make_plan(Plan& pl, int N, int H, int W, int Cin_p, int Cout_p, int KH, int 
     pl.ci_tiles = (Cin_p + pl.BN - 1) / pl.BN;
     const int T = 256 / pl.BN;
     const long base_units = (long)pl.co_tiles * pl.ci_tiles * ((KH * KW + T - 1) / T);
-    // enough units for ~2 waves, but keep at least 8 K steps per unit
-    long splits = (2L * imx::kNumSMs + base_units - 1) / base_units;
+    // Split the pixel reduction so that the units fill whole waves of the 148 persistent CTAs
+    // (a last wave that is mostly empty costs a full unit time), keeping >= 8 K steps per unit.
     long max_splits = ptiles / 8 > 1 ? ptiles / 8 : 1;
-    if (splits > max_splits) splits = max_splits;
-    if (splits < 1) splits = 1;
-    // no empty splits: per = ceil(ptiles / splits) must leave work for the last split
-    while (splits > 1 && (splits - 1) * ((ptiles + splits - 1) / splits) >= ptiles) --splits;
+    if (max_splits > 64) max_splits = 64;
+    long splits = 1;
+    double best = -1.0;
+    for (long sp = 1; sp <= max_splits; ++sp) {
+        if (sp > 1 && (sp - 1) * ((ptiles + sp - 1) / sp) >= ptiles) continue;   // would leave an empty split
+        const long units = base_units * sp;
+        const double waves = (double)units / imx::kNumSMs;
+        double eff = waves / (double)((units + imx::kNumSMs - 1) / imx::kNumSMs);
+        if (waves < 1.0) eff = waves;                       // not even one full wave
+        // more splits = more partial-sum traffic: require a clear gain to go further
+        const double score = eff - 0.01 * (double)sp;
+        if (score > best + 1e-9) { best = score; splits = sp; }
+    }
     pl.splits = (int)splits;
     pl.ws_floats = splits * KH * KW * (long)pl.co_tiles * BM * (long)pl.ci_tiles * pl.BN;
     return IMX_OK;

@@ -56,4 +56,21 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
+// Each lane holds v[0..31] (one value per column); returns in lane L the sum over all 32 lanes
+// of column L.  Recursive halving: 31 shuffles instead of 32 x 5 for 32 separate butterflies.
+// v is clobbered.  All indices are compile-time after unrolling, so v stays in registers.
+__device__ __forceinline__ float warp_transpose_sum32(float (&v)[32], int lane) {
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+        const bool upper = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < off; ++i) {
+            const float send = upper ? v[i] : v[i + off];
+            const float keep = upper ? v[i + off] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
+    }
+    return v[0];
+}
+
 }  // namespace imx
