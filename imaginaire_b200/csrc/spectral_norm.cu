@@ -1,0 +1,233 @@
+// Spectral-norm weight preparation.
+//
+// ref: torch.nn.utils.spectral_norm as configured by imaginaire/layers/weight_norm.py:85
+//      (dim 0, one power iteration per training-mode forward, eps 1e-12) and the EMA-side
+//      recompute imaginaire/utils/model_average.py:183-197.
+//
+// The reference's hook runs ~16 small ATen / cuBLAS launches per layer per forward (two
+// GEMVs, two normalisations, clones, a third GEMV + dot for sigma, a full W / sigma
+// materialisation) and autograd adds ~8 more in the backward.  Here one forward is four
+// launches that read W twice, and the backward is two:
+//   t = W^T u (partial sums over row slices) -> v = t / max(|t|, eps)
+//   s = W v                                   -> u = s / max(|s|, eps), sigma = u . s
+// 1/sigma is then folded into the bf16 repack (imx_pack_conv_weight_bf16) and
+//   dL/dW = G / sigma - (<G, W> / sigma^2) u v^T          (G = dL/d(W / sigma))
+// is applied in place on the fp32 weight gradient.
+// HBM-bound: 2 reads of W (4 B / element each) forward; read G, W + read/write G backward.
+#include "imx_common.cuh"
+#include "../../include/imx.h"
+
+namespace {
+
+constexpr int kT = 256;
+
+// partial[s][c] = sum_{r in slice s} W[r][c] * u[r];  grid (ceil(C / (kT*4)), S)
+__global__ void __launch_bounds__(kT)
+sn_wt_u_kernel(const float* __restrict__ W, const float* __restrict__ u, float* __restrict__ partial,
+               int R, int C, int rows_per_slice) {
+    const int c0 = (blockIdx.x * kT + threadIdx.x) * 4;
+    const int r0 = blockIdx.y * rows_per_slice;
+    const int r1 = min(R, r0 + rows_per_slice);
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    if (c0 + 3 < C && (C & 3) == 0) {
+        const float* p = W + (size_t)r0 * C + c0;
+#pragma unroll 4
+        for (int r = r0; r < r1; ++r, p += C) {
+            const float4 w = __ldg(reinterpret_cast<const float4*>(p));
+            const float ur = __ldg(u + r);
+            a0 = fmaf(w.x, ur, a0); a1 = fmaf(w.y, ur, a1); a2 = fmaf(w.z, ur, a2); a3 = fmaf(w.w, ur, a3);
+        }
+    } else if (c0 < C) {
+        for (int r = r0; r < r1; ++r) {
+            const float ur = __ldg(u + r);
+            const float* p = W + (size_t)r * C + c0;
+            a0 = fmaf(__ldg(p), ur, a0);
+            if (c0 + 1 < C) a1 = fmaf(__ldg(p + 1), ur, a1);
+            if (c0 + 2 < C) a2 = fmaf(__ldg(p + 2), ur, a2);
+            if (c0 + 3 < C) a3 = fmaf(__ldg(p + 3), ur, a3);
+        }
+    }
+    float* o = partial + (size_t)blockIdx.y * C + c0;
+    if (c0 < C) o[0] = a0;
+    if (c0 + 1 < C) o[1] = a1;
+    if (c0 + 2 < C) o[2] = a2;
+    if (c0 + 3 < C) o[3] = a3;
+}
+
+__device__ __forceinline__ float block_sum(float v, float* sh) {
+    v = imx::warp_sum(v);
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (lane == 0) sh[w] = v;
+    __syncthreads();
+    float t = (threadIdx.x < (blockDim.x >> 5)) ? sh[threadIdx.x] : 0.0f;
+    if (w == 0) t = imx::warp_sum(t);
+    if (threadIdx.x == 0) sh[0] = t;
+    __syncthreads();
+    t = sh[0];
+    __syncthreads();
+    return t;
+}
+
+// One block: t = sum of the slices, v = t / max(|t|, eps)  (written to v and v_copy)
+__global__ void __launch_bounds__(1024)
+sn_finish_v_kernel(const float* __restrict__ partial, float* __restrict__ v, float* __restrict__ v_copy,
+                   int C, int S, float eps) {
+    __shared__ float sh[32];
+    float sq = 0.0f;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        float t = 0.0f;
+        for (int s = 0; s < S; ++s) t += partial[(size_t)s * C + c];
+        v[c] = t;
+        sq = fmaf(t, t, sq);
+    }
+    const float nrm = sqrtf(block_sum(sq, sh));
+    const float inv = 1.0f / fmaxf(nrm, eps);
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        const float t = v[c] * inv;
+        v[c] = t;
+        if (v_copy) v_copy[c] = t;
+    }
+}
+
+// s[r] = W[r,:] . v; one warp per row; grid ceil(R / 8) blocks of 8 warps
+__global__ void __launch_bounds__(kT)
+sn_w_v_kernel(const float* __restrict__ W, const float* __restrict__ v, float* __restrict__ s, int R, int C) {
+    const int r = blockIdx.x * (kT / 32) + (threadIdx.x >> 5);
+    if (r >= R) return;
+    const int lane = threadIdx.x & 31;
+    const float* p = W + (size_t)r * C;
+    float acc = 0.0f;
+    if ((C & 3) == 0) {
+        for (int c = lane * 4; c < C; c += 128) {
+            const float4 w = __ldg(reinterpret_cast<const float4*>(p + c));
+            const float4 x = __ldg(reinterpret_cast<const float4*>(v + c));
+            acc = fmaf(w.x, x.x, acc); acc = fmaf(w.y, x.y, acc); acc = fmaf(w.z, x.z, acc); acc = fmaf(w.w, x.w, acc);
+        }
+    } else {
+        for (int c = lane; c < C; c += 32) acc = fmaf(__ldg(p + c), __ldg(v + c), acc);
+    }
+    acc = imx::warp_sum(acc);
+    if (lane == 0) s[r] = acc;
+}
+
+// One block.  update_u: u = s / max(|s|, eps).  sigma = u . s; writes 1/sigma, u_copy (and v_copy
+// when the power iteration did not run).
+__global__ void __launch_bounds__(1024)
+sn_finish_u_kernel(const float* __restrict__ s, float* __restrict__ u, float* __restrict__ u_copy,
+                   const float* __restrict__ v, float* __restrict__ v_copy, float* __restrict__ inv_sigma,
+                   int R, int C, float eps, int update_u) {
+    __shared__ float sh[32];
+    if (update_u) {
+        float sq = 0.0f;
+        for (int r = threadIdx.x; r < R; r += blockDim.x) sq = fmaf(s[r], s[r], sq);
+        const float inv = 1.0f / fmaxf(sqrtf(block_sum(sq, sh)), eps);
+        for (int r = threadIdx.x; r < R; r += blockDim.x) u[r] = s[r] * inv;
+        __syncthreads();
+    }
+    float d = 0.0f;
+    for (int r = threadIdx.x; r < R; r += blockDim.x) {
+        const float ur = u[r];
+        d = fmaf(ur, s[r], d);
+        if (u_copy) u_copy[r] = ur;
+    }
+    const float sigma = block_sum(d, sh);
+    if (threadIdx.x == 0) *inv_sigma = 1.0f / sigma;
+    if (!update_u && v_copy)
+        for (int c = threadIdx.x; c < C; c += blockDim.x) v_copy[c] = v[c];
+}
+
+// dot += sum G * W   (fp32 atomics; caller zero-fills)
+__global__ void __launch_bounds__(kT)
+sn_dot_kernel(const float* __restrict__ G, const float* __restrict__ W, float* __restrict__ dot, long n) {
+    __shared__ float sh[32];
+    float acc = 0.0f;
+    const long stride = (long)gridDim.x * kT * 4;
+    for (long i = ((long)blockIdx.x * kT + threadIdx.x) * 4; i < n; i += stride) {
+        if (i + 3 < n && (n & 3) == 0) {
+            const float4 g = __ldg(reinterpret_cast<const float4*>(G + i));
+            const float4 w = __ldg(reinterpret_cast<const float4*>(W + i));
+            acc = fmaf(g.x, w.x, acc); acc = fmaf(g.y, w.y, acc); acc = fmaf(g.z, w.z, acc); acc = fmaf(g.w, w.w, acc);
+        } else {
+            for (long j = i; j < n && j < i + 4; ++j) acc = fmaf(G[j], W[j], acc);
+        }
+    }
+    acc = block_sum(acc, sh);
+    if (threadIdx.x == 0) atomicAdd(dot, acc);
+}
+
+// G[r][c] = G[r][c] * inv_sigma - (dot * inv_sigma^2) * u[r] * v[c]
+__global__ void __launch_bounds__(kT)
+sn_grad_kernel(float* __restrict__ G, const float* __restrict__ u, const float* __restrict__ v,
+               const float* __restrict__ inv_sigma, const float* __restrict__ dot, int R, int C) {
+    const float is = __ldg(inv_sigma);
+    const float coef = __ldg(dot) * is * is;
+    const long n = (long)R * C;
+    for (long i = (long)blockIdx.x * kT + threadIdx.x; i < n; i += (long)gridDim.x * kT) {
+        const int r = (int)(i / C), c = (int)(i - (long)r * C);
+        G[i] = fmaf(G[i], is, -coef * __ldg(u + r) * __ldg(v + c));
+    }
+}
+
+inline int slices_for(int R, int C) {
+    const int col_blocks = (C + kT * 4 - 1) / (kT * 4);
+    int s = (2 * imx::kNumSMs + col_blocks - 1) / col_blocks;
+    if (s > R / 8) s = R / 8;
+    if (s < 1) s = 1;
+    if (s > 64) s = 64;
+    return s;
+}
+
+}  // namespace
+
+extern "C" int64_t imx_spectral_norm_scratch_bytes(int R, int C) {
+    if (R <= 0 || C <= 0) return -1;
+    // partial sums of W^T u over the row slices, then s = W v
+    return ((int64_t)slices_for(R, C) * C + R + 64) * 4;
+}
+
+extern "C" int imx_spectral_norm_sigma_f32(const float* W, float* u, float* v, float* u_copy, float* v_copy,
+                                           float* inv_sigma, void* scratch, int64_t scratch_bytes,
+                                           int R, int C, int n_power_iterations, float eps,
+                                           imx_stream_t stream) {
+    IMX_REQUIRE(R > 0 && C > 0, "spectral_norm_sigma: bad size");
+    IMX_REQUIRE(W && u && v && inv_sigma && scratch, "spectral_norm_sigma: null pointer");
+    IMX_REQUIRE(n_power_iterations >= 0, "spectral_norm_sigma: negative iteration count");
+    IMX_REQUIRE(scratch_bytes >= imx_spectral_norm_scratch_bytes(R, C), "spectral_norm_sigma: scratch too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int S = slices_for(R, C);
+    float* partial = reinterpret_cast<float*>(scratch);
+    float* s = partial + (size_t)S * C;
+    const int rows_per_slice = (R + S - 1) / S;
+    const dim3 g1((C + kT * 4 - 1) / (kT * 4), S);
+    for (int it = 0; it < n_power_iterations; ++it) {
+        sn_wt_u_kernel<<<g1, kT, 0, st>>>(W, u, partial, R, C, rows_per_slice);
+        sn_finish_v_kernel<<<1, 1024, 0, st>>>(partial, v, v_copy, C, S, eps);
+        sn_w_v_kernel<<<(R + kT / 32 - 1) / (kT / 32), kT, 0, st>>>(W, v, s, R, C);
+        const bool last = it == n_power_iterations - 1;
+        sn_finish_u_kernel<<<1, 1024, 0, st>>>(s, u, last ? u_copy : nullptr, v, nullptr, inv_sigma, R, C, eps, 1);
+    }
+    if (n_power_iterations == 0) {
+        sn_w_v_kernel<<<(R + kT / 32 - 1) / (kT / 32), kT, 0, st>>>(W, v, s, R, C);
+        sn_finish_u_kernel<<<1, 1024, 0, st>>>(s, u, u_copy, v, v_copy, inv_sigma, R, C, eps, 0);
+    }
+    return imx::check_launch("spectral_norm_sigma");
+}
+
+extern "C" int imx_spectral_norm_weight_grad_f32(float* G, const float* W, const float* u, const float* v,
+                                                 const float* inv_sigma, float* dot_scratch, int R, int C,
+                                                 imx_stream_t stream) {
+    IMX_REQUIRE(R > 0 && C > 0, "spectral_norm_weight_grad: bad size");
+    IMX_REQUIRE(G && W && u && v && inv_sigma && dot_scratch, "spectral_norm_weight_grad: null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaError_t e = cudaMemsetAsync(dot_scratch, 0, sizeof(float), st);
+    if (e != cudaSuccess) return imx::set_error((int)e, "spectral_norm_weight_grad: memset: %s", cudaGetErrorString(e));
+    const long n = (long)R * C;
+    long blocks = (n / 4 + kT - 1) / kT;
+    if (blocks > 4L * imx::kNumSMs) blocks = 4L * imx::kNumSMs;
+    if (blocks < 1) blocks = 1;
+    sn_dot_kernel<<<(int)blocks, kT, 0, st>>>(G, W, dot_scratch, n);
+    long b2 = (n + kT - 1) / kT;
+    if (b2 > 8L * imx::kNumSMs) b2 = 8L * imx::kNumSMs;
+    sn_grad_kernel<<<(int)b2, kT, 0, st>>>(G, u, v, inv_sigma, dot_scratch, R, C);
+    return imx::check_launch("spectral_norm_weight_grad");
+}

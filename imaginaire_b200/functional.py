@@ -124,21 +124,13 @@ def spectral_sigma(weight_orig, u_buf, v_buf, training, n_power_iterations=1, ep
     weight norm, imaginaire/layers/weight_norm.py:85): in training mode run the power iteration
     in place on the module's u / v buffers (no autograd), then sigma = u^T W v.  Returns
     (1/sigma as a 1-element tensor, u copy, v copy); the copies are what autograd may keep,
-    because the buffers change again on the next forward.  W v of the last iteration is reused
-    for sigma (torch recomputes the identical product), so the filter is read twice, not three
-    times, and W / sigma is never materialised: the division happens inside the repack kernel."""
-    mat = weight_orig.detach().reshape(weight_orig.shape[0], -1)
+    because the buffers change again on the next forward.  Four launches of
+    csrc/spectral_norm.cu instead of the hook's ~16 ATen / cuBLAS calls: W v of the last
+    iteration is reused for sigma (torch recomputes the identical product), so the filter is read
+    twice, and W / sigma is never materialised: the division happens inside the repack kernel."""
     with torch.no_grad():
-        wv = None
-        if training:
-            for _ in range(n_power_iterations):
-                v_buf.copy_(torch.nn.functional.normalize(torch.mv(mat.t(), u_buf), dim=0, eps=eps))
-                wv = torch.mv(mat, v_buf)
-                u_buf.copy_(torch.nn.functional.normalize(wv, dim=0, eps=eps))
-        if wv is None:
-            wv = torch.mv(mat, v_buf)
-        sigma = torch.dot(u_buf, wv)
-        return (1.0 / sigma).reshape(1), u_buf.clone(), v_buf.clone()
+        return ops.spectral_norm_sigma(weight_orig.detach(), u_buf, v_buf,
+                                       n_power_iterations if training else 0, eps)
 
 
 class _Conv2d(torch.autograd.Function):
@@ -177,9 +169,7 @@ class _Conv2d(torch.autograd.Function):
             if inv_sigma is not None:
                 # W_eff = W / sigma, sigma = u^T W v (u, v constants):
                 # dL/dW = G / sigma - (<G, W> / sigma^2) u v^T
-                c = (dw * weight).sum() * inv_sigma * inv_sigma
-                dw.mul_(inv_sigma)
-                dw.view(cout, -1).addr_(u * (-c), v)
+                ops.spectral_norm_weight_grad_(dw, weight.detach(), u, v, inv_sigma)
         if ctx.has_bias and ctx.needs_input_grad[2]:
             db = ops.channel_sum(dy)[:cout]   # over the padded channels, then the logical ones
         if ctx.has_res and ctx.needs_input_grad[3]:

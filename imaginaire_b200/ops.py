@@ -186,6 +186,35 @@ def pack_spade_gb_weight(w_gamma, w_beta, inv_sigma_gamma=None, inv_sigma_beta=N
     return out
 
 
+def spectral_norm_sigma(weight, u, v, n_power_iterations, eps):
+    """In-place power iteration on the buffers u, v and sigma of `weight` viewed as
+    [Cout, -1].  Returns (inv_sigma (1,), u copy, v copy)."""
+    _req_cuda(weight, u, v)
+    _req_f32c(weight, 'weight'); _req_f32c(u, 'u'); _req_f32c(v, 'v')
+    r = weight.shape[0]
+    c = weight.numel() // r
+    lib = _C.lib()
+    nbytes = lib.raw('imx_spectral_norm_scratch_bytes')(r, c)
+    scratch = torch.empty((int(nbytes),), dtype=torch.uint8, device=weight.device)
+    out = torch.empty((1 + r + c,), dtype=torch.float32, device=weight.device)
+    inv_sigma, u_copy, v_copy = out[:1], out[1:1 + r], out[1 + r:]
+    lib.call('imx_spectral_norm_sigma_f32', _ptr(weight), _ptr(u), _ptr(v), _ptr(u_copy), _ptr(v_copy),
+             _ptr(inv_sigma), _ptr(scratch), int(nbytes), r, c, int(n_power_iterations), float(eps), _stream())
+    return inv_sigma, u_copy, v_copy
+
+
+def spectral_norm_weight_grad_(grad, weight, u, v, inv_sigma):
+    """grad (= dL/d(W/sigma), fp32, same shape as weight) -> dL/dW, in place."""
+    _req_cuda(grad, weight)
+    _req_f32c(grad, 'grad'); _req_f32c(weight, 'weight')
+    r = weight.shape[0]
+    c = weight.numel() // r
+    dot = torch.empty((1,), dtype=torch.float32, device=grad.device)
+    _C.lib().call('imx_spectral_norm_weight_grad_f32', _ptr(grad), _ptr(weight), _ptr(u), _ptr(v), _ptr(inv_sigma),
+                  _ptr(dot), r, c, _stream())
+    return grad
+
+
 # ------------------------------------------------------------- statistics
 
 def bn_stats(x, per_instance=False):

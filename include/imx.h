@@ -114,6 +114,26 @@ IMX_API int imx_pack_conv_weight_bf16(const float* w, const float* inv_sigma, im
                               int Cout, int Cin, int KH, int KW, int Cin_p,
                               int transpose_flip, imx_stream_t stream);
 
+/* Spectral norm of a filter viewed as W[R][C] (R = Cout, C = Cin*KH*KW), fp32, with
+ * torch.nn.utils.spectral_norm's semantics: n_power_iterations times
+ * v = normalize(W^T u), u = normalize(W v) in place on the module buffers u[R], v[C] (0 in
+ * eval mode), then sigma = u . (W v).  Writes 1/sigma to inv_sigma[0] and copies of the
+ * final u, v to u_copy / v_copy (may be NULL) for the backward.  scratch: caller-owned, at
+ * least imx_spectral_norm_scratch_bytes(R, C) bytes, need not be initialised.
+ * ref: spectral_norm(conv) via imaginaire/layers/weight_norm.py:85; sigma recompute
+ *      imaginaire/utils/model_average.py:183-197 */
+IMX_API int imx_spectral_norm_sigma_f32(const float* W, float* u, float* v, float* u_copy, float* v_copy,
+                                        float* inv_sigma, void* scratch, int64_t scratch_bytes,
+                                        int R, int C, int n_power_iterations, float eps,
+                                        imx_stream_t stream);
+IMX_API int64_t imx_spectral_norm_scratch_bytes(int R, int C);
+
+/* Backward of W_eff = W / sigma(W) with u, v constant: in place on G = dL/dW_eff,
+ * G <- G / sigma - (<G, W> / sigma^2) u v^T  (= dL/dW).  dot_scratch: one float. */
+IMX_API int imx_spectral_norm_weight_grad_f32(float* G, const float* W, const float* u, const float* v,
+                                              const float* inv_sigma, float* dot_scratch, int R, int C,
+                                              imx_stream_t stream);
+
 /* ----------------------------------------------- normalisation + SPADE -- */
 
 /* Per-channel sums over an NHWC bf16 tensor: sum[g*C+c], sumsq[g*C+c] (fp32),

@@ -280,3 +280,38 @@ def test_spade_gb_fused_equals_materialised():
     xh = (x - m) / torch.sqrt(v + 1e-5) * nw.view(1, -1, 1, 1) + nb.view(1, -1, 1, 1)
     ref = so.leaky_relu(xh * (1 + gamma) + beta)
     assert H.rel_err(y.float().cpu(), ref) < 6e-3
+
+
+# ------------------------------------------------------------ spectral norm
+
+@pytest.mark.parametrize('shape', [(64, 35, 5, 5), (128, 128, 3, 3), (2048, 256, 3, 3), (8, 130, 1, 1), (3, 256, 5, 5)])
+@pytest.mark.parametrize('training', [True, False])
+def test_spectral_norm_sigma_vs_oracle(shape, training):
+    """Power iteration + sigma against the oracle's restatement of torch's spectral_norm."""
+    from imaginaire_b200 import ops
+    g = torch.Generator().manual_seed(51)
+    w = torch.randn(*shape, generator=g) * 0.1
+    u = F.normalize(torch.randn(shape[0], generator=g), dim=0)
+    v = F.normalize(torch.randn(w.numel() // shape[0], generator=g), dim=0)
+    sd = {'weight_orig': w.clone(), 'weight_u': u.clone(), 'weight_v': v.clone()}
+    w_eff = so.effective_weight(sd, '', training)            # updates sd's u, v when training
+    sigma_ref = float((w.flatten()[0] / w_eff.flatten()[0]))
+    ug, vg = u.to(DEV), v.to(DEV)
+    inv_sigma, uc, vc = ops.spectral_norm_sigma(w.to(DEV), ug, vg, 1 if training else 0, 1e-12)
+    assert abs(1.0 / float(inv_sigma) - sigma_ref) < 1e-4 * abs(sigma_ref)
+    assert H.rel_err(ug.cpu(), sd['weight_u']) < 1e-4 and H.rel_err(vg.cpu(), sd['weight_v']) < 1e-4
+    assert torch.equal(uc, ug) and torch.equal(vc, vg)        # the copies autograd keeps
+
+
+def test_spectral_norm_weight_grad_vs_autograd():
+    from imaginaire_b200 import ops
+    g = torch.Generator().manual_seed(52)
+    w = (torch.randn(96, 40, 3, 3, generator=g) * 0.1).requires_grad_(True)
+    u = F.normalize(torch.randn(96, generator=g), dim=0)
+    v = F.normalize(torch.randn(360, generator=g), dim=0)
+    grad_eff = torch.randn(96, 40, 3, 3, generator=g)
+    sigma = torch.dot(u, torch.mv(w.reshape(96, -1), v))
+    (w / sigma).backward(grad_eff)
+    out = ops.spectral_norm_weight_grad_(grad_eff.clone().to(DEV), w.detach().to(DEV), u.to(DEV), v.to(DEV),
+                                         (1.0 / sigma.detach()).reshape(1).to(DEV))
+    assert H.rel_err(out.cpu(), w.grad) < 1e-5
