@@ -38,13 +38,18 @@ constexpr int BK = 64;           // channels per K step (128 bytes of bf16: one 
 constexpr int UMMA_K = 16;
 constexpr int kThreads = 256;
 constexpr int kEpiWarp0 = 4;     // first epilogue warp (warp % 4 == TMEM lane quarter)
-constexpr int A_BYTES = BM * BK * 2;
+constexpr int A_TILE_BYTES = BM * BK * 2;
 
-template <int BN> struct Cfg {
+// MT = 128-pixel sub-tiles per CTA tile.  With a narrow channel tile (BN <= 128) one MMA per
+// K step would need more shared-memory fill (A + B bytes per MMA cycle) than L2 sustains, so
+// such layers use MT = 2: one 256-pixel TMA box, two MMAs that share the B tile, two TMEM
+// accumulators per stage.
+template <int BN, int MT> struct Cfg {
+    static constexpr int A_BYTES = MT * A_TILE_BYTES;
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
-    static constexpr int TMEM_COLS = (2 * BN < 32) ? 32 : 2 * BN;
+    static constexpr int STAGES = (196608 / STAGE_BYTES) > 8 ? 8 : (196608 / STAGE_BYTES);
+    static constexpr int TMEM_COLS = (2 * MT * BN < 32) ? 32 : 2 * MT * BN;
     static constexpr int STATS_SMEM_CH = 2048;   // per-CTA statistics accumulators for up to this many channels
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ +
                                       2 * STATS_SMEM_CH * 4;
@@ -81,11 +86,12 @@ __device__ __forceinline__ float act_apply(float v, int act) {
 }
 
 // kMode 0: plain conv epilogue.   kMode 1: SPADE gamma/beta projection + modulation.
-template <int BN, int kMode>
+template <int BN, int kMode, int MT>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                   const ConvArgs p) {
-    using C = Cfg<BN>;
+    using C = Cfg<BN, MT>;
+    constexpr int A_BYTES = C::A_BYTES;
     extern __shared__ uint8_t smem_raw[];
     // 128-byte swizzle atoms must sit on 1024-byte boundaries.
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -172,16 +178,19 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                 const uint32_t aphase = (iter >> 1) & 1;
                 mbar_wait(&tmem_empty[as], aphase ^ 1);
                 tc_fence_after_sync();
-                const uint32_t d_tmem = tmem_base + as * BN;
+                const uint32_t d_tmem = tmem_base + as * (MT * BN);
                 for (int k = 0; k < k_iters; ++k) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after_sync();
-                    const uint64_t da = make_kmajor_sw128_desc(smem_u32(smem_a + stage * A_BYTES));
                     const uint64_t db = make_kmajor_sw128_desc(smem_u32(smem_b + stage * C::B_BYTES));
 #pragma unroll
-                    for (int j = 0; j < BK / UMMA_K; ++j) {
-                        // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in (addr >> 4)
-                        umma_bf16_ss(d_tmem, da + 2 * j, db + 2 * j, idesc, (k | j) != 0);
+                    for (int mt = 0; mt < MT; ++mt) {
+                        const uint64_t da = make_kmajor_sw128_desc(smem_u32(smem_a + stage * A_BYTES + mt * A_TILE_BYTES));
+#pragma unroll
+                        for (int j = 0; j < BK / UMMA_K; ++j) {
+                            // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in (addr >> 4)
+                            umma_bf16_ss(d_tmem + mt * BN, da + 2 * j, db + 2 * j, idesc, (k | j) != 0);
+                        }
                     }
                     umma_commit(&empty_bar[stage]);
                     if (k == k_iters - 1) umma_commit(&tmem_full[as]);
@@ -192,8 +201,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     } else if (warp >= kEpiWarp0) {
         // ===== epilogue =====
         const int q = warp & 3;                 // TMEM lane quarter owned by this warp
-        const int row = q * 32 + lane;          // row of the 128-pixel tile
-        const int pr = row >> p.tw_log2, pc = row & (p.tw - 1);
+        const int row = q * 32 + lane;          // row of a 128-pixel sub-tile
         int iter = 0;
         for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++iter) {
             const int as = iter & 1;
@@ -203,14 +211,18 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             const int img = m_tile / tiles_per_img;
             const int rem = m_tile - img * tiles_per_img;
             const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
-            const int oy = ty * p.th + pr, ox = tx * p.tw + pc;
-            const bool valid = (oy < p.Ho) && (ox < p.Wo);
-            const size_t pix = ((size_t)img * p.Ho + oy) * p.Wo + ox;
             const int n0 = n_tile * BN;
 
             mbar_wait(&tmem_full[as], aphase);
             tc_fence_after_sync();
-            const uint32_t t_acc = tmem_base + as * BN + (static_cast<uint32_t>(q * 32) << 16);
+#pragma unroll 1
+            for (int mt = 0; mt < MT; ++mt) {
+            const int prow = mt * BM + row;         // pixel index inside the CTA tile
+            const int pr = prow >> p.tw_log2, pc = prow & (p.tw - 1);
+            const int oy = ty * p.th + pr, ox = tx * p.tw + pc;
+            const bool valid = (oy < p.Ho) && (ox < p.Wo);
+            const size_t pix = ((size_t)img * p.Ho + oy) * p.Wo + ox;
+            const uint32_t t_acc = tmem_base + as * (MT * BN) + mt * BN + (static_cast<uint32_t>(q * 32) << 16);
 
             if constexpr (kMode == 0) {
 #pragma unroll 1
@@ -218,7 +230,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                     uint32_t v[32];
                     tmem_ld_32x32(t_acc + ch * 32, v);
                     tmem_ld_wait();
-                    if (ch == BN / 32 - 1) {
+                    if (ch == BN / 32 - 1 && mt == MT - 1) {
                         // accumulator fully drained into registers: hand the TMEM stage back
                         tc_fence_before_sync();
                         mbar_arrive(&tmem_empty[as]);
@@ -370,6 +382,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                     }
                 }
             }
+            }   // mt
         }
     }
 
@@ -389,11 +402,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 
 // ------------------------------------------------------------------ host side
 
-template <int BN, int kMode>
+template <int BN, int kMode, int MT = 1>
 int launch(const CUtensorMap& ta, const CUtensorMap& tb, const ConvArgs& a, cudaStream_t stream) {
-    using C = Cfg<BN>;
-    static bool attr_set = false;   // per (BN, mode) instantiation
-    auto kern = conv_igemm_kernel<BN, kMode>;
+    using C = Cfg<BN, MT>;
+    static bool attr_set = false;   // per (BN, mode, MT) instantiation
+    auto kern = conv_igemm_kernel<BN, kMode, MT>;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
         if (e != cudaSuccess) return imx::set_error((int)e, "conv_igemm: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
@@ -406,7 +419,7 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const ConvArgs& a, cuda
 
 // Common geometry + tensor maps.  `rows_b` = number of rows of the packed filter matrix.
 int setup(ConvArgs& a, CUtensorMap& ta, CUtensorMap& tb, const void* x, const void* wpk, int N, int H, int W,
-          int Cin_p, int rows_b, int KH, int KW, int stride, int pad, int BN) {
+          int Cin_p, int rows_b, int KH, int KW, int stride, int pad, int BN, int MT = 1) {
     a.N = N; a.H = H; a.W = W;
     a.KH = KH; a.KW = KW; a.stride = stride; a.pad = pad;
     a.Ho = (H + 2 * pad - KH) / stride + 1;
@@ -415,7 +428,7 @@ int setup(ConvArgs& a, CUtensorMap& ta, CUtensorMap& tb, const void* x, const vo
     // pixel tile: tw = largest power of two <= min(Wo, 128) (at least 8 so th <= 16), th = 128 / tw
     int tw = 128;
     while (tw > 8 && tw > a.Wo) tw >>= 1;
-    a.tw = tw; a.th = BM / tw;
+    a.tw = tw; a.th = MT * BM / tw;
     a.tw_log2 = 0;
     while ((1 << a.tw_log2) < tw) ++a.tw_log2;
     a.tiles_x = (a.Wo + a.tw - 1) / a.tw;
@@ -463,11 +476,27 @@ extern "C" int imx_conv2d_igemm_fprop_bf16(const imx_bf16* x, const imx_bf16* wp
     const int BN = Cout_p > 128 ? 256 : (Cout_p > 64 ? 128 : (Cout_p > 32 ? 64 : 32));
     ConvArgs a{};
     CUtensorMap ta, tb;
-    int rc = setup(a, ta, tb, x, wpk, N, H, W, Cin_p, Cout, KH, KW, stride, pad, BN);
+    // Narrow channel tiles take 256-pixel CTA tiles (two MMAs per B tile) when that still leaves
+    // at least two tiles per SM.
+    int MT = 1;
+    if (BN <= 128) {
+        const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
+        const long tiles256 = (long)N * ((Ho * (long)Wo + 255) / 256) * ((Cout + BN - 1) / BN);
+        if (tiles256 >= 2L * imx::kNumSMs && (stride == 1 || Wo >= 128 || ((256 / (Wo < 128 ? Wo : 128)) - 1) * stride + 1 <= 256))
+            MT = 2;
+    }
+    int rc = setup(a, ta, tb, x, wpk, N, H, W, Cin_p, Cout, KH, KW, stride, pad, BN, MT);
     if (rc) return rc;
     a.Cout = Cout; a.Cout_p = Cout_p; a.flags = flags;
     a.bias = bias; a.residual = residual; a.out = out; a.stats = stats;
     cudaStream_t s = (cudaStream_t)stream;
+    if (MT == 2) {
+        switch (BN) {
+            case 128: return launch<128, 0, 2>(ta, tb, a, s);
+            case 64: return launch<64, 0, 2>(ta, tb, a, s);
+            default: return launch<32, 0, 2>(ta, tb, a, s);
+        }
+    }
     switch (BN) {
         case 256: return launch<256, 0>(ta, tb, a, s);
         case 128: return launch<128, 0>(ta, tb, a, s);

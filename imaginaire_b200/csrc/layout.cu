@@ -126,8 +126,46 @@ __global__ void nhwc_to_nchw_kernel(const __nv_bfloat16* __restrict__ src, float
     }
 }
 
-// packed[co][kh][kw][ci_p] = w[co][ci][kh][kw] * inv_sigma   (transpose_flip == 0)
-// packed[ci][K-1-kh][K-1-kw][co_p] = w[co][ci][kh][kw] * inv_sigma   (transpose_flip != 0)
+// packed[co][tap][ci_p] = w[co][ci][tap] * inv_sigma                       (kFlip == false)
+// packed[ci][T-1-tap][co_p] = w[co][ci][tap] * inv_sigma                   (kFlip == true)
+// A [inner x taps] -> [taps x inner] transpose per row of the packed matrix, staged through
+// shared memory so that the fp32 filter is read in contiguous runs and the bf16 rows are
+// written as contiguous 256-byte segments.  grid = (ceil(Cp / kPackTile), rows).
+constexpr int kPackTile = 128;
+constexpr int kPackMaxTaps = 49;   // up to 7x7; larger kernels take the scalar path
+
+template <bool kFlip>
+__global__ void __launch_bounds__(256)
+pack_weight_tiled_kernel(const float* __restrict__ w, const float* __restrict__ inv_sigma,
+                         __nv_bfloat16* __restrict__ packed, int Cout, int Cin, int taps, int Cp) {
+    extern __shared__ float tile[];   // [kPackTile][taps + 1]
+    const float s = inv_sigma ? __ldg(inv_sigma) : 1.0f;
+    const int r = blockIdx.y;                       // co (plain) or ci (flip)
+    const int i0 = blockIdx.x * kPackTile;          // first inner index of the tile: ci (plain) or co (flip)
+    const int inner = kFlip ? Cout : Cin;
+    const int n_in = min(kPackTile, inner - i0);    // valid inner entries (may be <= 0 for pure padding tiles)
+    const int pitch = taps + 1;
+    if (!kFlip) {
+        // contiguous run w[r][i0 .. i0+n_in)[0..taps)
+        const float* src = w + ((size_t)r * Cin + i0) * taps;
+        for (int e = threadIdx.x; e < n_in * taps; e += 256) tile[(e / taps) * pitch + e % taps] = __ldg(src + e) * s;
+    } else {
+        // for each co in the tile a run of `taps` floats at w[co][r][:]
+        for (int e = threadIdx.x; e < n_in * taps; e += 256) {
+            const int j = e / taps, t = e - j * taps;
+            tile[j * pitch + t] = __ldg(w + ((size_t)(i0 + j) * Cin + r) * taps + t) * s;
+        }
+    }
+    __syncthreads();
+    const int n_out = min(kPackTile, Cp - i0);
+    for (int e = threadIdx.x; e < taps * n_out; e += 256) {
+        const int t = e / n_out, j = e - t * n_out;
+        const float v = j < n_in ? tile[j * pitch + (kFlip ? taps - 1 - t : t)] : 0.0f;
+        packed[((size_t)r * taps + t) * Cp + i0 + j] = __float2bfloat16_rn(v);
+    }
+}
+
+// Scalar fallback for very large kernels.
 __global__ void pack_weight_kernel(const float* __restrict__ w, const float* __restrict__ inv_sigma,
                                    __nv_bfloat16* __restrict__ packed, int Cout, int Cin, int KH, int KW,
                                    int Cp, int transpose_flip) {
@@ -254,7 +292,20 @@ extern "C" int imx_pack_conv_weight_bf16(const float* w, const float* inv_sigma,
     IMX_REQUIRE(Cout > 0 && Cin > 0 && KH > 0 && KW > 0, "pack_conv_weight: bad size");
     IMX_REQUIRE(Cin_p % 8 == 0 && Cin_p >= (transpose_flip ? Cout : Cin),
                 "pack_conv_weight: padded inner dim (%d) too small or not a multiple of 8", Cin_p);
-    const long total = (long)(transpose_flip ? Cin : Cout) * KH * KW * Cin_p;
+    const int taps = KH * KW;
+    const int rows = transpose_flip ? Cin : Cout;
+    if (taps <= kPackMaxTaps && rows <= 65535) {
+        dim3 grid((Cin_p + kPackTile - 1) / kPackTile, rows);
+        const size_t smem = (size_t)kPackTile * (taps + 1) * sizeof(float);
+        if (transpose_flip)
+            pack_weight_tiled_kernel<true><<<grid, 256, smem, (cudaStream_t)stream>>>(
+                w, inv_sigma, reinterpret_cast<__nv_bfloat16*>(packed), Cout, Cin, taps, Cin_p);
+        else
+            pack_weight_tiled_kernel<false><<<grid, 256, smem, (cudaStream_t)stream>>>(
+                w, inv_sigma, reinterpret_cast<__nv_bfloat16*>(packed), Cout, Cin, taps, Cin_p);
+        return imx::check_launch("pack_conv_weight");
+    }
+    const long total = (long)rows * taps * Cin_p;
     pack_weight_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(
         w, inv_sigma, reinterpret_cast<__nv_bfloat16*>(packed), Cout, Cin, KH, KW, Cin_p, transpose_flip);
     return imx::check_launch("pack_conv_weight");
