@@ -244,29 +244,21 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
     }
 }
 
-// dw[co][ci][tap] = sum_split ws[split][tap][co][ci].  One block per (ci tile of 128, co): the
-// workspace rows are read contiguously along ci, transposed through shared memory, and the
-// gradient is written as one contiguous run of 128 * taps floats.
-constexpr int kRedTile = 128;
-
-__global__ void __launch_bounds__(256)
-wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw, int Cout, int Cin,
-                    int taps, int splits, int co_r, int ci_r) {
-    extern __shared__ float tile[];   // [kRedTile][taps + 1]
-    const int co = blockIdx.y;
-    const int ci0 = blockIdx.x * kRedTile;
-    const int n = min(kRedTile, Cin - ci0);
-    const int pitch = taps + 1;
-    for (int e = threadIdx.x; e < taps * n; e += 256) {
-        const int t = e / n, j = e - t * n;
+// dw[co][ci][kh][kw] = sum_split ws[split][tap][co][ci]
+__global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw, int Cout, int Cin,
+                                    int taps, int splits, int co_r, int ci_r) {
+    const long total = (long)Cout * Cin * taps;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        // consecutive threads -> consecutive ci (coalesced workspace reads)
+        const int ci = (int)(i % Cin);
+        long t = i / Cin;
+        const int tap = (int)(t % taps);
+        const int co = (int)(t / taps);
         float acc = 0.0f;
         for (int s = 0; s < splits; ++s)
-            acc += __ldg(ws + (((size_t)s * taps + t) * co_r + co) * ci_r + ci0 + j);
-        tile[j * pitch + t] = acc;
+            acc += __ldg(ws + (((size_t)s * taps + tap) * co_r + co) * ci_r + ci);
+        dw[((size_t)co * Cin + ci) * taps + tap] = acc;
     }
-    __syncthreads();
-    float* dst = dw + ((size_t)co * Cin + ci0) * taps;
-    for (int e = threadIdx.x; e < n * taps; e += 256) dst[e] = tile[(e / taps) * pitch + e % taps];
 }
 
 struct Plan {
@@ -402,11 +394,10 @@ extern "C" int imx_conv2d_igemm_wgrad_bf16(const imx_bf16* x, const imx_bf16* dy
         default: rc = launch_wgrad<64>(tdy, tx, a, s); break;
     }
     if (rc) return rc;
-    IMX_REQUIRE(Cout <= 65535, "conv2d_wgrad: Cout too large for the reduction grid");
-    const int taps = KH * KW;
-    dim3 rgrid((Cin + kRedTile - 1) / kRedTile, Cout);
-    wgrad_reduce_kernel<<<rgrid, 256, (size_t)kRedTile * (taps + 1) * sizeof(float), s>>>(
-        a.ws, dw, Cout, Cin, taps, pl.splits, a.co_r, a.ci_r);
+    const long total = (long)Cout * Cin * KH * KW;
+    long blocks = (total + 255) / 256;
+    if (blocks > 16L * imx::kNumSMs) blocks = 16L * imx::kNumSMs;
+    wgrad_reduce_kernel<<<(int)blocks, 256, 0, s>>>(a.ws, dw, Cout, Cin, KH * KW, pl.splits, a.co_r, a.ci_r);
     return imx::check_launch("conv2d_wgrad_reduce");
 }
 

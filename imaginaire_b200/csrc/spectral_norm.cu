@@ -231,3 +231,143 @@ extern "C" int imx_spectral_norm_weight_grad_f32(float* G, const float* W, const
     sn_grad_kernel<<<(int)b2, kT, 0, st>>>(G, u, v, inv_sigma, dot_scratch, R, C);
     return imx::check_launch("spectral_norm_weight_grad");
 }
+
+// ---------------------------------------------------------------------------------------------
+// All spectrally normalised layers of a network in one go.  The per-layer version above is a
+// chain of four small launches; a generator forward has ~90 such layers whose iterations depend
+// on the filters only, so they are batched: grid.y = layer, descriptors in device memory, five
+// launches per network forward in total.
+namespace {
+
+struct SnDesc {          // mirrored by imaginaire_b200/layers/conv.py (8 x int64)
+    const float* W;
+    float* u;
+    float* v;
+    long long t_off;     // offsets (floats) into the shared scratch: t[C] (zeroed by the caller), s[R]
+    long long s_off;
+    long long out_off;   // offset (floats) into the output buffer: [1/sigma | u copy (R) | v copy (C)]
+    long long R;
+    long long C;
+};
+
+__global__ void __launch_bounds__(kT)
+snb_wt_u_kernel(const SnDesc* __restrict__ descs, float* __restrict__ scratch, int rows_per_slice) {
+    const SnDesc d = descs[blockIdx.y];
+    const int R = (int)d.R, C = (int)d.C;
+    const int col_blocks = (C + kT * 4 - 1) / (kT * 4);
+    const int slices = (R + rows_per_slice - 1) / rows_per_slice;
+    if ((int)blockIdx.x >= col_blocks * slices) return;
+    const int cb = blockIdx.x % col_blocks, sl = blockIdx.x / col_blocks;
+    const int c0 = (cb * kT + threadIdx.x) * 4;
+    const int r0 = sl * rows_per_slice, r1 = min(R, r0 + rows_per_slice);
+    if (c0 >= C) return;
+    float a[4] = {0.f, 0.f, 0.f, 0.f};
+    if (c0 + 3 < C && (C & 3) == 0) {
+        const float* p = d.W + (size_t)r0 * C + c0;
+#pragma unroll 4
+        for (int r = r0; r < r1; ++r, p += C) {
+            const float4 w = __ldg(reinterpret_cast<const float4*>(p));
+            const float ur = __ldg(d.u + r);
+            a[0] = fmaf(w.x, ur, a[0]); a[1] = fmaf(w.y, ur, a[1]); a[2] = fmaf(w.z, ur, a[2]); a[3] = fmaf(w.w, ur, a[3]);
+        }
+    } else {
+        for (int r = r0; r < r1; ++r) {
+            const float ur = __ldg(d.u + r);
+            for (int k = 0; k < 4 && c0 + k < C; ++k) a[k] = fmaf(__ldg(d.W + (size_t)r * C + c0 + k), ur, a[k]);
+        }
+    }
+    float* t = scratch + d.t_off + c0;
+    for (int k = 0; k < 4 && c0 + k < C; ++k) atomicAdd(t + k, a[k]);
+}
+
+__global__ void __launch_bounds__(1024)
+snb_finish_v_kernel(const SnDesc* __restrict__ descs, float* __restrict__ scratch, float* __restrict__ out, float eps) {
+    __shared__ float sh[32];
+    const SnDesc d = descs[blockIdx.x];
+    const int R = (int)d.R, C = (int)d.C;
+    const float* t = scratch + d.t_off;
+    float sq = 0.0f;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) sq = fmaf(t[c], t[c], sq);
+    const float inv = 1.0f / fmaxf(sqrtf(block_sum(sq, sh)), eps);
+    float* vc = out + d.out_off + 1 + R;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        const float x = t[c] * inv;
+        d.v[c] = x;
+        vc[c] = x;
+    }
+}
+
+__global__ void __launch_bounds__(kT)
+snb_w_v_kernel(const SnDesc* __restrict__ descs, float* __restrict__ scratch) {
+    const SnDesc d = descs[blockIdx.y];
+    const int R = (int)d.R, C = (int)d.C;
+    const int r = blockIdx.x * (kT / 32) + (threadIdx.x >> 5);
+    if (r >= R) return;
+    const int lane = threadIdx.x & 31;
+    const float* p = d.W + (size_t)r * C;
+    float acc = 0.0f;
+    if ((C & 3) == 0) {
+        for (int c = lane * 4; c < C; c += 128) {
+            const float4 w = __ldg(reinterpret_cast<const float4*>(p + c));
+            const float4 x = *reinterpret_cast<const float4*>(d.v + c);
+            acc = fmaf(w.x, x.x, acc); acc = fmaf(w.y, x.y, acc); acc = fmaf(w.z, x.z, acc); acc = fmaf(w.w, x.w, acc);
+        }
+    } else {
+        for (int c = lane; c < C; c += 32) acc = fmaf(__ldg(p + c), d.v[c], acc);
+    }
+    acc = imx::warp_sum(acc);
+    if (lane == 0) scratch[d.s_off + r] = acc;
+}
+
+__global__ void __launch_bounds__(1024)
+snb_finish_u_kernel(const SnDesc* __restrict__ descs, const float* __restrict__ scratch, float* __restrict__ out,
+                    float eps, int update_u) {
+    __shared__ float sh[32];
+    const SnDesc d = descs[blockIdx.x];
+    const int R = (int)d.R, C = (int)d.C;
+    const float* s = scratch + d.s_off;
+    float* o = out + d.out_off;
+    if (update_u) {
+        float sq = 0.0f;
+        for (int r = threadIdx.x; r < R; r += blockDim.x) sq = fmaf(s[r], s[r], sq);
+        const float inv = 1.0f / fmaxf(sqrtf(block_sum(sq, sh)), eps);
+        for (int r = threadIdx.x; r < R; r += blockDim.x) d.u[r] = s[r] * inv;
+        __syncthreads();
+    }
+    float dd = 0.0f;
+    for (int r = threadIdx.x; r < R; r += blockDim.x) {
+        const float ur = d.u[r];
+        dd = fmaf(ur, s[r], dd);
+        o[1 + r] = ur;
+    }
+    const float sigma = block_sum(dd, sh);
+    if (threadIdx.x == 0) o[0] = 1.0f / sigma;
+    if (!update_u)
+        for (int c = threadIdx.x; c < C; c += blockDim.x) o[1 + R + c] = d.v[c];
+}
+
+}  // namespace
+
+extern "C" int imx_spectral_norm_sigma_batched_f32(const void* descs, int n_layers, int max_R, int max_C,
+                                                   void* scratch, float* out, int n_power_iterations, float eps,
+                                                   imx_stream_t stream) {
+    IMX_REQUIRE(n_layers >= 0 && n_layers <= 65535, "spectral_norm_sigma_batched: bad layer count");
+    if (n_layers == 0) return IMX_OK;
+    IMX_REQUIRE(descs && scratch && out, "spectral_norm_sigma_batched: null pointer");
+    IMX_REQUIRE(max_R > 0 && max_C > 0, "spectral_norm_sigma_batched: bad size");
+    IMX_REQUIRE(n_power_iterations == 0 || n_power_iterations == 1,
+                "spectral_norm_sigma_batched: 0 or 1 power iteration (the scratch is zeroed once by the caller)");
+    cudaStream_t st = (cudaStream_t)stream;
+    const SnDesc* d = reinterpret_cast<const SnDesc*>(descs);
+    float* sc = reinterpret_cast<float*>(scratch);
+    if (n_power_iterations == 1) {
+        const int rows_per_slice = 64;
+        const int col_blocks = (max_C + kT * 4 - 1) / (kT * 4);
+        const int slices = (max_R + rows_per_slice - 1) / rows_per_slice;
+        snb_wt_u_kernel<<<dim3(col_blocks * slices, n_layers), kT, 0, st>>>(d, sc, rows_per_slice);
+        snb_finish_v_kernel<<<n_layers, 1024, 0, st>>>(d, sc, out, eps);
+    }
+    snb_w_v_kernel<<<dim3((max_R + kT / 32 - 1) / (kT / 32), n_layers), kT, 0, st>>>(d, sc);
+    snb_finish_u_kernel<<<n_layers, 1024, 0, st>>>(d, sc, out, eps, n_power_iterations);
+    return imx::check_launch("spectral_norm_sigma_batched");
+}

@@ -8,6 +8,7 @@ Conv2dBlock.
 import torch
 from torch import nn
 
+from ..layers.conv import prefetch_spectral_norms
 from ..utils.data import get_paired_input_image_channel_number, get_paired_input_label_channel_number
 from .fpse import FPSEDiscriminator
 from .multires_patch import NLayerPatchDiscriminator
@@ -35,6 +36,7 @@ class Discriminator(nn.Module):
             weight_norm_type, getattr(dis_cfg, 'fpse_activation_norm_type', 'none'))
 
     def _single_forward(self, input_label, input_image):
+        prefetch_spectral_norms(self)   # every layer below runs exactly once per _single_forward
         input_x = torch.cat((input_label, input_image), 1)
         outputs = list(self.fpse_discriminator(input_image, input_label))
         features = []

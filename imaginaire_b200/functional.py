@@ -119,7 +119,7 @@ def _act_backward(dy, y, act):
     return dy
 
 
-def spectral_sigma(weight_orig, u_buf, v_buf, training, n_power_iterations=1, eps=1e-12):
+def spectral_sigma(weight_orig, u_buf, v_buf, training, n_power_iterations=1, eps=1e-12, out=None):
     """Spectral norm of a filter with torch.nn.utils.spectral_norm's semantics (the reference's
     weight norm, imaginaire/layers/weight_norm.py:85): in training mode run the power iteration
     in place on the module's u / v buffers (no autograd), then sigma = u^T W v.  Returns
@@ -130,7 +130,7 @@ def spectral_sigma(weight_orig, u_buf, v_buf, training, n_power_iterations=1, ep
     twice, and W / sigma is never materialised: the division happens inside the repack kernel."""
     with torch.no_grad():
         return ops.spectral_norm_sigma(weight_orig.detach(), u_buf, v_buf,
-                                       n_power_iterations if training else 0, eps)
+                                       n_power_iterations if training else 0, eps, out=out)
 
 
 class _Conv2d(torch.autograd.Function):

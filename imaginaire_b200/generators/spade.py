@@ -27,6 +27,7 @@ from torch import nn
 
 from .. import functional as NF
 from ..layers import Conv2dBlock, LinearBlock, Res2dBlock
+from ..layers.conv import prefetch_spectral_norms
 from ..layers.residual import _inner_stats_mode
 from ..utils.data import (get_crop_h_w, get_paired_input_image_channel_number,
                           get_paired_input_label_channel_number)
@@ -92,7 +93,10 @@ class Generator(nn.Module):
         return torch.randn(label.size(0), self.style_dims, dtype=torch.float32, device=label.device)
 
     def forward(self, data, random_style=False):
+        prefetch_spectral_norms(self.spade_generator)
         if self.use_style_encoder:
+            if not random_style:
+                prefetch_spectral_norms(self.style_encoder)
             if random_style:
                 z, mu, logvar = self._random_z(data['label']), None, None
             else:

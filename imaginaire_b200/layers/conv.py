@@ -61,6 +61,9 @@ class Conv2d(nn.Conv2d):
         hook = self.spectral_hook()
         if hook is None:
             return self.effective_weight(), None
+        ready = self.__dict__.pop('_sn_ready', None)
+        if ready is not None:
+            return self.weight_orig, ready      # computed for the whole network by prefetch_spectral_norms
         return self.weight_orig, NF.spectral_sigma(self.weight_orig, self.weight_u, self.weight_v, self.training,
                                                    hook.n_power_iterations, hook.eps)
 
@@ -71,6 +74,49 @@ class Conv2d(nn.Conv2d):
 
     def forward(self, x):
         return self.native_forward(NF.to_nhwc(x))
+
+
+def prefetch_spectral_norms(root):
+    """Runs this forward's spectral-norm power iteration and sigma of EVERY spectrally normalised
+    convolution under `root` in one batched call (imx_spectral_norm_sigma_batched_f32: five
+    launches instead of four per layer).  The iteration depends on the filters only, so doing all
+    layers up front is the same computation as the reference's per-layer hook; each layer picks
+    its (1/sigma, u, v) up in weight_for_kernel().  Call it only for modules that WILL run in
+    this forward: like the hook, every call advances u and v once."""
+    layers = [m for m in root.modules() if isinstance(m, Conv2d) and m.spectral_hook() is not None]
+    if not layers or not layers[0].weight_orig.is_cuda:
+        return
+    hooks = [m.spectral_hook() for m in layers]
+    if any(h.n_power_iterations != 1 or h.eps != hooks[0].eps for h in hooks):
+        return                      # unusual settings: every layer falls back to its own call
+    key = tuple((m.weight_orig.data_ptr(), m.weight_u.data_ptr(), m.weight_v.data_ptr()) for m in layers)
+    plan = root.__dict__.get('_sn_plan')
+    if plan is None or plan['key'] != key:
+        dev = layers[0].weight_orig.device
+        rows, t_off, out_off, spans = [], 0, 0, []
+        for m in layers:
+            r = m.weight_orig.shape[0]
+            c = m.weight_orig.numel() // r
+            rows.append([m.weight_orig.data_ptr(), m.weight_u.data_ptr(), m.weight_v.data_ptr(), t_off, 0, out_off, r, c])
+            spans.append((out_off, r, c))
+            t_off += c
+            out_off += 1 + r + c
+        s_off = t_off
+        for row in rows:
+            row[4] = s_off
+            s_off += row[6]
+        plan = dict(key=key, descs=torch.tensor(rows, dtype=torch.int64).to(dev), t_floats=t_off,
+                    scratch=torch.empty((s_off,), dtype=torch.float32, device=dev), out_floats=out_off, spans=spans,
+                    max_r=max(r[6] for r in rows), max_c=max(r[7] for r in rows))
+        root.__dict__['_sn_plan'] = plan
+    training = layers[0].training
+    with torch.no_grad():
+        if training:
+            plan['scratch'][:plan['t_floats']].zero_()
+        out = ops.spectral_norm_sigma_batched(plan['descs'], len(layers), plan['max_r'], plan['max_c'], plan['scratch'],
+                                              plan['out_floats'], 1 if training else 0, hooks[0].eps)
+    for m, (off, r, c) in zip(layers, plan['spans']):
+        m.__dict__['_sn_ready'] = (out[off:off + 1], out[off + 1:off + 1 + r], out[off + 1 + r:off + 1 + r + c])
 
 
 _FUSABLE_ACT = {nn.LeakyReLU: ops.ACT_LRELU, nn.ReLU: ops.ACT_RELU}

@@ -186,7 +186,7 @@ def pack_spade_gb_weight(w_gamma, w_beta, inv_sigma_gamma=None, inv_sigma_beta=N
     return out
 
 
-def spectral_norm_sigma(weight, u, v, n_power_iterations, eps):
+def spectral_norm_sigma(weight, u, v, n_power_iterations, eps, out=None):
     """In-place power iteration on the buffers u, v and sigma of `weight` viewed as
     [Cout, -1].  Returns (inv_sigma (1,), u copy, v copy)."""
     _req_cuda(weight, u, v)
@@ -196,11 +196,20 @@ def spectral_norm_sigma(weight, u, v, n_power_iterations, eps):
     lib = _C.lib()
     nbytes = lib.raw('imx_spectral_norm_scratch_bytes')(r, c)
     scratch = torch.empty((int(nbytes),), dtype=torch.uint8, device=weight.device)
-    out = torch.empty((1 + r + c,), dtype=torch.float32, device=weight.device)
+    if out is None:
+        out = torch.empty((1 + r + c,), dtype=torch.float32, device=weight.device)
     inv_sigma, u_copy, v_copy = out[:1], out[1:1 + r], out[1 + r:]
     lib.call('imx_spectral_norm_sigma_f32', _ptr(weight), _ptr(u), _ptr(v), _ptr(u_copy), _ptr(v_copy),
              _ptr(inv_sigma), _ptr(scratch), int(nbytes), r, c, int(n_power_iterations), float(eps), _stream())
     return inv_sigma, u_copy, v_copy
+
+
+def spectral_norm_sigma_batched(descs, n_layers, max_r, max_c, scratch, out_floats, n_power_iterations, eps):
+    """descs: int64 [n_layers, 8] device tensor (see include/imx.h).  Returns the output buffer."""
+    out = torch.empty((out_floats,), dtype=torch.float32, device=descs.device)
+    _C.lib().call('imx_spectral_norm_sigma_batched_f32', _ptr(descs), int(n_layers), int(max_r), int(max_c),
+                  _ptr(scratch), _ptr(out), int(n_power_iterations), float(eps), _stream())
+    return out
 
 
 def spectral_norm_weight_grad_(grad, weight, u, v, inv_sigma):

@@ -128,6 +128,15 @@ IMX_API int imx_spectral_norm_sigma_f32(const float* W, float* u, float* v, floa
                                         imx_stream_t stream);
 IMX_API int64_t imx_spectral_norm_scratch_bytes(int R, int C);
 
+/* The same for many layers at once (one network forward): descs = device array of n_layers
+ * records of eight 64-bit fields {W, u, v, t_off, s_off, out_off, R, C}; t_off / s_off are
+ * float offsets into `scratch` (t: C floats that the caller zero-fills, s: R floats),
+ * out_off a float offset into `out` where [1/sigma | u copy (R) | v copy (C)] is written.
+ * n_power_iterations is 1 (training) or 0 (eval).  Four launches in total. */
+IMX_API int imx_spectral_norm_sigma_batched_f32(const void* descs, int n_layers, int max_R, int max_C,
+                                                void* scratch, float* out, int n_power_iterations, float eps,
+                                                imx_stream_t stream);
+
 /* Backward of W_eff = W / sigma(W) with u, v constant: in place on G = dL/dW_eff,
  * G <- G / sigma - (<G, W> / sigma^2) u v^T  (= dL/dW).  dot_scratch: one float. */
 IMX_API int imx_spectral_norm_weight_grad_f32(float* G, const float* W, const float* u, const float* v,
