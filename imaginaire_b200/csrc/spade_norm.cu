@@ -184,7 +184,7 @@ __device__ __forceinline__ void load_norm_params(const ModArgs& a, int n, int c,
 
 // grid = (blocks, N).  Each block walks a pixel range of one sample.
 template <int kMode>  // 0: forward   1: backward pass 1 (dgamma/dbeta + reductions)   2: backward pass 2 (dx)
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 2)
 modulate_kernel(ModArgs a, uint4* __restrict__ out0, void* __restrict__ out1, void* __restrict__ out2,
                 float* __restrict__ red, float inv_count, int use_batch_stats,
                 int cg, int tpr, int rows) {
@@ -228,17 +228,38 @@ modulate_kernel(ModArgs a, uint4* __restrict__ out0, void* __restrict__ out1, vo
         float r1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, r2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         float ag[8] = {0, 0, 0, 0, 0, 0, 0, 0}, ab[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         if (active) {
-            for (long p = p0 + r; p < p1; p += rows) {
+            // Raw 128-bit loads of one pixel row.  The next row's loads are issued before the
+            // current row is processed (register double buffering): twice the bytes in flight
+            // per thread, which is what a 2-CTA/SM kernel needs to approach HBM bandwidth.
+            struct Raw { uint4 x, g, b, dy; };
+            auto load_raw = [&](long p) {
+                Raw q;
                 long px = p;
                 if (a.up2x) {
                     const int yy = (int)(p / a.W), xx = (int)(p - (long)yy * a.W);
                     px = (long)(yy >> 1) * Wx + (xx >> 1);
                 }
-                float xv[8], g[8], be[8];
-                unpack8(a.up2x ? __ldg(xb + (size_t)px * cg + c8) : imx::ldg_stream(xb + (size_t)px * cg + c8), xv);
+                q.x = a.up2x ? __ldg(xb + (size_t)px * cg + c8) : imx::ldg_stream(xb + (size_t)px * cg + c8);
                 if (a.gb_mode == 0) {
-                    unpack8(imx::ldg_stream(reinterpret_cast<const uint4*>(a.gamma) + ob + (size_t)p * cg + c8), g);
-                    unpack8(imx::ldg_stream(reinterpret_cast<const uint4*>(a.beta) + ob + (size_t)p * cg + c8), be);
+                    q.g = imx::ldg_stream(reinterpret_cast<const uint4*>(a.gamma) + ob + (size_t)p * cg + c8);
+                    q.b = imx::ldg_stream(reinterpret_cast<const uint4*>(a.beta) + ob + (size_t)p * cg + c8);
+                } else {
+                    q.g = make_uint4(0, 0, 0, 0);
+                    q.b = make_uint4(0, 0, 0, 0);
+                }
+                if (kMode != 0) q.dy = imx::ldg_stream(a.dy + ob + (size_t)p * cg + c8);
+                else q.dy = make_uint4(0, 0, 0, 0);
+                return q;
+            };
+            Raw cur = load_raw(p0 + r < p1 ? p0 + r : p1 - 1);
+            for (long p = p0 + r; p < p1; p += rows) {
+                const long pn = p + rows;
+                const Raw nxt = load_raw(pn < p1 ? pn : p);   // tail: harmless re-read of the current row
+                float xv[8], g[8], be[8];
+                unpack8(cur.x, xv);
+                if (a.gb_mode == 0) {
+                    unpack8(cur.g, g);
+                    unpack8(cur.b, be);
                 } else if (a.gb_mode == 1) {
 #pragma unroll
                     for (int k = 0; k < 8; ++k) { g[k] = gv[k]; be[k] = bv[k]; }
@@ -256,7 +277,7 @@ modulate_kernel(ModArgs a, uint4* __restrict__ out0, void* __restrict__ out1, vo
                     imx::stg_stream(out0 + ob + (size_t)p * cg + c8, pack8(y));
                 } else {
                     float dyv[8];
-                    unpack8(imx::ldg_stream(a.dy + ob + (size_t)p * cg + c8), dyv);
+                    unpack8(cur.dy, dyv);
                     float o0[8], o1[8];
 #pragma unroll
                     for (int k = 0; k < 8; ++k) {
@@ -285,6 +306,7 @@ modulate_kernel(ModArgs a, uint4* __restrict__ out0, void* __restrict__ out1, vo
                         imx::stg_stream(out0 + ob + (size_t)p * cg + c8, pack8(o0));
                     }
                 }
+                cur = nxt;
             }
         }
         if (kMode == 1) {
@@ -350,7 +372,7 @@ extern "C" int imx_bn_stats_nhwc_bf16(const imx_bf16* x, float* sum, float* sums
     const int groups = per_instance ? N : 1;
     IMX_REQUIRE(groups <= 65535, "bn_stats: batch too large");
     const long HWg = per_instance ? HW : (long)N * HW;
-    dim3 grid(pick_blocks(HWg, m.rows, groups), groups);
+    dim3 grid(pick_blocks(HWg, m.rows, groups, 4), groups);
     stats_kernel<true><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<const uint4*>(x), sum, sumsq, HWg, C, m.cg, m.tpr, m.rows, m.cg);
     return imx::check_launch("bn_stats");
@@ -363,7 +385,7 @@ extern "C" int imx_channel_sum_nhwc_bf16(const imx_bf16* x, float* out, int NP, 
     IMX_REQUIRE(C % 8 == 0 && Cp % 8 == 0, "channel_sum: C and Cp must be multiples of 8");
     if ((long)NP * C == 0) return IMX_OK;
     const RowMap m = make_rowmap(C);
-    dim3 grid(pick_blocks(NP, m.rows, 1), 1);
+    dim3 grid(pick_blocks(NP, m.rows, 1, 4), 1);
     stats_kernel<false><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<const uint4*>(x), out, nullptr, NP, C, m.cg, m.tpr, m.rows, Cp / 8);
     return imx::check_launch("channel_sum");
