@@ -389,9 +389,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     tc_fence_before_sync();
     __syncthreads();
     if (stats_in_smem) {
-        for (int i = threadIdx.x; i < 2 * p.Cout; i += kThreads) {
-            const float v = s_stats[i];
-            if (v != 0.0f) atomicAdd(p.stats + i, v);
+        if ((p.Cout & 3) == 0) {
+            for (int i = threadIdx.x * 4; i < 2 * p.Cout; i += kThreads * 4)
+                imx::red_add_v4(p.stats + i, s_stats[i], s_stats[i + 1], s_stats[i + 2], s_stats[i + 3]);
+        } else {
+            for (int i = threadIdx.x; i < 2 * p.Cout; i += kThreads) atomicAdd(p.stats + i, s_stats[i]);
         }
     }
     if (warp == 2) {

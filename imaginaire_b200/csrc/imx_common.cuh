@@ -50,6 +50,13 @@ __device__ __forceinline__ void stg_stream(void* p, const uint4& v) {
                  :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
+// Vector reduction to global memory: one REDG.ADD.F32x4 instead of four scalar atomics (the
+// accumulators of the statistics kernels are hammered by every CTA at the same time; the L2
+// atomic units serialise per address, so fewer, wider operations matter).  p must be 16-byte aligned.
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -115,8 +115,8 @@ stats_kernel(const uint4* __restrict__ x, float* __restrict__ sum, float* __rest
 #pragma unroll
                     for (int k = 0; k < 8; ++k) acc[k] += red[tid + rr * tpr][k];
                 float* dst = (pass == 0 ? sum : sumsq) + (size_t)g * C + c8 * 8;
-#pragma unroll
-                for (int k = 0; k < 8; ++k) atomicAdd(dst + k, acc[k]);
+                imx::red_add_v4(dst, acc[0], acc[1], acc[2], acc[3]);
+                imx::red_add_v4(dst + 4, acc[4], acc[5], acc[6], acc[7]);
             }
         }
     }
@@ -329,11 +329,12 @@ modulate_kernel(ModArgs a, uint4* __restrict__ out0, void* __restrict__ out1, vo
                     if (pass == 0) {
                         const int G = a.per_instance ? a.N : 1;
                         const int so = (a.per_instance ? n * a.C : 0) + c;
-#pragma unroll
-                        for (int k = 0; k < 8; ++k) {
-                            atomicAdd(red + so + k, acc[k]);
-                            atomicAdd(red + (size_t)G * a.C + so + k, acc[8 + k]);
-                        }
+                        float* d0 = red + so;
+                        float* d1 = red + (size_t)G * a.C + so;
+                        imx::red_add_v4(d0, acc[0], acc[1], acc[2], acc[3]);
+                        imx::red_add_v4(d0 + 4, acc[4], acc[5], acc[6], acc[7]);
+                        imx::red_add_v4(d1, acc[8], acc[9], acc[10], acc[11]);
+                        imx::red_add_v4(d1 + 4, acc[12], acc[13], acc[14], acc[15]);
                     } else {
                         float* dg = reinterpret_cast<float*>(out1) + (size_t)n * a.C + c;
                         float* db = reinterpret_cast<float*>(out2) + (size_t)n * a.C + c;
