@@ -51,8 +51,9 @@ template <int BN, int MT> struct Cfg {
     static constexpr int STAGES = (196608 / STAGE_BYTES) > 8 ? 8 : (196608 / STAGE_BYTES);
     static constexpr int TMEM_COLS = (2 * MT * BN < 32) ? 32 : 2 * MT * BN;
     static constexpr int STATS_SMEM_CH = 2048;   // per-CTA statistics accumulators for up to this many channels
+    static constexpr int EPI_SMEM_BYTES = 6144;  // per-tile epilogue coefficients, two stages
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ +
-                                      2 * STATS_SMEM_CH * 4;
+                                      2 * STATS_SMEM_CH * 4 + EPI_SMEM_BYTES;
 };
 
 struct ConvArgs {
@@ -78,6 +79,9 @@ struct ConvArgs {
     const float* nb;
     int C, per_instance, act, up2x;
 };
+
+// named barrier of the four epilogue warps
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
 __device__ __forceinline__ float act_apply(float v, int act) {
     if (act == 1) return v > 0.0f ? v : 0.2f * v;
@@ -107,6 +111,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     // once at the end: 2*Cout global atomics per CTA instead of per tile (the per-tile version
     // serialises on the few L2 slices that hold the 2*Cout accumulators).
     float* s_stats = reinterpret_cast<float*>(smem + C::STAGES * C::STAGE_BYTES + 256);
+    float* s_epi = s_stats + 2 * C::STATS_SMEM_CH;
     const bool stats_in_smem = kMode == 0 && (p.flags & IMX_EPI_STATS) && !(p.flags & IMX_EPI_STATS_INSTANCE) &&
                                p.Cout <= C::STATS_SMEM_CH;
     if (stats_in_smem)
@@ -213,8 +218,38 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
             const int n0 = n_tile * BN;
 
-            mbar_wait(&tmem_full[as], aphase);
-            tc_fence_after_sync();
+            // Per-channel epilogue coefficients of this tile go to shared memory once (double
+            // buffered by accumulator stage), so the per-element work reads them as broadcast
+            // LDS instead of 32 dependent global loads per chunk.
+            if constexpr (kMode == 0) {
+                if (p.flags & IMX_EPI_BIAS) {
+                    for (int i = threadIdx.x - kEpiWarp0 * 32; i < BN; i += 128)
+                        s_epi[as * BN + i] = (n0 + i < p.Cout) ? __ldg(p.bias + n0 + i) : 0.0f;
+                    epi_bar_sync();
+                }
+            } else {
+                // channels c0 + [0, 64) of every 128-column group: {mean, rstd*w, b, 1 + bias_gamma}, bias_beta
+                float4* cf = reinterpret_cast<float4*>(s_epi) + as * (BN / 2);
+                float* cbb = s_epi + 4 * BN + as * (BN / 2);
+                for (int i = threadIdx.x - kEpiWarp0 * 32; i < BN / 2; i += 128) {
+                    const int c = (n0 / 128 + (i >> 6)) * 64 + (i & 63);
+                    float4 v = make_float4(0.f, 0.f, 0.f, 1.f);
+                    float bb = 0.0f;
+                    if (c < p.C) {
+                        const int so = (p.per_instance ? img * p.C : 0) + c;
+                        v.x = __ldg(p.mean + so);
+                        v.y = __ldg(p.rstd + so) * (p.nw ? __ldg(p.nw + c) : 1.0f);
+                        v.z = p.nb ? __ldg(p.nb + c) : 0.0f;
+                        v.w = 1.0f + (p.bias ? __ldg(p.bias + c) : 0.0f);
+                        bb = p.bias_beta ? __ldg(p.bias_beta + c) : 0.0f;
+                    }
+                    cf[i] = v;
+                    cbb[i] = bb;
+                }
+                epi_bar_sync();
+            }
+
+            bool waited = false;
 #pragma unroll 1
             for (int mt = 0; mt < MT; ++mt) {
             const int prow = mt * BM + row;         // pixel index inside the CTA tile
@@ -225,37 +260,38 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             const uint32_t t_acc = tmem_base + as * (MT * BN) + mt * BN + (static_cast<uint32_t>(q * 32) << 16);
 
             if constexpr (kMode == 0) {
-#pragma unroll 1
-                for (int ch = 0; ch < BN / 32; ++ch) {
-                    uint32_t v[32];
-                    tmem_ld_32x32(t_acc + ch * 32, v);
-                    tmem_ld_wait();
-                    if (ch == BN / 32 - 1 && mt == MT - 1) {
-                        // accumulator fully drained into registers: hand the TMEM stage back
-                        tc_fence_before_sync();
-                        mbar_arrive(&tmem_empty[as]);
+                constexpr int NCH = BN / 32;
+                const bool has_res = (p.flags & IMX_EPI_RESIDUAL) != 0;
+                const uint4* rbase = reinterpret_cast<const uint4*>(p.residual + pix * p.Cout_p + n0);
+                // residual of chunk ch: four 16-byte pieces of this pixel's row (issued two chunks ahead)
+                auto load_res = [&](int ch, uint4 (&r)[4]) {
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        r[g] = make_uint4(0u, 0u, 0u, 0u);
+                        if (has_res && valid && ch < NCH && n0 + ch * 32 + g * 8 < p.Cout_p) r[g] = __ldg(rbase + ch * 4 + g);
                     }
+                };
+                auto process = [&](int ch, const uint32_t (&v)[32], const uint4 (&r)[4]) {
                     const int nb = n0 + ch * 32;
-                    if (nb >= p.Cout_p) continue;   // warp-uniform
+                    if (nb >= p.Cout_p) return;   // warp-uniform
                     float f[32];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
                     if (p.flags & IMX_EPI_BIAS) {
+                        const float4* sb = reinterpret_cast<const float4*>(s_epi + as * BN + ch * 32);
 #pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            if (nb + j < p.Cout) f[j] += __ldg(p.bias + nb + j);
+                        for (int g = 0; g < 8; ++g) {
+                            const float4 b4 = sb[g];
+                            f[4 * g] += b4.x; f[4 * g + 1] += b4.y; f[4 * g + 2] += b4.z; f[4 * g + 3] += b4.w;
+                        }
                     }
-                    if ((p.flags & IMX_EPI_RESIDUAL) && valid) {
-                        const uint4* r = reinterpret_cast<const uint4*>(p.residual + pix * p.Cout_p + nb);
+                    if (has_res) {
 #pragma unroll
                         for (int g = 0; g < 4; ++g) {
-                            if (nb + g * 8 < p.Cout_p) {
-                                const uint4 rv = __ldg(r + g);
-                                f[g * 8 + 0] += imx::bf16_lo(rv.x); f[g * 8 + 1] += imx::bf16_hi(rv.x);
-                                f[g * 8 + 2] += imx::bf16_lo(rv.y); f[g * 8 + 3] += imx::bf16_hi(rv.y);
-                                f[g * 8 + 4] += imx::bf16_lo(rv.z); f[g * 8 + 5] += imx::bf16_hi(rv.z);
-                                f[g * 8 + 6] += imx::bf16_lo(rv.w); f[g * 8 + 7] += imx::bf16_hi(rv.w);
-                            }
+                            f[g * 8 + 0] += imx::bf16_lo(r[g].x); f[g * 8 + 1] += imx::bf16_hi(r[g].x);
+                            f[g * 8 + 2] += imx::bf16_lo(r[g].y); f[g * 8 + 3] += imx::bf16_hi(r[g].y);
+                            f[g * 8 + 4] += imx::bf16_lo(r[g].z); f[g * 8 + 5] += imx::bf16_hi(r[g].z);
+                            f[g * 8 + 6] += imx::bf16_lo(r[g].w); f[g * 8 + 7] += imx::bf16_hi(r[g].w);
                         }
                     }
                     if (p.flags & IMX_EPI_LRELU) {
@@ -321,6 +357,33 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                             atomicAdd(sdst + (size_t)(inst ? p.N : 1) * p.Cout, q_mine);
                         }
                     }
+                };
+                // Software pipeline over the 32-column chunks: the TMEM load of chunk ch+1 and the
+                // residual loads of chunk ch+2 are in flight while chunk ch is processed.
+                uint32_t va[32], vb[32];
+                uint4 ra[4], rb[4];
+                load_res(0, ra);
+                load_res(1, rb);
+                if (!waited) {
+                    mbar_wait(&tmem_full[as], aphase);
+                    tc_fence_after_sync();
+                    waited = true;
+                }
+                tmem_ld_32x32(t_acc, va);
+#pragma unroll 1
+                for (int ch = 0; ch < NCH; ch += 2) {
+                    tmem_ld_wait();
+                    if (ch + 1 < NCH) tmem_ld_32x32(t_acc + (ch + 1) * 32, vb);
+                    else if (mt == MT - 1) { tc_fence_before_sync(); mbar_arrive(&tmem_empty[as]); }
+                    process(ch, va, ra);
+                    load_res(ch + 2, ra);
+                    if (ch + 1 < NCH) {
+                        tmem_ld_wait();
+                        if (ch + 2 < NCH) tmem_ld_32x32(t_acc + (ch + 2) * 32, va);
+                        else if (mt == MT - 1) { tc_fence_before_sync(); mbar_arrive(&tmem_empty[as]); }
+                        process(ch + 1, vb, rb);
+                        load_res(ch + 3, rb);
+                    }
                 }
             } else {
                 // ---- SPADE: columns [g*128, g*128+64) = gamma, [g*128+64, g*128+128) = beta of
@@ -328,58 +391,68 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                 const int oyx = p.up2x ? (oy >> 1) : oy, oxx = p.up2x ? (ox >> 1) : ox;
                 const int Hx = p.up2x ? (p.Ho >> 1) : p.Ho, Wx = p.up2x ? (p.Wo >> 1) : p.Wo;
                 const size_t xpix = ((size_t)img * Hx + oyx) * Wx + oxx;
-#pragma unroll 1
-                for (int g = 0; g < BN / 128; ++g) {
-                    const int c0 = (n0 / 128 + g) * 64;
-#pragma unroll 1
-                    for (int h = 0; h < 2; ++h) {
-                        uint32_t vg[32], vb[32];
-                        tmem_ld_32x32(t_acc + g * 128 + h * 32, vg);
-                        tmem_ld_32x32(t_acc + g * 128 + 64 + h * 32, vb);
-                        tmem_ld_wait();
-                        if (g == BN / 128 - 1 && h == 1) {
-                            tc_fence_before_sync();
-                            mbar_arrive(&tmem_empty[as]);
-                        }
-                        const int cb = c0 + h * 32;
-                        if (cb >= p.C) continue;   // warp-uniform (C % 32 == 0 enforced on the host)
-                        uint32_t xr[16];
-                        if (valid) {
-                            const uint4* xp = reinterpret_cast<const uint4*>(p.x + xpix * p.C + cb);
+                const float4* cf = reinterpret_cast<const float4*>(s_epi) + as * (BN / 2);
+                const float* cbb = s_epi + 4 * BN + as * (BN / 2);
+                constexpr int NCH = BN / 64;     // chunks of 32 channels (32 gamma + 32 beta columns)
+                auto chan0 = [&](int cc) { return (n0 / 128 + (cc >> 1)) * 64 + (cc & 1) * 32; };
+                auto load_x = [&](int cc, uint4 (&xr)[4]) {
 #pragma unroll
-                            for (int t = 0; t < 4; ++t) {
-                                const uint4 xv = __ldg(xp + t);
-                                xr[4 * t] = xv.x; xr[4 * t + 1] = xv.y; xr[4 * t + 2] = xv.z; xr[4 * t + 3] = xv.w;
-                            }
-                        } else {
-#pragma unroll
-                            for (int t = 0; t < 16; ++t) xr[t] = 0u;
-                        }
-                        const int so = (p.per_instance ? img * p.C : 0) + cb;
-                        uint32_t o[16];
-#pragma unroll
-                        for (int j = 0; j < 32; j += 2) {
-                            float y2[2];
-#pragma unroll
-                            for (int e = 0; e < 2; ++e) {
-                                const int c = j + e;
-                                const float xv = e == 0 ? imx::bf16_lo(xr[j >> 1]) : imx::bf16_hi(xr[j >> 1]);
-                                const float m = __ldg(p.mean + so + c), rs = __ldg(p.rstd + so + c);
-                                float xh = (xv - m) * rs;
-                                if (p.nw) xh = fmaf(xh, __ldg(p.nw + cb + c), p.nb ? __ldg(p.nb + cb + c) : 0.0f);
-                                float gam = __uint_as_float(vg[c]), bet = __uint_as_float(vb[c]);
-                                if (p.bias) gam += __ldg(p.bias + cb + c);
-                                if (p.bias_beta) bet += __ldg(p.bias_beta + cb + c);
-                                y2[e] = act_apply(fmaf(xh, 1.0f + gam, bet), p.act);
-                            }
-                            o[j >> 1] = imx::pack_bf16(y2[0], y2[1]);
-                        }
-                        if (valid) {
-                            uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.out) + pix * p.C + cb);
-#pragma unroll
-                            for (int t = 0; t < 4; ++t) dst[t] = make_uint4(o[4 * t], o[4 * t + 1], o[4 * t + 2], o[4 * t + 3]);
-                        }
+                    for (int t = 0; t < 4; ++t) {
+                        xr[t] = make_uint4(0u, 0u, 0u, 0u);
+                        if (valid && cc < NCH && chan0(cc) < p.C)
+                            xr[t] = __ldg(reinterpret_cast<const uint4*>(p.x + xpix * p.C + chan0(cc)) + t);
                     }
+                };
+                uint4 xa[4], xb[4];
+                load_x(0, xa);
+                load_x(1, xb);
+                if (!waited) {
+                    mbar_wait(&tmem_full[as], aphase);
+                    tc_fence_after_sync();
+                    waited = true;
+                }
+                auto process = [&](int cc, const uint4 (&xr4)[4]) {
+                    const int g = cc >> 1, h = cc & 1;
+                    uint32_t vg[32], vb[32];
+                    tmem_ld_32x32(t_acc + g * 128 + h * 32, vg);
+                    tmem_ld_32x32(t_acc + g * 128 + 64 + h * 32, vb);
+                    tmem_ld_wait();
+                    if (cc == NCH - 1 && mt == MT - 1) {
+                        tc_fence_before_sync();
+                        mbar_arrive(&tmem_empty[as]);
+                    }
+                    const int cb = chan0(cc);
+                    if (cb >= p.C) return;   // warp-uniform (C % 32 == 0 enforced on the host)
+                    const uint32_t xr[16] = {xr4[0].x, xr4[0].y, xr4[0].z, xr4[0].w, xr4[1].x, xr4[1].y, xr4[1].z, xr4[1].w,
+                                             xr4[2].x, xr4[2].y, xr4[2].z, xr4[2].w, xr4[3].x, xr4[3].y, xr4[3].z, xr4[3].w};
+                    uint32_t o[16];
+#pragma unroll
+                    for (int j = 0; j < 32; j += 2) {
+                        float y2[2];
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            const int c = j + e;
+                            const float xv = e == 0 ? imx::bf16_lo(xr[j >> 1]) : imx::bf16_hi(xr[j >> 1]);
+                            const float4 k4 = cf[g * 64 + h * 32 + c];
+                            const float xh = fmaf(xv - k4.x, k4.y, k4.z);
+                            const float gam1 = __uint_as_float(vg[c]) + k4.w;
+                            const float bet = __uint_as_float(vb[c]) + cbb[g * 64 + h * 32 + c];
+                            y2[e] = act_apply(fmaf(xh, gam1, bet), p.act);
+                        }
+                        o[j >> 1] = imx::pack_bf16(y2[0], y2[1]);
+                    }
+                    if (valid) {
+                        uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.out) + pix * p.C + cb);
+#pragma unroll
+                        for (int t = 0; t < 4; ++t) dst[t] = make_uint4(o[4 * t], o[4 * t + 1], o[4 * t + 2], o[4 * t + 3]);
+                    }
+                };
+#pragma unroll 1
+                for (int cc = 0; cc < NCH; cc += 2) {
+                    process(cc, xa);
+                    load_x(cc + 2, xa);
+                    process(cc + 1, xb);
+                    load_x(cc + 3, xb);
                 }
             }
             }   // mt
@@ -478,13 +551,15 @@ extern "C" int imx_conv2d_igemm_fprop_bf16(const imx_bf16* x, const imx_bf16* wp
     const int BN = Cout_p > 128 ? 256 : (Cout_p > 64 ? 128 : (Cout_p > 32 ? 64 : 32));
     ConvArgs a{};
     CUtensorMap ta, tb;
-    // Narrow channel tiles take 256-pixel CTA tiles (two MMAs per B tile) when that still leaves
-    // at least two tiles per SM.
+    // Narrow channel tiles (BN <= 128) need more operand bytes per MMA cycle than L2 delivers, so
+    // they run ~1.7x slower per pixel with 128-pixel tiles than with 256-pixel tiles (two MMAs
+    // per B tile).  Whenever there is more than one wave of 128-pixel tiles the 256-pixel tiling
+    // is at least as fast even counting its coarser wave quantisation.
     int MT = 1;
     if (BN <= 128) {
         const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
-        const long tiles256 = (long)N * ((Ho * (long)Wo + 255) / 256) * ((Cout + BN - 1) / BN);
-        if (tiles256 >= 2L * imx::kNumSMs && (stride == 1 || Wo >= 128 || ((256 / (Wo < 128 ? Wo : 128)) - 1) * stride + 1 <= 256))
+        const long tiles128 = (long)N * ((Ho * (long)Wo + 127) / 128) * ((Cout + BN - 1) / BN);
+        if (tiles128 > imx::kNumSMs && (stride == 1 || Wo >= 128 || ((256 / (Wo < 128 ? Wo : 128)) - 1) * stride + 1 <= 256))
             MT = 2;
     }
     int rc = setup(a, ta, tb, x, wpk, N, H, W, Cin_p, Cout, KH, KW, stride, pad, BN, MT);

@@ -66,12 +66,15 @@ __device__ __forceinline__ Unit decode_unit(int u, const WgradArgs& p) {
     Unit r;
     const int taps = p.KH * p.KW;
     const int groups = (taps + T - 1) / T;
-    r.split = u % p.splits; u /= p.splits;
+    // Tap group fastest, pixel split slowest: the CTAs of one wave then work on the same pixel
+    // range (same dY boxes, overlapping X boxes), so those are fetched from HBM once and hit L2
+    // for every other unit of the wave.
     const int g = u % groups; u /= groups;
     r.tap0 = g * T;
     r.ntaps = taps - r.tap0 < T ? taps - r.tap0 : T;
-    r.ci_t = u % p.ci_tiles;
-    r.co_t = u / p.ci_tiles;
+    r.ci_t = u % p.ci_tiles; u /= p.ci_tiles;
+    r.co_t = u % p.co_tiles;
+    r.split = u / p.co_tiles;
     return r;
 }
 
@@ -285,21 +288,21 @@ int make_plan(Plan& pl, int N, int H, int W, int Cin_p, int Cout_p, int KH, int 
     pl.ci_tiles = (Cin_p + pl.BN - 1) / pl.BN;
     const int T = 256 / pl.BN;
     const long base_units = (long)pl.co_tiles * pl.ci_tiles * ((KH * KW + T - 1) / T);
-    // Split the pixel reduction so that the units fill whole waves of the 148 persistent CTAs
-    // (a last wave that is mostly empty costs a full unit time), keeping >= 8 K steps per unit.
-    long max_splits = ptiles / 8 > 1 ? ptiles / 8 : 1;
+    // Split the pixel reduction so that the units fill the 148 persistent CTAs.  Cost model (us):
+    // rounds x (K steps per unit x 0.3 + 1) for the GEMM, plus the partial-sum traffic
+    // (workspace written, then read by the reduction kernel) at ~3 TB/s.
+    long max_splits = ptiles / 4 > 1 ? ptiles / 4 : 1;
     if (max_splits > 64) max_splits = 64;
     long splits = 1;
-    double best = -1.0;
+    double best = 1e30;
+    const double out_bytes = 4.0 * KH * KW * (double)pl.co_tiles * BM * (double)pl.ci_tiles * pl.BN;
     for (long sp = 1; sp <= max_splits; ++sp) {
         if (sp > 1 && (sp - 1) * ((ptiles + sp - 1) / sp) >= ptiles) continue;   // would leave an empty split
         const long units = base_units * sp;
-        const double waves = (double)units / imx::kNumSMs;
-        double eff = waves / (double)((units + imx::kNumSMs - 1) / imx::kNumSMs);
-        if (waves < 1.0) eff = waves;                       // not even one full wave
-        // more splits = more partial-sum traffic: require a clear gain to go further
-        const double score = eff - 0.01 * (double)sp;
-        if (score > best + 1e-9) { best = score; splits = sp; }
+        const long rounds = (units + imx::kNumSMs - 1) / imx::kNumSMs;
+        const double ksteps = (double)((ptiles + sp - 1) / sp);
+        const double cost = rounds * (ksteps * 0.3 + 1.0) + (double)sp * out_bytes / 3.0e6;
+        if (cost < best - 1e-9) { best = cost; splits = sp; }
     }
     pl.splits = (int)splits;
     pl.ws_floats = splits * KH * KW * (long)pl.co_tiles * BM * (long)pl.ci_tiles * pl.BN;

@@ -53,6 +53,27 @@ def hbm():
     torch.cuda.synchronize()
 
 
+def epi():
+    """Epilogue-dominated convs: 1x1 256->512, 5x5 64->128, 3x3 512->512 with statistics + residual."""
+    torch.manual_seed(0)
+    dev = 'cuda'
+    x = nhwc(torch.randn(8, 256, 64, 128, device=dev))
+    w1 = ops.pack_conv_weight(torch.randn(512, 256, 1, 1, device=dev) * 0.05)
+    bias = torch.randn(512, device=dev)
+    x2 = nhwc(torch.randn(8, 64, 128, 256, device=dev))
+    w2 = ops.pack_conv_weight(torch.randn(128, 64, 5, 5, device=dev) * 0.05)
+    b2 = torch.randn(128, device=dev)
+    x3 = nhwc(torch.randn(8, 512, 128, 256, device=dev))
+    w3 = ops.pack_conv_weight(torch.randn(512, 512, 3, 3, device=dev) * 0.01)
+    st = torch.zeros(2, 1, 512, device=dev)
+    for _ in range(2):
+        ops.conv2d_fprop(x, w1, 512, 1, 1, 1, 0, bias=bias, flags=ops.EPI_LRELU)
+        ops.conv2d_fprop(x, w1, 512, 1, 1, 1, 0)
+        ops.conv2d_fprop(x2, w2, 128, 5, 5, 1, 2, bias=b2, flags=ops.EPI_RELU)
+        ops.conv2d_fprop(x3, w3, 512, 3, 3, 1, 1, stats=st, residual=x3)
+    torch.cuda.synchronize()
+
+
 if __name__ == '__main__':
-    {'conv': conv, 'hbm': hbm}[sys.argv[1]]()
+    {'conv': conv, 'hbm': hbm, 'epi': epi}[sys.argv[1]]()
     print('ok')
