@@ -135,25 +135,41 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
                 const Unit un = decode_unit<C::T>(u, p);
                 int kb, ke;
                 k_range(un.split, kb, ke);
+                // Per-unit constants hoisted out of the pixel loop (this single thread's
+                // instruction latency is on the critical path: ~6 TMA issues per 512 MMA cycles).
+                int dx[C::T], dy[C::T];
+#pragma unroll
+                for (int t = 0; t < C::T; ++t) {
+                    const int tap = un.tap0 + t;
+                    const int kh = tap / p.KW;
+                    dx[t] = tap - kh * p.KW - p.pad;
+                    dy[t] = kh - p.pad;
+                }
+                const int co0 = un.co_t * BM, ci0 = un.ci_t * BN;
+                int img = kb / tiles_per_img;
+                int rem = kb - img * tiles_per_img;
+                int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
                 for (int k = kb; k < ke; ++k) {
-                    const int img = k / tiles_per_img;
-                    const int rem = k - img * tiles_per_img;
-                    const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
                     const int oy0 = ty * p.th, ox0 = tx * p.tw;
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     mbar_arrive_expect_tx(&full_bar[stage], A_BYTES + un.ntaps * C::TAP_BYTES);
                     uint8_t* sa = smem_a + stage * A_BYTES;
-                    tma_load_4d(sa, &tmap_dy, &full_bar[stage], un.co_t * BM, ox0, oy0, img);
-                    tma_load_4d(sa + BOX_BYTES, &tmap_dy, &full_bar[stage], un.co_t * BM + 64, ox0, oy0, img);
+                    tma_load_4d(sa, &tmap_dy, &full_bar[stage], co0, ox0, oy0, img);
+                    tma_load_4d(sa + BOX_BYTES, &tmap_dy, &full_bar[stage], co0 + 64, ox0, oy0, img);
                     uint8_t* sb = smem_b + stage * C::B_BYTES;
-                    for (int t = 0; t < un.ntaps; ++t) {
-                        const int tap = un.tap0 + t;
-                        const int kh = tap / p.KW, kw = tap - kh * p.KW;
+                    const int ix0 = ox0 * p.stride, iy0 = oy0 * p.stride;
 #pragma unroll
-                        for (int j = 0; j < BN / 64; ++j)
-                            tma_load_4d(sb + t * C::TAP_BYTES + j * BOX_BYTES, &tmap_x, &full_bar[stage],
-                                        un.ci_t * BN + j * 64, ox0 * p.stride + kw - p.pad,
-                                        oy0 * p.stride + kh - p.pad, img);
+                    for (int t = 0; t < C::T; ++t) {
+                        if (t < un.ntaps) {
+#pragma unroll
+                            for (int j = 0; j < BN / 64; ++j)
+                                tma_load_4d(sb + t * C::TAP_BYTES + j * BOX_BYTES, &tmap_x, &full_bar[stage],
+                                            ci0 + j * 64, ix0 + dx[t], iy0 + dy[t], img);
+                        }
+                    }
+                    if (++tx == p.tiles_x) {
+                        tx = 0;
+                        if (++ty == p.tiles_y) { ty = 0; ++img; }
                     }
                     if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                 }
@@ -161,7 +177,6 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            constexpr uint32_t idesc = make_idesc_bf16_f32(BM, BN, 1, 1);   // both operands MN-major
             int stage = 0;
             uint32_t phase = 0;
             int iter = 0;
@@ -174,20 +189,22 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
                 mbar_wait(&tmem_empty[as], aphase ^ 1);
                 tc_fence_after_sync();
                 const uint32_t d_tmem = tmem_base + as * (C::T * BN);
+                // The X boxes of the unit's taps lie back to back in the stage (64-channel groups
+                // BOX_BYTES apart = the descriptor's LBO), so ONE MMA with N = ntaps * BN covers all
+                // taps: accumulator columns [t * BN, (t + 1) * BN) belong to tap t.  Both operands
+                // are MN-major.
+                const uint32_t idesc = make_idesc_bf16_f32(BM, un.ntaps * BN, 1, 1);
                 for (int k = kb; k < ke; ++k) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after_sync();
                     const uint32_t a0 = smem_u32(smem_a + stage * A_BYTES);
                     const uint32_t b0 = smem_u32(smem_b + stage * C::B_BYTES);
-                    for (int t = 0; t < un.ntaps; ++t) {
 #pragma unroll
-                        for (int j = 0; j < BKP / UMMA_K; ++j) {
-                            // 16 pixels = 16 rows of 128 B inside every 64-channel box
-                            const uint64_t da = make_mnmajor_sw128_desc(a0 + j * UMMA_K * 128, 1024, BOX_BYTES);
-                            const uint64_t db = make_mnmajor_sw128_desc(b0 + t * C::TAP_BYTES + j * UMMA_K * 128, 1024,
-                                                                        BOX_BYTES);
-                            umma_bf16_ss(d_tmem + t * BN, da, db, idesc, (k > kb) || (j > 0));
-                        }
+                    for (int j = 0; j < BKP / UMMA_K; ++j) {
+                        // 16 pixels = 16 rows of 128 B inside every 64-channel box
+                        const uint64_t da = make_mnmajor_sw128_desc(a0 + j * UMMA_K * 128, 1024, BOX_BYTES);
+                        const uint64_t db = make_mnmajor_sw128_desc(b0 + j * UMMA_K * 128, 1024, BOX_BYTES);
+                        umma_bf16_ss(d_tmem, da, db, idesc, (k > kb) || (j > 0));
                     }
                     umma_commit(&empty_bar[stage]);
                     if (k == ke - 1) umma_commit(&tmem_full[as]);
