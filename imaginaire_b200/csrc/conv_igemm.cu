@@ -64,6 +64,8 @@ struct ConvArgs {
     int tw_log2, tw, th;
     int tiles_x, tiles_y, tiles_n, total_tiles;
     int kc_blocks;
+    int splits, k_per_split;     // split-K: work item = (tile, split); each split owns k_per_split K steps
+    float* ws;                   // split-K: fp32 [pixels][Cout_p] partial sums (zero-filled by the host code)
     int flags;
     // plain epilogue
     const float* bias;
@@ -150,7 +152,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             // ===== TMA producer =====
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+            for (int item = blockIdx.x; item < p.total_tiles * p.splits; item += gridDim.x) {
+                const int tile = item / p.splits, split = item - tile * p.splits;
                 const int n_tile = tile % p.tiles_n;
                 const int m_tile = tile / p.tiles_n;
                 const int img = m_tile / tiles_per_img;
@@ -159,14 +162,20 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                 const int iy0 = ty * p.th * p.stride - p.pad;
                 const int ix0 = tx * p.tw * p.stride - p.pad;
                 const int n0 = n_tile * BN;
-                for (int tap = 0; tap < taps; ++tap) {
-                    const int kh = tap / p.KW, kw = tap - kh * p.KW;
-                    for (int kc = 0; kc < p.kc_blocks; ++kc) {
-                        mbar_wait(&empty_bar[stage], phase ^ 1);
-                        mbar_arrive_expect_tx(&full_bar[stage], C::STAGE_BYTES);
-                        tma_load_4d(smem_a + stage * A_BYTES, &tmap_a, &full_bar[stage], kc * BK, ix0 + kw, iy0 + kh, img);
-                        tma_load_3d(smem_b + stage * C::B_BYTES, &tmap_b, &full_bar[stage], kc * BK, tap, n0);
-                        if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                const int kb = split * p.k_per_split;
+                const int ke = kb + p.k_per_split < k_iters ? kb + p.k_per_split : k_iters;
+                int tap = kb / p.kc_blocks;
+                int kc = kb - tap * p.kc_blocks;
+                int kh = tap / p.KW, kw = tap - kh * p.KW;
+                for (int k = kb; k < ke; ++k) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    mbar_arrive_expect_tx(&full_bar[stage], C::STAGE_BYTES);
+                    tma_load_4d(smem_a + stage * A_BYTES, &tmap_a, &full_bar[stage], kc * BK, ix0 + kw, iy0 + kh, img);
+                    tma_load_3d(smem_b + stage * C::B_BYTES, &tmap_b, &full_bar[stage], kc * BK, tap, n0);
+                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                    if (++kc == p.kc_blocks) {
+                        kc = 0; ++tap;
+                        if (++kw == p.KW) { kw = 0; ++kh; }
                     }
                 }
             }
@@ -178,13 +187,16 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             int stage = 0;
             uint32_t phase = 0;
             int iter = 0;
-            for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++iter) {
+            for (int item = blockIdx.x; item < p.total_tiles * p.splits; item += gridDim.x, ++iter) {
+                const int split = item % p.splits;
+                const int kb = split * p.k_per_split;
+                const int ke = kb + p.k_per_split < k_iters ? kb + p.k_per_split : k_iters;
                 const int as = iter & 1;
                 const uint32_t aphase = (iter >> 1) & 1;
                 mbar_wait(&tmem_empty[as], aphase ^ 1);
                 tc_fence_after_sync();
                 const uint32_t d_tmem = tmem_base + as * (MT * BN);
-                for (int k = 0; k < k_iters; ++k) {
+                for (int k = kb; k < ke; ++k) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after_sync();
                     const uint64_t db = make_kmajor_sw128_desc(smem_u32(smem_b + stage * C::B_BYTES));
@@ -194,11 +206,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 #pragma unroll
                         for (int j = 0; j < BK / UMMA_K; ++j) {
                             // advance 16 bf16 = 32 bytes along K inside the swizzle row: +2 in (addr >> 4)
-                            umma_bf16_ss(d_tmem + mt * BN, da + 2 * j, db + 2 * j, idesc, (k | j) != 0);
+                            umma_bf16_ss(d_tmem + mt * BN, da + 2 * j, db + 2 * j, idesc, (k > kb) || (j != 0));
                         }
                     }
                     umma_commit(&empty_bar[stage]);
-                    if (k == k_iters - 1) umma_commit(&tmem_full[as]);
+                    if (k == ke - 1) umma_commit(&tmem_full[as]);
                     if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                 }
             }
@@ -208,7 +220,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         const int q = warp & 3;                 // TMEM lane quarter owned by this warp
         const int row = q * 32 + lane;          // row of a 128-pixel sub-tile
         int iter = 0;
-        for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++iter) {
+        for (int item = blockIdx.x; item < p.total_tiles * p.splits; item += gridDim.x, ++iter) {
+            const int tile = item / p.splits;
             const int as = iter & 1;
             const uint32_t aphase = (iter >> 1) & 1;
             const int n_tile = tile % p.tiles_n;
@@ -218,6 +231,40 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
             const int n0 = n_tile * BN;
 
+            if (kMode == 0 && p.splits > 1) {
+                // split-K: add the raw fp32 partial sums into the workspace; bias / activation /
+                // residual are applied by the finishing kernel once every split has landed.
+                mbar_wait(&tmem_full[as], aphase);
+                tc_fence_after_sync();
+#pragma unroll 1
+                for (int mt = 0; mt < MT; ++mt) {
+                    const int prow = mt * BM + row;
+                    const int pr = prow >> p.tw_log2, pc = prow & (p.tw - 1);
+                    const int oy = ty * p.th + pr, ox = tx * p.tw + pc;
+                    const bool valid = (oy < p.Ho) && (ox < p.Wo);
+                    const size_t pix = ((size_t)img * p.Ho + oy) * p.Wo + ox;
+                    const uint32_t t_acc = tmem_base + as * (MT * BN) + mt * BN + (static_cast<uint32_t>(q * 32) << 16);
+#pragma unroll 1
+                    for (int ch = 0; ch < BN / 32; ++ch) {
+                        uint32_t v[32];
+                        tmem_ld_32x32(t_acc + ch * 32, v);
+                        tmem_ld_wait();
+                        if (ch == BN / 32 - 1 && mt == MT - 1) {
+                            tc_fence_before_sync();
+                            mbar_arrive(&tmem_empty[as]);
+                        }
+                        const int nb = n0 + ch * 32;
+                        if (!valid || nb >= p.Cout_p) continue;
+                        float* dst = p.ws + pix * p.Cout_p + nb;
+#pragma unroll
+                        for (int g = 0; g < 8; ++g)
+                            if (nb + g * 4 < p.Cout_p)
+                                imx::red_add_v4(dst + g * 4, __uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1]),
+                                                __uint_as_float(v[4 * g + 2]), __uint_as_float(v[4 * g + 3]));
+                    }
+                }
+                continue;
+            }
             // Per-channel epilogue coefficients of this tile go to shared memory once (double
             // buffered by accumulator stage), so the per-element work reads them as broadcast
             // LDS instead of 32 dependent global loads per chunk.
@@ -487,7 +534,8 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const ConvArgs& a, cuda
         if (e != cudaSuccess) return imx::set_error((int)e, "conv_igemm: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
         attr_set = true;
     }
-    const int grid = a.total_tiles < num_sms() ? a.total_tiles : num_sms();
+    const long items = (long)a.total_tiles * a.splits;
+    const int grid = items < num_sms() ? (int)items : num_sms();
     kern<<<grid, kThreads, C::SMEM_BYTES, stream>>>(ta, tb, a);
     return imx::check_launch("conv_igemm");
 }
@@ -513,6 +561,9 @@ int setup(ConvArgs& a, CUtensorMap& ta, CUtensorMap& tb, const void* x, const vo
     if (total > 0x7fffffffL) return imx::set_error(IMX_ERR_TOO_LARGE, "conv_igemm: too many tiles");
     a.total_tiles = (int)total;
     a.kc_blocks = (Cin_p + BK - 1) / BK;
+    a.splits = 1;
+    a.k_per_split = KH * KW * a.kc_blocks;
+    a.ws = nullptr;
 
     const uint64_t dims_a[4] = {(uint64_t)Cin_p, (uint64_t)W, (uint64_t)H, (uint64_t)N};
     const uint64_t str_a[3] = {(uint64_t)Cin_p * 2, (uint64_t)W * Cin_p * 2, (uint64_t)H * W * Cin_p * 2};
@@ -532,54 +583,173 @@ using imx::aligned16;
 
 }  // namespace
 
-extern "C" int imx_conv2d_igemm_fprop_bf16(const imx_bf16* x, const imx_bf16* wpk, const float* bias,
-                                           const imx_bf16* residual, void* out, float* stats,
-                                           int N, int H, int W, int Cin_p,
-                                           int Cout, int Cout_p, int KH, int KW,
-                                           int stride, int pad, int flags, imx_stream_t stream) {
-    IMX_REQUIRE(x && wpk && out, "conv2d_fprop: null pointer");
+namespace {
+
+// Applies bias / residual / activation to the split-K sums and stores the output tensor.
+__global__ void splitk_finish_kernel(const float* __restrict__ ws, const float* __restrict__ bias,
+                                     const uint16_t* __restrict__ residual, void* __restrict__ out,
+                                     long pixels, int Cout, int Cout_p, int flags) {
+    const int c4n = Cout_p / 4;
+    const long total = pixels * c4n;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % c4n) * 4;
+        const long pix = i / c4n;
+        const float4 v4 = __ldg(reinterpret_cast<const float4*>(ws) + i);
+        float f[4] = {v4.x, v4.y, v4.z, v4.w};
+        if (flags & IMX_EPI_BIAS) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (c + j < Cout) f[j] += __ldg(bias + c + j);
+        }
+        if (flags & IMX_EPI_RESIDUAL) {
+            const uint2 r = __ldg(reinterpret_cast<const uint2*>(residual + pix * Cout_p + c));
+            f[0] += imx::bf16_lo(r.x); f[1] += imx::bf16_hi(r.x);
+            f[2] += imx::bf16_lo(r.y); f[3] += imx::bf16_hi(r.y);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if (flags & IMX_EPI_LRELU) f[j] = f[j] > 0.0f ? f[j] : 0.2f * f[j];
+            if (flags & IMX_EPI_RELU) f[j] = fmaxf(f[j], 0.0f);
+            if (flags & IMX_EPI_TANH) f[j] = tanhf(f[j]);
+        }
+        if (flags & IMX_EPI_OUT_F32)
+            reinterpret_cast<float4*>(out)[i] = make_float4(f[0], f[1], f[2], f[3]);
+        else
+            reinterpret_cast<uint2*>(out)[i] = make_uint2(imx::pack_bf16(f[0], f[1]), imx::pack_bf16(f[2], f[3]));
+    }
+}
+
+struct FpropPlan { int BN, MT, splits, k_per_split; long ws_bytes; };
+
+// Tile shape and split-K factor from a small cost model, in units of one K step of a full-rate
+// tile (~0.3 us).  Narrow channel tiles (BN <= 128) with 128-pixel tiles are operand-bandwidth
+// bound (1.7x slower per pixel), 256-pixel tiles are not.  Layers with fewer tiles than SMs split
+// the K loop (taps x channel blocks) over several CTAs, which add fp32 partial sums into a
+// workspace; that costs a memset and a finishing kernel (~15 units).
+void plan_fprop(FpropPlan& pl, int N, int H, int W, int Cin_p, int Cout, int Cout_p, int KH, int KW, int stride, int pad,
+                int flags, bool allow_split) {
+    pl.BN = Cout_p > 128 ? 256 : (Cout_p > 64 ? 128 : (Cout_p > 32 ? 64 : 32));
+    const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
+    const long k_iters = (long)KH * KW * ((Cin_p + BK - 1) / BK);
+    const int tiles_n = (Cout + pl.BN - 1) / pl.BN;
+    const bool mt2_ok = pl.BN <= 128 &&
+                        (stride == 1 || Wo >= 128 || ((256 / (Wo < 128 ? Wo : 128)) - 1) * stride + 1 <= 256);
+    if (flags & IMX_EPI_STATS) allow_split = false;
+    double best = 1e30;
+    pl.MT = 1; pl.splits = 1;
+    for (int mt = 1; mt <= (mt2_ok ? 2 : 1); ++mt) {
+        int tw = 128;
+        while (tw > 8 && tw > Wo) tw >>= 1;
+        const int th = mt * BM / tw;
+        const long tiles = (long)N * ((Wo + tw - 1) / tw) * ((Ho + th - 1) / th) * tiles_n;
+        // K-step time relative to a 128 x 256 tile: the larger of the MMA time and the operand
+        // fill time (A: mt x 16 KB, B: BN / 8 KB against 48 KB); measured 0.85 for BN = 128, MT = 1.
+        const double t_mma = mt * pl.BN / 256.0, t_fill = (mt * 16.0 + pl.BN / 8.0) / 48.0 * 1.27;
+        const double t_step = t_mma > t_fill ? t_mma : t_fill;
+        const double ws_units = (double)N * Ho * Wo * Cout_p * 4.0 / 2.0e6 / 0.3;   // one pass over the workspace
+        for (int sp = 1; sp <= (allow_split && tiles < imx::kNumSMs ? 16 : 1); ++sp) {
+            const long per = (k_iters + sp - 1) / sp;
+            if (sp > 1 && (per < 8 || (long)(sp - 1) * per >= k_iters)) continue;
+            const long rounds = (tiles * sp + imx::kNumSMs - 1) / imx::kNumSMs;
+            const double cost = rounds * (per * t_step + 2.0) + (sp > 1 ? 15.0 + ws_units * (sp + 2) : 0.0);
+            if (cost < best - 1e-9) { best = cost; pl.MT = mt; pl.splits = sp; }
+        }
+    }
+    pl.k_per_split = (int)((k_iters + pl.splits - 1) / pl.splits);
+    pl.ws_bytes = pl.splits > 1 ? (long)N * Ho * Wo * Cout_p * 4 : 0;
+}
+
+int check_fprop_args(int N, int H, int W, int Cin_p, int Cout, int Cout_p, int KH, int KW, int stride, int pad) {
     IMX_REQUIRE(N >= 0 && H > 0 && W > 0, "conv2d_fprop: bad input size");
     IMX_REQUIRE(Cin_p > 0 && Cin_p % 8 == 0, "conv2d_fprop: Cin_p (%d) must be a positive multiple of 8", Cin_p);
     IMX_REQUIRE(Cout > 0 && Cout_p >= Cout && Cout_p % 8 == 0, "conv2d_fprop: Cout_p (%d) must be >= Cout (%d) and a multiple of 8", Cout_p, Cout);
     IMX_REQUIRE(KH > 0 && KW > 0 && KH <= 16 && KW <= 16, "conv2d_fprop: bad kernel size");
     IMX_REQUIRE(stride >= 1 && stride <= 2 && pad >= 0, "conv2d_fprop: stride must be 1 or 2, pad >= 0");
+    return IMX_OK;
+}
+
+int fprop_impl(const imx_bf16* x, const imx_bf16* wpk, const float* bias, const imx_bf16* residual, void* out,
+               float* stats, void* workspace, int64_t workspace_bytes, int N, int H, int W, int Cin_p, int Cout,
+               int Cout_p, int KH, int KW, int stride, int pad, int flags, imx_stream_t stream) {
+    IMX_REQUIRE(x && wpk && out, "conv2d_fprop: null pointer");
+    int rc = check_fprop_args(N, H, W, Cin_p, Cout, Cout_p, KH, KW, stride, pad);
+    if (rc) return rc;
     IMX_REQUIRE(!(flags & IMX_EPI_BIAS) || bias, "conv2d_fprop: bias flag without bias");
     IMX_REQUIRE(!(flags & IMX_EPI_RESIDUAL) || residual, "conv2d_fprop: residual flag without residual");
     IMX_REQUIRE(!(flags & IMX_EPI_STATS) || stats, "conv2d_fprop: stats flag without stats buffer");
     IMX_REQUIRE(aligned16(x) && aligned16(wpk) && aligned16(out) && aligned16(residual), "conv2d_fprop: pointers must be 16-byte aligned");
     if (N == 0) return IMX_OK;
-    const int BN = Cout_p > 128 ? 256 : (Cout_p > 64 ? 128 : (Cout_p > 32 ? 64 : 32));
+    FpropPlan pl;
+    plan_fprop(pl, N, H, W, Cin_p, Cout, Cout_p, KH, KW, stride, pad, flags, workspace != nullptr);
+    if (pl.splits > 1) {
+        IMX_REQUIRE(workspace_bytes >= pl.ws_bytes && aligned16(workspace),
+                    "conv2d_fprop: split-K workspace too small (%lld bytes given, %lld needed) or misaligned",
+                    (long long)workspace_bytes, (long long)pl.ws_bytes);
+    }
+    const int BN = pl.BN, MT = pl.MT;
     ConvArgs a{};
     CUtensorMap ta, tb;
-    // Narrow channel tiles (BN <= 128) need more operand bytes per MMA cycle than L2 delivers, so
-    // they run ~1.7x slower per pixel with 128-pixel tiles than with 256-pixel tiles (two MMAs
-    // per B tile).  Whenever there is more than one wave of 128-pixel tiles the 256-pixel tiling
-    // is at least as fast even counting its coarser wave quantisation.
-    int MT = 1;
-    if (BN <= 128) {
-        const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
-        const long tiles128 = (long)N * ((Ho * (long)Wo + 127) / 128) * ((Cout + BN - 1) / BN);
-        if (tiles128 > imx::kNumSMs && (stride == 1 || Wo >= 128 || ((256 / (Wo < 128 ? Wo : 128)) - 1) * stride + 1 <= 256))
-            MT = 2;
-    }
-    int rc = setup(a, ta, tb, x, wpk, N, H, W, Cin_p, Cout, KH, KW, stride, pad, BN, MT);
+    rc = setup(a, ta, tb, x, wpk, N, H, W, Cin_p, Cout, KH, KW, stride, pad, BN, MT);
     if (rc) return rc;
     a.Cout = Cout; a.Cout_p = Cout_p; a.flags = flags;
     a.bias = bias; a.residual = residual; a.out = out; a.stats = stats;
+    a.splits = pl.splits; a.k_per_split = pl.k_per_split; a.ws = reinterpret_cast<float*>(workspace);
     cudaStream_t s = (cudaStream_t)stream;
+    if (pl.splits > 1) {
+        cudaError_t e = cudaMemsetAsync(workspace, 0, (size_t)pl.ws_bytes, s);
+        if (e != cudaSuccess) return imx::set_error((int)e, "conv2d_fprop: workspace memset: %s", cudaGetErrorString(e));
+    }
     if (MT == 2) {
         switch (BN) {
-            case 128: return launch<128, 0, 2>(ta, tb, a, s);
-            case 64: return launch<64, 0, 2>(ta, tb, a, s);
-            default: return launch<32, 0, 2>(ta, tb, a, s);
+            case 128: rc = launch<128, 0, 2>(ta, tb, a, s); break;
+            case 64: rc = launch<64, 0, 2>(ta, tb, a, s); break;
+            default: rc = launch<32, 0, 2>(ta, tb, a, s); break;
+        }
+    } else {
+        switch (BN) {
+            case 256: rc = launch<256, 0>(ta, tb, a, s); break;
+            case 128: rc = launch<128, 0>(ta, tb, a, s); break;
+            case 64: rc = launch<64, 0>(ta, tb, a, s); break;
+            default: rc = launch<32, 0>(ta, tb, a, s); break;
         }
     }
-    switch (BN) {
-        case 256: return launch<256, 0>(ta, tb, a, s);
-        case 128: return launch<128, 0>(ta, tb, a, s);
-        case 64: return launch<64, 0>(ta, tb, a, s);
-        default: return launch<32, 0>(ta, tb, a, s);
-    }
+    if (rc || pl.splits == 1) return rc;
+    const long pixels = (long)N * a.Ho * a.Wo;
+    long blocks = (pixels * (Cout_p / 4) + 255) / 256;
+    if (blocks > 8L * imx::kNumSMs) blocks = 8L * imx::kNumSMs;
+    splitk_finish_kernel<<<(int)blocks, 256, 0, s>>>(a.ws, bias, reinterpret_cast<const uint16_t*>(residual), out, pixels,
+                                                     Cout, Cout_p, flags);
+    return imx::check_launch("conv2d_fprop_splitk_finish");
+}
+
+}  // namespace
+
+extern "C" int imx_conv2d_igemm_fprop_bf16(const imx_bf16* x, const imx_bf16* wpk, const float* bias,
+                                           const imx_bf16* residual, void* out, float* stats,
+                                           int N, int H, int W, int Cin_p,
+                                           int Cout, int Cout_p, int KH, int KW,
+                                           int stride, int pad, int flags, imx_stream_t stream) {
+    return fprop_impl(x, wpk, bias, residual, out, stats, nullptr, 0, N, H, W, Cin_p, Cout, Cout_p, KH, KW, stride, pad,
+                      flags, stream);
+}
+
+extern "C" int64_t imx_conv2d_fprop_workspace_bytes(int N, int H, int W, int Cin_p, int Cout, int Cout_p,
+                                                    int KH, int KW, int stride, int pad, int flags) {
+    if (check_fprop_args(N, H, W, Cin_p, Cout, Cout_p, KH, KW, stride, pad)) return -1;
+    if (N == 0) return 0;
+    FpropPlan pl;
+    plan_fprop(pl, N, H, W, Cin_p, Cout, Cout_p, KH, KW, stride, pad, flags, true);
+    return pl.ws_bytes;
+}
+
+extern "C" int imx_conv2d_igemm_fprop_splitk_bf16(const imx_bf16* x, const imx_bf16* wpk, const float* bias,
+                                                  const imx_bf16* residual, void* out, float* stats,
+                                                  void* workspace, int64_t workspace_bytes,
+                                                  int N, int H, int W, int Cin_p,
+                                                  int Cout, int Cout_p, int KH, int KW,
+                                                  int stride, int pad, int flags, imx_stream_t stream) {
+    return fprop_impl(x, wpk, bias, residual, out, stats, workspace, workspace_bytes, N, H, W, Cin_p, Cout, Cout_p, KH, KW,
+                      stride, pad, flags, stream);
 }
 
 extern "C" int imx_spade_gb_conv_modulate_bf16(const imx_bf16* hidden, const imx_bf16* wgb,

@@ -122,6 +122,70 @@ stats_kernel(const uint4* __restrict__ x, float* __restrict__ sum, float* __rest
     }
 }
 
+// dx = dy * act'(y) for an activation that was fused into a conv epilogue (y = act(pre)), plus
+// the per-channel sum of dx (the conv's bias gradient) in the same pass.
+__global__ void __launch_bounds__(kThreads)
+act_bwd_sum_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y, uint4* __restrict__ dx,
+                   float* __restrict__ sum, long NP, int cg, int tpr, int rows, float slope) {
+    __shared__ float red[kThreads][9];
+    const int tid = threadIdx.x;
+    const int ci = tid % tpr, r = tid / tpr;
+    const bool active = r < rows;
+    const long per = (NP + gridDim.x - 1) / gridDim.x;
+    const long p0 = (long)blockIdx.x * per;
+    const long p1 = p0 + per < NP ? p0 + per : NP;
+    for (int c8 = ci; c8 < cg; c8 += tpr) {
+        float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (active) {
+            auto one = [&](const uint4 gv, const uint4 yv, long p) {
+                float g[8], yy[8];
+                unpack8(gv, g);
+                unpack8(yv, yy);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    g[k] = yy[k] > 0.0f ? g[k] : g[k] * slope;
+                }
+                const uint4 o = pack8(g);
+                imx::stg_stream(dx + (size_t)p * cg + c8, o);
+                // the sum is taken over the values as stored, like a separate pass over dx would
+                unpack8(o, g);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) s[k] += g[k];
+            };
+            long p = p0 + r;
+            for (; p + 3L * rows < p1; p += 4L * rows) {
+                uint4 gv[4], yv[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    gv[u] = imx::ldg_stream(dy + (size_t)(p + (long)u * rows) * cg + c8);
+                    yv[u] = imx::ldg_stream(y + (size_t)(p + (long)u * rows) * cg + c8);
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) one(gv[u], yv[u], p + (long)u * rows);
+            }
+            for (; p < p1; p += rows)
+                one(imx::ldg_stream(dy + (size_t)p * cg + c8), imx::ldg_stream(y + (size_t)p * cg + c8), p);
+        }
+        if (sum) {
+            __syncthreads();
+#pragma unroll
+            for (int k = 0; k < 8; ++k) red[tid][k] = s[k];
+            __syncthreads();
+            if (r == 0) {
+                float acc[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) acc[k] = red[tid][k];
+                for (int rr = 1; rr < rows; ++rr)
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) acc[k] += red[tid + rr * tpr][k];
+                float* dst = sum + c8 * 8;
+                imx::red_add_v4(dst, acc[0], acc[1], acc[2], acc[3]);
+                imx::red_add_v4(dst + 4, acc[4], acc[5], acc[6], acc[7]);
+            }
+        }
+    }
+}
+
 __global__ void finalize_kernel(const float* __restrict__ sum, const float* __restrict__ sumsq,
                                 float count, float eps, float* __restrict__ mean,
                                 float* __restrict__ rstd, float* running_mean, float* running_var,
@@ -163,6 +227,7 @@ struct ModArgs {
     const void* beta;
     int N, H, W, C;
     int per_instance, gb_mode, act, up2x;
+    float* gbsum;   // backward pass 1, gb_mode 0: optional (2, C) per-channel sums of dgamma / dbeta
 };
 
 // Per-thread channel parameters: xn = x * rs + mr (inner norm), xh = xn * w + b (affine).
@@ -291,7 +356,7 @@ modulate_kernel(ModArgs a, uint4* __restrict__ out0, void* __restrict__ out1, vo
                             o1[k] = dpre;        // dbeta
                             r1[k] += dxh;                  // -> dbias of the inner norm
                             r2[k] = fmaf(dxh, xn, r2[k]);  // -> dweight of the inner norm
-                            if (a.gb_mode == 1) { ag[k] += o0[k]; ab[k] += o1[k]; }
+                            if (a.gb_mode == 1 || a.gbsum) { ag[k] += o0[k]; ab[k] += o1[k]; }
                         } else {
                             // dx = rstd * w * (dxh - mean(dxh) - xn * mean(dxh * xn))
                             o0[k] = rs[k] * ww[k] * (dxh - m1[k] - xn * m2[k]);
@@ -311,7 +376,7 @@ modulate_kernel(ModArgs a, uint4* __restrict__ out0, void* __restrict__ out1, vo
         }
         if (kMode == 1) {
             // block-level reduction of r1, r2 (and adaptive dgamma/dbeta) over the row groups
-            for (int pass = 0; pass < (a.gb_mode == 1 ? 2 : 1); ++pass) {
+            for (int pass = 0; pass < ((a.gb_mode == 1 || a.gbsum) ? 2 : 1); ++pass) {
                 __syncthreads();
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
@@ -335,6 +400,14 @@ modulate_kernel(ModArgs a, uint4* __restrict__ out0, void* __restrict__ out1, vo
                         imx::red_add_v4(d0 + 4, acc[4], acc[5], acc[6], acc[7]);
                         imx::red_add_v4(d1, acc[8], acc[9], acc[10], acc[11]);
                         imx::red_add_v4(d1 + 4, acc[12], acc[13], acc[14], acc[15]);
+                    } else if (a.gb_mode == 0) {
+                        // sums over all pixels of the batch = bias gradients of the gamma / beta convs
+                        float* dg = a.gbsum + c;
+                        float* db = a.gbsum + a.C + c;
+                        imx::red_add_v4(dg, acc[0], acc[1], acc[2], acc[3]);
+                        imx::red_add_v4(dg + 4, acc[4], acc[5], acc[6], acc[7]);
+                        imx::red_add_v4(db, acc[8], acc[9], acc[10], acc[11]);
+                        imx::red_add_v4(db + 4, acc[12], acc[13], acc[14], acc[15]);
                     } else {
                         float* dg = reinterpret_cast<float*>(out1) + (size_t)n * a.C + c;
                         float* db = reinterpret_cast<float*>(out2) + (size_t)n * a.C + c;
@@ -392,6 +465,20 @@ extern "C" int imx_channel_sum_nhwc_bf16(const imx_bf16* x, float* out, int NP, 
     return imx::check_launch("channel_sum");
 }
 
+extern "C" int imx_act_bwd_bias_nhwc_bf16(const imx_bf16* dy, const imx_bf16* y, imx_bf16* dx, float* bias_grad,
+                                          int64_t NP, int C, int act, imx_stream_t stream) {
+    IMX_REQUIRE(dy && y && dx, "act_bwd_bias: null pointer");
+    IMX_REQUIRE(NP >= 0 && C >= 0 && C % 8 == 0, "act_bwd_bias: C (%d) must be a non-negative multiple of 8", C);
+    IMX_REQUIRE(act == 1 || act == 2, "act_bwd_bias: act must be 1 (LeakyReLU 0.2) or 2 (ReLU)");
+    if (NP * C == 0) return IMX_OK;
+    const RowMap m = make_rowmap(C);
+    dim3 grid(pick_blocks(NP, m.rows, 1, 4), 1);
+    act_bwd_sum_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(y), reinterpret_cast<uint4*>(dx), bias_grad, NP,
+        m.cg, m.tpr, m.rows, act == 1 ? 0.2f : 0.0f);
+    return imx::check_launch("act_bwd_bias");
+}
+
 extern "C" int imx_bn_finalize(const float* sum, const float* sumsq, float count, float eps,
                                float* mean, float* rstd, float* running_mean, float* running_var,
                                float momentum, int G, int C, imx_stream_t stream) {
@@ -419,7 +506,7 @@ extern "C" int imx_spade_modulate_fwd(const imx_bf16* x, const float* mean, cons
     if ((long)N * H * W * C == 0) return IMX_OK;
     const RowMap m = make_rowmap(C);
     ModArgs a{reinterpret_cast<const uint4*>(x), nullptr, mean, rstd, w, b, gamma, beta,
-              N, H, W, C, stats_per_instance, gb_mode, act, up2x};
+              N, H, W, C, stats_per_instance, gb_mode, act, up2x, nullptr};
     dim3 grid(pick_blocks((long)H * W, m.rows, N, 6), N);
     modulate_kernel<0><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
         a, reinterpret_cast<uint4*>(y), nullptr, nullptr, nullptr, 0.0f, 1, m.cg, m.tpr, m.rows);
@@ -430,7 +517,7 @@ extern "C" int imx_spade_modulate_bwd_reduce(const imx_bf16* x, const imx_bf16* 
                                              const float* mean, const float* rstd,
                                              const float* w, const float* b,
                                              const void* gamma, const void* beta,
-                                             void* dgamma, void* dbeta, float* red,
+                                             void* dgamma, void* dbeta, float* red, float* gb_sums,
                                              int N, int H, int W, int C,
                                              int stats_per_instance, int gb_mode, int act,
                                              imx_stream_t stream) {
@@ -441,7 +528,7 @@ extern "C" int imx_spade_modulate_bwd_reduce(const imx_bf16* x, const imx_bf16* 
     if ((long)N * H * W * C == 0) return IMX_OK;
     const RowMap m = make_rowmap(C);
     ModArgs a{reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(dy), mean, rstd, w, b, gamma, beta,
-              N, H, W, C, stats_per_instance, gb_mode, act, 0};
+              N, H, W, C, stats_per_instance, gb_mode, act, 0, gb_mode == 0 ? gb_sums : nullptr};
     dim3 grid(pick_blocks((long)H * W, m.rows, N), N);
     modulate_kernel<1><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
         a, nullptr, dgamma, dbeta, red, 0.0f, 1, m.cg, m.tpr, m.rows);
@@ -463,7 +550,7 @@ extern "C" int imx_spade_modulate_bwd_dx(const imx_bf16* x, const imx_bf16* dy,
     if ((long)N * H * W * C == 0) return IMX_OK;
     const RowMap m = make_rowmap(C);
     ModArgs a{reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(dy), mean, rstd, w, b, gamma, beta,
-              N, H, W, C, stats_per_instance, gb_mode, act, 0};
+              N, H, W, C, stats_per_instance, gb_mode, act, 0, nullptr};
     dim3 grid(pick_blocks((long)H * W, m.rows, N, 6), N);
     modulate_kernel<2><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
         a, reinterpret_cast<uint4*>(dx), nullptr, nullptr, const_cast<float*>(red),

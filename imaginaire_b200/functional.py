@@ -142,10 +142,19 @@ class _Conv2d(torch.autograd.Function):
     def forward(ctx, x, weight, bias, residual, stride, pad, act, stats, inv_sigma, u, v):
         cout, cin, kh, kw = weight.shape
         cin_p = x.shape[1]
-        wpk = _packed_weight(weight, cin_p, False, inv_sigma)
         flags = {ops.ACT_NONE: 0, ops.ACT_LRELU: ops.EPI_LRELU, ops.ACT_RELU: ops.EPI_RELU}[act]
-        y = ops.conv2d_fprop(x, wpk, cout, kh, kw, stride, pad, bias=bias, residual=residual, flags=flags,
-                             stats=stats)
+        if _small_cin(cin_p, kh, kw):
+            # few input channels: patches (im2col) + a 1x1 GEMM with K = taps * 8
+            col = ops.im2col_c8(x, kh, kw, stride, pad)
+            wpk = _packed_weight(weight, 8, False, inv_sigma).view(cout, 1, 1, kh * kw * 8)
+            y = ops.conv2d_fprop(col, wpk, cout, 1, 1, 1, 0, bias=bias, residual=residual, flags=flags, stats=stats)
+        elif _small_cout(cout, kh, kw, stride, pad) and act == ops.ACT_NONE and residual is None and stats is None:
+            # few output channels: per-tap products as a 1x1 GEMM, then the shifted sum over taps
+            y = _small_cout_conv(x, weight.detach().permute(2, 3, 0, 1), bias, kh, kw, pad, cout, inv_sigma)
+        else:
+            wpk = _packed_weight(weight, cin_p, False, inv_sigma)
+            y = ops.conv2d_fprop(x, wpk, cout, kh, kw, stride, pad, bias=bias, residual=residual, flags=flags,
+                                 stats=stats)
         ctx.stride, ctx.pad, ctx.act = stride, pad, act
         ctx.geom = (cout, cin, kh, kw, x.shape[2], x.shape[3])
         ctx.has_bias = bias is not None
@@ -159,22 +168,58 @@ class _Conv2d(torch.autograd.Function):
         x, weight, y, inv_sigma, u, v = ctx.saved_tensors
         cout, cin, kh, kw, h, w = ctx.geom
         dy = _as_nhwc(dy)
+        want_db = ctx.has_bias and ctx.needs_input_grad[2]
+        chsum = getattr(dy, '_imx_chsum', None)     # left by the kernel that produced dy, if it had it for free
         if y is not None:
-            dy = _act_backward(dy, y, ctx.act)
+            dy, chsum = ops.act_bwd_bias(dy, y, ctx.act, want_db)
         dx = dw = db = dres = None
         if ctx.needs_input_grad[0]:
             dx = conv2d_dgrad(dy, weight, ctx.stride, ctx.pad, h, w, x.shape[1], inv_sigma)
         if ctx.needs_input_grad[1]:
-            dw = ops.conv2d_wgrad(x, dy, cin, cout, kh, kw, ctx.stride, ctx.pad)   # d/d(w * inv_sigma)
+            dw = _conv2d_wgrad(x, dy, cin, cout, kh, kw, ctx.stride, ctx.pad)   # d/d(w * inv_sigma)
             if inv_sigma is not None:
                 # W_eff = W / sigma, sigma = u^T W v (u, v constants):
                 # dL/dW = G / sigma - (<G, W> / sigma^2) u v^T
                 ops.spectral_norm_weight_grad_(dw, weight.detach(), u, v, inv_sigma)
-        if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = ops.channel_sum(dy)[:cout]   # over the padded channels, then the logical ones
+        if want_db:
+            # over the padded channels, then the logical ones
+            db = (chsum if chsum is not None else ops.channel_sum(dy))[:cout]
         if ctx.has_res and ctx.needs_input_grad[3]:
             dres = dy
         return dx, dw, db, dres, None, None, None, None, None, None, None
+
+
+def _small_cin(cin_p, kh, kw):
+    return cin_p == 8 and kh * kw > 1
+
+
+def _small_cout(cout, kh, kw, stride, pad):
+    return cout <= 8 and kh == kw and kh > 1 and stride == 1 and 2 * pad == kh - 1
+
+
+def _small_cout_conv(x, w_taps, bias, kh, kw, pad, cout, inv_sigma):
+    """'same' convolution with <= 8 output channels.  w_taps: (KH, KW, Cout, Cin) view of the filter.
+    P[p][(tap, co)] = x[p] . w[tap, co, :] on the tensor cores (fp32 out), then the shifted tap sum."""
+    cin = w_taps.shape[3]
+    rows = w_taps.reshape(kh * kw * cout, cin, 1, 1)
+    wpk = ops.pack_conv_weight(rows, inv_sigma, cin_p=x.shape[1])
+    prod = ops.conv2d_fprop(x, wpk, kh * kw * cout, 1, 1, 1, 0, out_f32=True)
+    return ops.shift_add_taps(prod, bias, kh, kw, pad, cout)
+
+
+def _conv2d_wgrad(x, dy, cin, cout, kh, kw, stride, pad):
+    """Filter gradient [Cout, Cin, KH, KW] (fp32) of conv2d(x) given dy."""
+    if _small_cin(x.shape[1], kh, kw):
+        col = ops.im2col_c8(x, kh, kw, stride, pad)
+        g = ops.conv2d_wgrad(col, dy, kh * kw * 8, cout, 1, 1, 1, 0)            # [Cout, (tap, ci)]
+        return g.view(cout, kh, kw, 8).permute(0, 3, 1, 2)[:, :cin].contiguous()
+    if dy.shape[1] == 8 and _small_cout(cout, kh, kw, stride, pad):
+        # dW[co][ci][t] = sum_p x[p][ci] * dy[p - t + pad][co]: patches of dy with flipped taps
+        cin_p = x.shape[1]
+        col = ops.im2col_c8(dy, kh, kw, 1, kh - 1 - pad)
+        g = ops.conv2d_wgrad(col, x, kh * kw * 8, cin_p, 1, 1, 1, 0)            # [Cin_p, (flipped tap, co)]
+        return g.view(cin_p, kh, kw, 8).flip(1, 2).permute(3, 0, 1, 2)[:cout, :cin].contiguous()
+    return ops.conv2d_wgrad(x, dy, cin, cout, kh, kw, stride, pad)
 
 
 def conv2d_dgrad(dy, weight, stride, pad, h, w, cin_p, inv_sigma=None):
@@ -182,7 +227,8 @@ def conv2d_dgrad(dy, weight, stride, pad, h, w, cin_p, inv_sigma=None):
     spatially flipped filter.  A stride-2 forward is handled by zero-insertion."""
     cout, cin, kh, kw = weight.shape
     cout_p = dy.shape[1]
-    wt = _packed_weight(weight, cout_p, True, inv_sigma)   # [Cin, KH, KW, Cout_p]
+    if kh != kw:
+        raise RuntimeError('conv2d_dgrad: only square kernels are supported')
     if stride != 1:
         n, _, ho, wo = dy.shape
         dh = (ho - 1) * stride + 1 + (h + 2 * pad - kh) % stride
@@ -190,9 +236,18 @@ def conv2d_dgrad(dy, weight, stride, pad, h, w, cin_p, inv_sigma=None):
         z = torch.zeros((n, dh, dw_, cout_p), dtype=torch.bfloat16, device=dy.device).permute(0, 3, 1, 2)
         z[:, :, 0:(ho - 1) * stride + 1:stride, 0:(wo - 1) * stride + 1:stride] = dy
         dy = z
-    if kh != kw:
-        raise RuntimeError('conv2d_dgrad: only square kernels are supported')
-    return ops.conv2d_fprop(dy, wt, cin, kh, kw, 1, kh - 1 - pad, cout_p=cin_p)
+    pad_t = kh - 1 - pad
+    if _small_cin(cout_p, kh, kw):
+        # dy has 8 channels (e.g. the to-RGB layer): patches of dy + a 1x1 GEMM
+        col = ops.im2col_c8(dy, kh, kw, 1, pad_t)
+        wt = _packed_weight(weight, 8, True, inv_sigma).view(cin, 1, 1, kh * kw * 8)
+        return ops.conv2d_fprop(col, wt, cin, 1, 1, 1, 0, cout_p=cin_p)
+    if cin_p == 8 and _small_cout(cin, kh, kw, 1, pad_t):
+        # the input had 8 channels (image layers): per-tap products + shifted sum
+        w_taps = weight.detach().flip(2, 3).permute(2, 3, 1, 0)    # (KH, KW, Cin, Cout) of the flipped filter
+        return _small_cout_conv(dy, w_taps, None, kh, kw, pad_t, cin, inv_sigma)
+    wt = _packed_weight(weight, cout_p, True, inv_sigma)   # [Cin, KH, KW, Cout_p]
+    return ops.conv2d_fprop(dy, wt, cin, kh, kw, 1, pad_t, cout_p=cin_p)
 
 
 def conv2d(x, weight, bias=None, residual=None, stride=1, pad=0, act=ops.ACT_NONE, stats_mode=None, sn=None):
@@ -286,7 +341,8 @@ def sync_batch_stats(sums, count, eps, group=None):
     of [mean, invstd, count] + batch_norm_gather_stats_with_counts (torch
     nn/modules/_functions.py:49-86): same global mean / biased variance, also for unequal
     per-rank counts.  Returns (mean, rstd, unbiased_var), each (C,); nothing leaves the device."""
-    packed = torch.cat([sums.reshape(-1), sums.new_tensor([float(count)])])
+    # the count is written by a fill kernel: a Python scalar -> tensor copy would stall the launch queue
+    packed = torch.cat([sums.reshape(-1), torch.full((1,), float(count), dtype=sums.dtype, device=sums.device)])
     dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=group)
     gsums = packed[:-1].view_as(sums)
     count_t = packed[-1]

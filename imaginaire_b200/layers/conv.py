@@ -83,7 +83,10 @@ def prefetch_spectral_norms(root):
     layers up front is the same computation as the reference's per-layer hook; each layer picks
     its (1/sigma, u, v) up in weight_for_kernel().  Call it only for modules that WILL run in
     this forward: like the hook, every call advances u and v once."""
-    layers = [m for m in root.modules() if isinstance(m, Conv2d) and m.spectral_hook() is not None]
+    layers = root.__dict__.get('_sn_layers')
+    if layers is None:      # the module tree is static: walk it once
+        layers = [m for m in root.modules() if isinstance(m, Conv2d) and m.spectral_hook() is not None]
+        root.__dict__['_sn_layers'] = layers
     if not layers or not layers[0].weight_orig.is_cuda:
         return
     hooks = [m.spectral_hook() for m in layers]

@@ -49,11 +49,19 @@ class _VGG19Features(nn.Module):
         return out
 
 
+_IMAGENET_STATS = {}
+
+
 def apply_imagenet_normalization(x):
     """[-1, 1] images -> ImageNet-normalised.  ref: imaginaire/utils/misc.py:221-240"""
+    key = (x.device, x.dtype)
+    if key not in _IMAGENET_STATS:
+        # built once per device: creating them from Python lists every call is a pageable
+        # host-to-device copy that stalls the launch queue
+        _IMAGENET_STATS[key] = (torch.tensor([0.485, 0.456, 0.406], dtype=x.dtype, device=x.device).view(1, 3, 1, 1),
+                                torch.tensor([0.229, 0.224, 0.225], dtype=x.dtype, device=x.device).view(1, 3, 1, 1))
+    mean, std = _IMAGENET_STATS[key]
     x = (x[:, :3] + 1) / 2
-    mean = x.new_tensor([0.485, 0.456, 0.406]).view(1, 3, 1, 1)
-    std = x.new_tensor([0.229, 0.224, 0.225]).view(1, 3, 1, 1)
     return (x - mean) / std
 
 

@@ -14,12 +14,15 @@ from . import _C
 
 EPI_BIAS, EPI_RELU, EPI_LRELU, EPI_RESIDUAL, EPI_TANH, EPI_STATS, EPI_OUT_F32 = 1, 2, 4, 8, 16, 32, 64
 EPI_STATS_INSTANCE = 128
+# layers with more output pixels than this always have enough tiles; skip the split-K query
+_SPLITK_MAX_PIXELS = 148 * 256 * 2
 ACT_NONE, ACT_LRELU, ACT_RELU = 0, 1, 2
 ACT_CODES = {'': 0, 'none': 0, None: 0, 'leakyrelu': 1, 'relu': 2}
 
 
 def _stream():
-    return torch.cuda.current_stream().cuda_stream
+    # raw handle of torch's current stream; torch.cuda.current_stream() costs ~15 us of host time per call
+    return torch._C._cuda_getCurrentRawStream(torch.cuda.current_device())
 
 
 def _ptr(t):
@@ -43,7 +46,7 @@ def round_up(v, m):
 
 
 def is_nhwc_bf16(t):
-    return t.dim() == 4 and t.dtype == torch.bfloat16 and t.permute(0, 2, 3, 1).is_contiguous()
+    return t.dim() == 4 and t.dtype == torch.bfloat16 and t.is_contiguous(memory_format=torch.channels_last)
 
 
 def _req_nhwc(t, name):
@@ -258,6 +261,16 @@ def channel_sum(x, c=None):
 
 # -------------------------------------------------------------- modulation
 
+def act_bwd_bias(dy, y, act, want_bias_grad):
+    """(dy * act'(y), per-channel sum of it or None) for an activation fused into a conv epilogue."""
+    _req_cuda(dy, y); _req_nhwc(dy, 'dy'); _req_nhwc(y, 'y')
+    n, c, h, w = dy.shape
+    dx = empty_nhwc(n, c, h, w, dy.device)
+    bg = torch.zeros((c,), dtype=torch.float32, device=dy.device) if want_bias_grad else None
+    _C.lib().call('imx_act_bwd_bias_nhwc_bf16', _ptr(dy), _ptr(y), _ptr(dx), _ptr(bg), n * h * w, c, int(act), _stream())
+    return dx, bg
+
+
 def _gb_mode(gamma):
     if gamma is None:
         return 2
@@ -298,9 +311,14 @@ def spade_modulate_bwd(x, dy, mean, rstd, w, b, gamma, beta, per_instance, act, 
         dbeta = torch.zeros((n, c), dtype=torch.float32, device=x.device)
     else:
         dgamma = dbeta = None
+    gb_sums = torch.zeros((2, c), dtype=torch.float32, device=x.device) if mode == 0 else None
     _C.lib().call('imx_spade_modulate_bwd_reduce', _ptr(x), _ptr(dy), _ptr(mean), _ptr(rstd), _ptr(w), _ptr(b),
-                  _ptr(gamma), _ptr(beta), _ptr(dgamma), _ptr(dbeta), _ptr(red), n, h, wd, c, int(per_instance),
-                  mode, int(act), _stream())
+                  _ptr(gamma), _ptr(beta), _ptr(dgamma), _ptr(dbeta), _ptr(red), _ptr(gb_sums), n, h, wd, c,
+                  int(per_instance), mode, int(act), _stream())
+    if gb_sums is not None:
+        # picked up by the gamma / beta convolutions' backward as their bias gradients
+        dgamma._imx_chsum = gb_sums[0]
+        dbeta._imx_chsum = gb_sums[1]
     # dweight / dbias of the inner norm use the LOCAL reductions (DDP averages them later)
     dweight = red[1].sum(0) if w is not None else None
     dbias = red[0].sum(0) if b is not None else None
@@ -346,8 +364,19 @@ def conv2d_fprop(x, wpk, cout, kh, kw, stride=1, pad=0, bias=None, residual=None
             flags |= EPI_STATS_INSTANCE
     if out_f32:
         flags |= EPI_OUT_F32
-    _C.lib().call('imx_conv2d_igemm_fprop_bf16', _ptr(x), _ptr(wpk), _ptr(bias), _ptr(residual), _ptr(out),
-                  _ptr(stats), n, h, w, cin_p, cout, cout_p, kh, kw, stride, pad, flags, _stream())
+    lib = _C.lib()
+    nbytes = 0
+    if not (flags & EPI_STATS) and n * ho * wo <= _SPLITK_MAX_PIXELS:
+        nbytes = lib.raw('imx_conv2d_fprop_workspace_bytes')(n, h, w, cin_p, cout, cout_p, kh, kw, stride, pad, flags)
+        if nbytes < 0:
+            raise _C.ImxError('imx_conv2d_fprop_workspace_bytes: %s' % lib.last_error())
+    if nbytes > 0:
+        ws = torch.empty((int(nbytes),), dtype=torch.uint8, device=x.device)
+        lib.call('imx_conv2d_igemm_fprop_splitk_bf16', _ptr(x), _ptr(wpk), _ptr(bias), _ptr(residual), _ptr(out),
+                 _ptr(stats), _ptr(ws), int(nbytes), n, h, w, cin_p, cout, cout_p, kh, kw, stride, pad, flags, _stream())
+    else:
+        lib.call('imx_conv2d_igemm_fprop_bf16', _ptr(x), _ptr(wpk), _ptr(bias), _ptr(residual), _ptr(out),
+                 _ptr(stats), n, h, w, cin_p, cout, cout_p, kh, kw, stride, pad, flags, _stream())
     return out
 
 
@@ -359,6 +388,32 @@ def spade_gb_conv_modulate(hidden, wgb, bias_gamma, bias_beta, x, mean, rstd, w,
     _C.lib().call('imx_spade_gb_conv_modulate_bf16', _ptr(hidden), _ptr(wgb), _ptr(bias_gamma), _ptr(bias_beta),
                   _ptr(x), _ptr(mean), _ptr(rstd), _ptr(w), _ptr(b), _ptr(y), n, h, wd, ch_p, c, kh, kw, pad,
                   int(per_instance), int(act), int(up2x), _stream())
+    return y
+
+
+def im2col_c8(x, kh, kw, stride, pad):
+    """x: NHWC bf16 with 8 channels -> (N, KH*KW*8, Ho, Wo) NHWC bf16 patches (tap-major, channel fastest)."""
+    _req_cuda(x); _req_nhwc(x, 'x')
+    n, c, h, w = x.shape
+    if c != 8:
+        raise RuntimeError('im2col_c8 needs an 8-channel tensor, got %d channels' % c)
+    ho = (h + 2 * pad - kh) // stride + 1
+    wo = (w + 2 * pad - kw) // stride + 1
+    col = empty_nhwc(n, kh * kw * 8, ho, wo, x.device)
+    _C.lib().call('imx_im2col_c8_nhwc_bf16', _ptr(x), _ptr(col), n, h, w, kh, kw, stride, pad, _stream())
+    return col
+
+
+def shift_add_taps(p, bias, kh, kw, pad, cout):
+    """p: (N, ncols, H, W) fp32 NHWC per-tap products -> (N, 8, H, W) NHWC bf16 'same' convolution output."""
+    _req_cuda(p)
+    n, ncols, h, w = p.shape
+    if p.dtype != torch.float32 or not p.is_contiguous(memory_format=torch.channels_last):
+        raise RuntimeError('shift_add_taps: p must be fp32 in channels_last (NHWC) memory')
+    if bias is not None:
+        _req_f32c(bias, 'bias')
+    y = empty_nhwc(n, 8, h, w, p.device)
+    _C.lib().call('imx_shift_add_taps_f32', _ptr(p), _ptr(bias), _ptr(y), n, h, w, ncols, kh, kw, pad, cout, _stream())
     return y
 
 

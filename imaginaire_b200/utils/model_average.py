@@ -72,8 +72,45 @@ class ModelAverage(nn.Module):
         # target = beta * target + (1 - beta) * source
         torch._foreach_mul_(plain_t, beta)
         torch._foreach_add_(plain_t, plain_s, alpha=1.0 - beta)
+        sn_layers = [e for e in sn if e[2] is not None]
         for t, w, u, v in sn:
             if u is None:
                 t.copy_(w)
-            else:
+        if not sn_layers:
+            return
+        if not sn_layers[0][1].is_cuda:
+            for t, w, u, v in sn_layers:
                 t.mul_(beta).add_(self.sn_compute_weight(w, u, v), alpha=1.0 - beta)
+            return
+        # sigma = u^T W v of every spectral layer in one batched call (no power iteration), then
+        # target = beta * target + (1 - beta) * W / sigma.   ref: model_average.py:183-197
+        inv = self._batched_inv_sigma(sn_layers)
+        targets = [e[0] for e in sn_layers]
+        torch._foreach_mul_(targets, beta)
+        for (t, w, _, _), s in zip(sn_layers, inv):
+            t.addcmul_(w, s, value=1.0 - beta)
+
+    def _batched_inv_sigma(self, sn_layers):
+        from .. import ops
+        plan = self.__dict__.get('_ema_sn_plan')
+        key = tuple((w.data_ptr(), u.data_ptr(), v.data_ptr()) for _, w, u, v in sn_layers)
+        if plan is None or plan['key'] != key:
+            dev = sn_layers[0][1].device
+            rows, t_off, out_off = [], 0, 0
+            for _, w, u, v in sn_layers:
+                r = w.shape[0]
+                c = w.numel() // r
+                rows.append([w.data_ptr(), u.data_ptr(), v.data_ptr(), t_off, 0, out_off, r, c])
+                t_off += c
+                out_off += 1 + r + c
+            s_off = t_off
+            for row in rows:
+                row[4] = s_off
+                s_off += row[6]
+            plan = dict(key=key, descs=torch.tensor(rows, dtype=torch.int64).to(dev),
+                        scratch=torch.empty((s_off,), dtype=torch.float32, device=dev), out_floats=out_off,
+                        offs=[row[5] for row in rows], max_r=max(r[6] for r in rows), max_c=max(r[7] for r in rows))
+            self.__dict__['_ema_sn_plan'] = plan
+        out = ops.spectral_norm_sigma_batched(plan['descs'], len(sn_layers), plan['max_r'], plan['max_c'], plan['scratch'],
+                                              plan['out_floats'], 0, 1e-12)
+        return [out[o:o + 1] for o in plan['offs']]

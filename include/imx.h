@@ -182,12 +182,15 @@ IMX_API int imx_spade_modulate_fwd(const imx_bf16* x, const float* mean, const f
  * write dgamma, dbeta (gb_mode 0: NHWC bf16; gb_mode 1: accumulated into fp32
  * [n*C+c], caller zero-fills) and accumulate the per-(group,channel) reductions
  * red[0][g*C+c] = sum dxhat_affine, red[1][g*C+c] = sum dxhat_affine * xn
- * (fp32, caller zero-fills; these are also dbias / dweight of the inner norm). */
+ * (fp32, caller zero-fills; these are also dbias / dweight of the inner norm).
+ * gb_sums (optional, gb_mode 0 only): fp32 (2, C), caller zero-fills; receives the sums of
+ * dgamma and dbeta over all pixels of the batch, i.e. the bias gradients of the convolutions
+ * that produced gamma and beta, saving two passes over those tensors. */
 IMX_API int imx_spade_modulate_bwd_reduce(const imx_bf16* x, const imx_bf16* dy,
                                   const float* mean, const float* rstd,
                                   const float* w, const float* b,
                                   const void* gamma, const void* beta,
-                                  void* dgamma, void* dbeta, float* red,
+                                  void* dgamma, void* dbeta, float* red, float* gb_sums,
                                   int N, int H, int W, int C,
                                   int stats_per_instance, int gb_mode, int act,
                                   imx_stream_t stream);
@@ -234,6 +237,42 @@ IMX_API int imx_conv2d_igemm_fprop_bf16(const imx_bf16* x, const imx_bf16* wpk, 
                                 int N, int H, int W, int Cin_p,
                                 int Cout, int Cout_p, int KH, int KW,
                                 int stride, int pad, int flags, imx_stream_t stream);
+
+/* Layers with at most 8 channels on one side (the 5x5 to-RGB convolution 256 -> 3 of
+ * imaginaire/generators/spade.py:318-323, its gradients, the first layer of the image networks)
+ * run as a 1x1 GEMM on the tensor cores plus one of these two memory-bound passes.
+ *
+ * imx_im2col_c8_nhwc_bf16: col[n,oy,ox,(kh,kw,c)] = x[n, oy*stride+kh-pad, ox*stride+kw-pad, c]
+ * (zero outside), x: N x H x W x 8 bf16, col: N x Ho x Wo x (KH*KW*8) bf16.  A convolution of x
+ * is then a 1x1 convolution of col with the packed filter [Cout][KH*KW*8].
+ *
+ * imx_shift_add_taps_f32: y[n,oy,ox,co] = bias[co] + sum_{kh,kw} P[n, oy+kh-pad, ox+kw-pad,
+ * (kh*KW+kw)*Cout + co] for a 'same' convolution (2*pad == K-1), where
+ * P[n,iy,ix,(tap,co)] = sum_ci x[n,iy,ix,ci] * w[co,ci,tap] (fp32, `ncols` floats per pixel) came
+ * from a 1x1 convolution with KH*KW*Cout output columns.  y: N x H x W x 8 bf16, channels >= Cout
+ * are zero; bias may be NULL.
+ * ref: torch.nn.Conv2d inside Conv2dBlock, imaginaire/layers/conv.py:93-104 */
+IMX_API int imx_im2col_c8_nhwc_bf16(const imx_bf16* x, imx_bf16* col, int N, int H, int W,
+                            int KH, int KW, int stride, int pad, imx_stream_t stream);
+IMX_API int imx_shift_add_taps_f32(const float* P, const float* bias, imx_bf16* y, int N, int H, int W,
+                           int ncols, int KH, int KW, int pad, int Cout, imx_stream_t stream);
+
+/* Split-K variant for layers with fewer pixel tiles than SMs (small images, many channels):
+ * the K loop (taps x channel blocks) is divided over several CTAs that add fp32 partial
+ * sums into `workspace`; a finishing kernel applies the epilogue.  The library zero-fills
+ * the workspace itself (one cudaMemsetAsync on `stream`).
+ * imx_conv2d_fprop_workspace_bytes returns the bytes this layer wants (0: the plain tiling
+ * is already the fastest and workspace may be NULL; < 0: invalid arguments).  With
+ * workspace == NULL, or IMX_EPI_STATS set, this is exactly imx_conv2d_igemm_fprop_bf16.
+ * ref: same as imx_conv2d_igemm_fprop_bf16 (no separate reference counterpart). */
+IMX_API int64_t imx_conv2d_fprop_workspace_bytes(int N, int H, int W, int Cin_p, int Cout, int Cout_p,
+                                         int KH, int KW, int stride, int pad, int flags);
+IMX_API int imx_conv2d_igemm_fprop_splitk_bf16(const imx_bf16* x, const imx_bf16* wpk, const float* bias,
+                                       const imx_bf16* residual, void* out, float* stats,
+                                       void* workspace, int64_t workspace_bytes,
+                                       int N, int H, int W, int Cin_p,
+                                       int Cout, int Cout_p, int KH, int KW,
+                                       int stride, int pad, int flags, imx_stream_t stream);
 
 /* SPADE projection conv fused with the modulation (gamma/beta never reach HBM):
  *   gb = conv(hidden; wgb) (+bias), wgb rows interleaved per 64-channel block as
@@ -298,6 +337,14 @@ IMX_API int imx_conv2d_igemm_wgrad_bf16_noalloc(const imx_bf16* x, const imx_bf1
  * out[c] = sum_{n,p} x[n,p,c]; fp32, caller zero-fills. */
 IMX_API int imx_channel_sum_nhwc_bf16(const imx_bf16* x, float* out, int NP, int C, int Cp,
                               imx_stream_t stream);
+
+/* dx = dy * act'(y) for an activation fused into a conv epilogue (y = act(pre): LeakyReLU(0.2)
+ * or ReLU, so act' depends on the sign of y only), and, when bias_grad != NULL, bias_grad[c] +=
+ * sum over the NP pixels of dx (fp32, C entries, caller zero-fills): the backward of
+ * `nonlinearity(conv(x) + bias)` up to the conv itself in one pass.  All tensors NP x C bf16.
+ * ref: autograd of imaginaire/layers/conv.py:77-91 (order 'CNA' blocks), nonlinearity.py:22 */
+IMX_API int imx_act_bwd_bias_nhwc_bf16(const imx_bf16* dy, const imx_bf16* y, imx_bf16* dx, float* bias_grad,
+                               int64_t NP, int C, int act, imx_stream_t stream);
 
 #ifdef __cplusplus
 }

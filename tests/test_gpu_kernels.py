@@ -197,6 +197,39 @@ def test_conv2d_epilogues_vs_oracle():
         assert H.rel_err(st[1].cpu().flatten(), (yq * yq).sum(dims).flatten()) < 1e-4
 
 
+@pytest.mark.parametrize('case', [(8, 2048, 128, 16, 32, 5, 1, 2), (8, 512, 512, 16, 32, 4, 2, 1), (2, 256, 40, 9, 13, 3, 1, 1)])
+def test_conv2d_fprop_split_k_matches_plain_tiling(case):
+    """Layers with fewer pixel tiles than SMs split the K loop over CTAs (fp32 partial sums in a
+    workspace + finishing kernel).  Same operands through the plain entry point: the only
+    difference is the fp32 summation order, far below the bf16 rounding of the output."""
+    from imaginaire_b200 import ops, _C
+    n, cin, cout, h, w, k, s, p = case
+    g = torch.Generator().manual_seed(35)
+    x = nhwc(torch.randn(n, cin, h, w, generator=g))
+    wpk = ops.pack_conv_weight((torch.randn(cout, cin, k, k, generator=g) / (cin * k * k) ** 0.5).to(DEV))
+    b = torch.randn(cout, generator=g).to(DEV)
+    res_shape = (n, ops.round_up(cout, 8), (h + 2 * p - k) // s + 1, (w + 2 * p - k) // s + 1)
+    res = nhwc(torch.randn(*res_shape, generator=g))
+    lib = _C.lib()
+    flags = ops.EPI_BIAS | ops.EPI_LRELU | ops.EPI_RESIDUAL
+    need = lib.raw('imx_conv2d_fprop_workspace_bytes')(n, h, w, cin, cout, res_shape[1], k, k, s, p, flags)
+    assert need == n * res_shape[2] * res_shape[3] * res_shape[1] * 4      # split-K chosen for these shapes
+    y_split = ops.conv2d_fprop(x, wpk, cout, k, k, s, p, bias=b, residual=res, flags=ops.EPI_LRELU)
+    y_plain = ops.empty_nhwc(*res_shape, x.device)
+    lib.call('imx_conv2d_igemm_fprop_bf16', x.data_ptr(), wpk.data_ptr(), b.data_ptr(), res.data_ptr(), y_plain.data_ptr(),
+             None, n, h, w, cin, cout, res_shape[1], k, k, s, p, flags, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    # two bf16-rounded results of differently ordered fp32 sums differ by at most one bf16 ulp (2^-7 relative)
+    assert H.rel_err(y_split.float().cpu(), y_plain.float().cpu()) < 1e-2
+    assert float((y_split.float() - y_plain.float()).abs().mean() / y_plain.float().abs().mean()) < 2e-3
+    # a too-small workspace is refused, not overrun
+    with pytest.raises(_C.ImxError):
+        ws = torch.empty(16, dtype=torch.uint8, device=DEV)
+        lib.call('imx_conv2d_igemm_fprop_splitk_bf16', x.data_ptr(), wpk.data_ptr(), b.data_ptr(), res.data_ptr(),
+                 y_plain.data_ptr(), None, ws.data_ptr(), 16, n, h, w, cin, cout, res_shape[1], k, k, s, p, flags,
+                 torch.cuda.current_stream().cuda_stream)
+
+
 @pytest.mark.parametrize('case', [(1, 64, 128, 8, 8, 1, 1, 0), (2, 64, 64, 16, 32, 3, 1, 1), (1, 40, 72, 13, 11, 5, 1, 2),
                                   (2, 64, 512, 32, 64, 5, 1, 2), (2, 64, 128, 32, 32, 4, 2, 1),
                                   (4, 256, 256, 32, 64, 3, 1, 1)])
@@ -232,7 +265,60 @@ def test_conv2d_dgrad_vs_oracle(case):
     assert H.rel_err(dx[:, :cin].float().cpu(), ref) < 4e-3
 
 
+@pytest.mark.parametrize('case', [(2, 3, 16, 20, 33, 3, 1, 1),      # few input channels (image -> first layer)
+                                  (2, 3, 32, 32, 48, 3, 2, 1),      # ... stride 2; dgrad = zero insertion + tap sum
+                                  (1, 3, 24, 17, 19, 5, 1, 2),
+                                  (2, 40, 3, 21, 37, 5, 1, 2),      # few output channels (to-RGB)
+                                  (2, 256, 3, 32, 64, 5, 1, 2),
+                                  (1, 64, 1, 16, 16, 3, 1, 1)])
+def test_small_channel_convs_forward_and_gradients(case):
+    """Layers with <= 8 channels on one side run as im2col / per-tap-product GEMMs plus a
+    memory-bound pass (csrc/small_conv.cu).  Forward, dx, dW and dbias against torch autograd
+    on the same bf16-rounded operands."""
+    from imaginaire_b200 import ops, functional as NF
+    n, cin, cout, h, w, k, s, p = case
+    g = torch.Generator().manual_seed(36)
+    x = torch.randn(n, cin, h, w, generator=g).bfloat16().float()
+    wt = (torch.randn(cout, cin, k, k, generator=g) / (cin * k * k) ** 0.5).bfloat16().float()
+    b = torch.randn(cout, generator=g)
+    cin_p = ops.round_up(cin, 8)
+    xp = torch.zeros(n, cin_p, h, w); xp[:, :cin] = x
+    xd = nhwc(xp).requires_grad_(True)
+    wd = wt.to(DEV).requires_grad_(True)
+    bd = b.to(DEV).requires_grad_(True)
+    y = NF.conv2d(xd, wd, bd, stride=s, pad=p)
+    xr, wr, br = x.clone().requires_grad_(True), wt.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    ref = F.conv2d(xr, wr, br, stride=s, padding=p)
+    assert y.shape == (n, ops.round_up(cout, 8)) + tuple(ref.shape[2:])
+    assert H.rel_err(y[:, :cout].float().cpu(), ref) < 6e-3
+    assert float(y[:, cout:].float().abs().max() if y.shape[1] > cout else 0.0) == 0.0
+    dy = torch.randn(ref.shape, generator=g).bfloat16().float()
+    dyp = torch.zeros(y.shape); dyp[:, :cout] = dy
+    y.backward(nhwc(dyp))
+    ref.backward(dy)
+    assert H.rel_err(xd.grad[:, :cin].float().cpu(), xr.grad) < 6e-3
+    assert H.rel_err(wd.grad.cpu(), wr.grad) < 6e-3
+    assert H.rel_err(bd.grad.cpu(), br.grad) < 1e-4
+
+
 # ------------------------------------------------- statistics / modulation
+
+@pytest.mark.parametrize('shape', [(2, 64, 16, 32), (3, 512, 9, 7), (1, 8, 1, 1), (2, 2048, 4, 8)])
+@pytest.mark.parametrize('act', [1, 2])
+def test_act_backward_with_bias_grad_exact(shape, act):
+    """dx = dy * act'(y) and its per-channel sum in one pass; exact against the same arithmetic in torch."""
+    from imaginaire_b200 import ops
+    g = torch.Generator().manual_seed(41)
+    y = nhwc(torch.randn(*shape, generator=g))
+    dy = nhwc(torch.randn(*shape, generator=g))
+    dx, bg = ops.act_bwd_bias(dy, y, act, True)
+    slope = 0.2 if act == 1 else 0.0
+    ref = torch.where(y.float() > 0, dy.float(), dy.float() * slope).bfloat16()
+    assert torch.equal(dx.cpu(), ref.cpu())
+    assert H.rel_err(bg.cpu(), ref.float().sum((0, 2, 3)).cpu()) < 1e-5
+    dx2, none = ops.act_bwd_bias(dy, y, act, False)
+    assert none is None and torch.equal(dx2, dx)
+
 
 @pytest.mark.parametrize('shape', [(2, 64, 16, 32), (3, 512, 8, 8), (2, 2048, 4, 8), (1, 40, 5, 7), (2, 4096, 2, 2)])
 @pytest.mark.parametrize('inst', [False, True])

@@ -29,5 +29,5 @@ for e in prof.key_averages():
 rows.sort(reverse=True)
 tot = sum(r[0] for r in rows)
 print('total device kernel time %.1f ms over %d kernel names' % (tot / 1e3, len(rows)))
-for t, c, k in rows[:45]:
+for t, c, k in rows[:int(os.environ.get("TOP", 45))]:
     print('%8.2f ms %5.1f%% x%-5d %s' % (t / 1e3, 100.0 * t / tot, c, k[:110]))
