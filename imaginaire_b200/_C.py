@@ -15,6 +15,7 @@ HEADER_PATH = os.path.join(os.path.dirname(_HERE), 'include', 'imx.h')
 _SCALARS = {
     'int': ctypes.c_int,
     'float': ctypes.c_float,
+    'double': ctypes.c_double,
     'int64_t': ctypes.c_int64,
     'imx_stream_t': ctypes.c_void_p,
 }

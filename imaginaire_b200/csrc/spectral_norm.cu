@@ -348,6 +348,45 @@ snb_finish_u_kernel(const SnDesc* __restrict__ descs, const float* __restrict__ 
 
 }  // namespace
 
+namespace {
+
+// target = beta * target + (1 - beta) * W / sigma for every described layer (grid.y = layer).
+__global__ void __launch_bounds__(256)
+snb_ema_kernel(const SnDesc* __restrict__ descs, const long long* __restrict__ targets,
+               const float* __restrict__ out, float beta) {
+    const SnDesc d = descs[blockIdx.y];
+    const long n = (long)d.R * d.C;
+    float* t = reinterpret_cast<float*>(targets[blockIdx.y]);
+    const float k = (1.0f - beta) * out[d.out_off];      // (1 - beta) / sigma
+    const long n4 = ((reinterpret_cast<uintptr_t>(d.W) | reinterpret_cast<uintptr_t>(t)) & 15) == 0 ? n / 4 : 0;
+    const long stride = (long)gridDim.x * blockDim.x;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n4; i += stride) {
+        const float4 w = __ldg(reinterpret_cast<const float4*>(d.W) + i);
+        float4 a = reinterpret_cast<float4*>(t)[i];
+        a.x = fmaf(beta, a.x, k * w.x); a.y = fmaf(beta, a.y, k * w.y);
+        a.z = fmaf(beta, a.z, k * w.z); a.w = fmaf(beta, a.w, k * w.w);
+        reinterpret_cast<float4*>(t)[i] = a;
+    }
+    for (long i = n4 * 4 + blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += stride)
+        t[i] = fmaf(beta, t[i], k * __ldg(d.W + i));
+}
+
+}  // namespace
+
+extern "C" int imx_spectral_norm_ema_update_f32(const void* descs, const void* targets, int n_layers, int64_t max_elems,
+                                                const float* sigma_out, float beta, imx_stream_t stream) {
+    IMX_REQUIRE(n_layers >= 0 && n_layers <= 65535, "spectral_norm_ema_update: bad layer count");
+    if (n_layers == 0) return IMX_OK;
+    IMX_REQUIRE(descs && targets && sigma_out, "spectral_norm_ema_update: null pointer");
+    IMX_REQUIRE(max_elems > 0, "spectral_norm_ema_update: bad size");
+    long blocks = (max_elems / 4 + 255) / 256;
+    if (blocks > 2 * imx::kNumSMs) blocks = 2 * imx::kNumSMs;
+    if (blocks < 1) blocks = 1;
+    snb_ema_kernel<<<dim3((unsigned)blocks, n_layers), 256, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const SnDesc*>(descs), reinterpret_cast<const long long*>(targets), sigma_out, beta);
+    return imx::check_launch("spectral_norm_ema_update");
+}
+
 extern "C" int imx_spectral_norm_sigma_batched_f32(const void* descs, int n_layers, int max_R, int max_C,
                                                    void* scratch, float* out, int n_power_iterations, float eps,
                                                    imx_stream_t stream) {

@@ -215,6 +215,12 @@ def spectral_norm_sigma_batched(descs, n_layers, max_r, max_c, scratch, out_floa
     return out
 
 
+def spectral_norm_ema_update(descs, targets, n_layers, max_elems, sigma_out, beta):
+    """targets[i] = beta * targets[i] + (1 - beta) * W_i / sigma_i for the layers of a batched sigma call."""
+    _C.lib().call('imx_spectral_norm_ema_update_f32', _ptr(descs), _ptr(targets), int(n_layers), int(max_elems),
+                  _ptr(sigma_out), float(beta), _stream())
+
+
 def spectral_norm_weight_grad_(grad, weight, u, v, inv_sigma):
     """grad (= dL/d(W/sigma), fp32, same shape as weight) -> dL/dW, in place."""
     _req_cuda(grad, weight)

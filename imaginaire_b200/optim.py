@@ -1,0 +1,67 @@
+"""Optimizers of the training step on the library's own kernels.
+
+ref: get_optimizer_for_params, imaginaire/utils/trainer.py:261-306 ('adam' -> apex FusedAdam when
+``fused_opt`` else torch.optim.Adam).  apex is not part of this build; FusedAdam here is
+torch.optim.Adam's state layout and hyper-parameters with ``step()`` running
+imx_adam_multi_tensor_f32 (csrc/optim.cu): one 28-byte-per-parameter pass, ~12 launches for the
+generator's ~480 tensors.
+"""
+import ctypes
+
+import torch
+
+from . import _C, ops
+
+
+class FusedAdam(torch.optim.Adam):
+    """Drop-in for torch.optim.Adam (no amsgrad / maximize / capturable): same ``state_dict()``
+    entries (``step`` as a CPU scalar tensor, ``exp_avg``, ``exp_avg_sq``), so checkpoints written
+    by either load into the other."""
+
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0):
+        super().__init__(params, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        for group in self.param_groups:
+            by_step = {}
+            for p in group['params']:
+                g = p.grad
+                if g is None:
+                    continue
+                if g.is_sparse:
+                    raise RuntimeError('FusedAdam does not support sparse gradients')
+                if not p.is_cuda or p.dtype != torch.float32 or not p.is_contiguous():
+                    raise RuntimeError('FusedAdam needs contiguous float32 CUDA parameters (no CPU fallback); got %s %s'
+                                       % (p.device.type, p.dtype))
+                state = self.state[p]
+                if len(state) == 0:
+                    state['step'] = torch.tensor(0.0, dtype=torch.float32)
+                    state['exp_avg'] = torch.zeros_like(p, memory_format=torch.contiguous_format)
+                    state['exp_avg_sq'] = torch.zeros_like(p, memory_format=torch.contiguous_format)
+                state['step'] += 1
+                if g.dtype != torch.float32 or not g.is_contiguous():
+                    g = g.float().contiguous()
+                by_step.setdefault(int(state['step']), []).append((p, g, state['exp_avg'], state['exp_avg_sq']))
+            beta1, beta2 = group['betas']
+            for step, items in by_step.items():
+                _adam_launch(items, float(group['lr']), float(beta1), float(beta2), float(group['eps']),
+                             float(group['weight_decay']), step)
+        return loss
+
+
+def _adam_launch(items, lr, beta1, beta2, eps, weight_decay, step):
+    n = len(items)
+    ptr_t = ctypes.c_void_p * n
+    cols = [ptr_t(*[t[k].data_ptr() for t in items]) for k in range(4)]
+    numel = (ctypes.c_int64 * n)(*[t[0].numel() for t in items])
+    lib = _C.lib()
+    lib.call('imx_adam_multi_tensor_f32', cols[0], cols[1], cols[2], cols[3], numel, n, lr, beta1, beta2, eps,
+             weight_decay, step, ops._stream())
+    # launches issued: one per 96 tensors / 1184 chunks of 32768 elements
+    chunks = sum((t[0].numel() + 32767) // 32768 for t in items)
+    lib.launches += max((n + 95) // 96, (chunks + 1183) // 1184) - 1

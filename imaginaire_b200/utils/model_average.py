@@ -84,16 +84,12 @@ class ModelAverage(nn.Module):
             return
         # sigma = u^T W v of every spectral layer in one batched call (no power iteration), then
         # target = beta * target + (1 - beta) * W / sigma.   ref: model_average.py:183-197
-        inv = self._batched_inv_sigma(sn_layers)
-        targets = [e[0] for e in sn_layers]
-        torch._foreach_mul_(targets, beta)
-        for (t, w, _, _), s in zip(sn_layers, inv):
-            t.addcmul_(w, s, value=1.0 - beta)
+        self._batched_sn_update(sn_layers, beta)
 
-    def _batched_inv_sigma(self, sn_layers):
+    def _batched_sn_update(self, sn_layers, beta):
         from .. import ops
         plan = self.__dict__.get('_ema_sn_plan')
-        key = tuple((w.data_ptr(), u.data_ptr(), v.data_ptr()) for _, w, u, v in sn_layers)
+        key = tuple((t.data_ptr(), w.data_ptr(), u.data_ptr(), v.data_ptr()) for t, w, u, v in sn_layers)
         if plan is None or plan['key'] != key:
             dev = sn_layers[0][1].device
             rows, t_off, out_off = [], 0, 0
@@ -109,8 +105,10 @@ class ModelAverage(nn.Module):
                 s_off += row[6]
             plan = dict(key=key, descs=torch.tensor(rows, dtype=torch.int64).to(dev),
                         scratch=torch.empty((s_off,), dtype=torch.float32, device=dev), out_floats=out_off,
-                        offs=[row[5] for row in rows], max_r=max(r[6] for r in rows), max_c=max(r[7] for r in rows))
+                        targets=torch.tensor([e[0].data_ptr() for e in sn_layers], dtype=torch.int64).to(dev),
+                        max_elems=max(r[6] * r[7] for r in rows), max_r=max(r[6] for r in rows),
+                        max_c=max(r[7] for r in rows))
             self.__dict__['_ema_sn_plan'] = plan
         out = ops.spectral_norm_sigma_batched(plan['descs'], len(sn_layers), plan['max_r'], plan['max_c'], plan['scratch'],
                                               plan['out_floats'], 0, 1e-12)
-        return [out[o:o + 1] for o in plan['offs']]
+        ops.spectral_norm_ema_update(plan['descs'], plan['targets'], len(sn_layers), plan['max_elems'], out, beta)

@@ -3,8 +3,8 @@ ref: imaginaire/utils/trainer.py:24-37 (seeds), :69-125 (get_model_optimizer_and
      :128-216 (wrap / DDP), :242-306 (optimisers)
 
 apex is replaced as SURVEY.md Appendix C prescribes: mixed precision is the kernels' own
-bf16-storage / fp32-accumulate arithmetic (no loss scaling), FusedAdam becomes
-torch.optim.Adam(fused=True), apex DDP becomes torch DDP over NCCL.
+bf16-storage / fp32-accumulate arithmetic (no loss scaling), apex FusedAdam becomes
+imaginaire_b200.optim.FusedAdam (csrc/optim.cu), apex DDP becomes torch DDP over NCCL.
 """
 import random
 
@@ -17,6 +17,7 @@ from ..generators.spade import Generator
 from .distributed import get_rank, get_world_size
 from .init_weight import weights_init
 from .model_average import ModelAverage
+from ..optim import FusedAdam
 
 
 def set_random_seed(seed, by_rank=False):
@@ -31,8 +32,11 @@ def set_random_seed(seed, by_rank=False):
 def get_optimizer(opt_cfg, params):
     if opt_cfg.type != 'adam':
         raise NotImplementedError('only adam is wired up for the SPADE step')
-    return torch.optim.Adam(params, lr=opt_cfg.lr, eps=getattr(opt_cfg, 'eps', 1e-8),
-                            betas=(opt_cfg.adam_beta1, opt_cfg.adam_beta2), fused=True)
+    params = list(params)
+    kwargs = dict(lr=opt_cfg.lr, eps=getattr(opt_cfg, 'eps', 1e-8), betas=(opt_cfg.adam_beta1, opt_cfg.adam_beta2))
+    if params and all(p.is_cuda for p in params):
+        return FusedAdam(params, **kwargs)            # the library's multi-tensor kernel
+    return torch.optim.Adam(params, **kwargs)         # CPU-side unit tests of the host logic
 
 
 def get_model_optimizer_and_scheduler(cfg, seed=0, device='cuda'):
@@ -76,5 +80,6 @@ def _wrap_model(model):
     if get_world_size() > 1:
         return DistributedDataParallel(model, device_ids=[torch.cuda.current_device()],
                                        output_device=torch.cuda.current_device(),
-                                       find_unused_parameters=True, broadcast_buffers=False)
+                                       find_unused_parameters=True, broadcast_buffers=False,
+                                       gradient_as_bucket_view=True, bucket_cap_mb=64)
     return WrappedModel(model)

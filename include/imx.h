@@ -137,6 +137,14 @@ IMX_API int imx_spectral_norm_sigma_batched_f32(const void* descs, int n_layers,
                                                 void* scratch, float* out, int n_power_iterations, float eps,
                                                 imx_stream_t stream);
 
+/* Moving average of spectrally normalised filters: for every layer of `descs` (same records as
+ * imx_spectral_norm_sigma_batched_f32, whose output buffer `sigma_out` holds 1/sigma at each
+ * layer's out_off), target = beta * target + (1 - beta) * W / sigma.  targets: device array of
+ * n_layers 64-bit pointers to fp32 tensors shaped like W.  One launch.
+ * ref: ModelAverage.update_average, imaginaire/utils/model_average.py:87-132, 183-197 */
+IMX_API int imx_spectral_norm_ema_update_f32(const void* descs, const void* targets, int n_layers, int64_t max_elems,
+                                     const float* sigma_out, float beta, imx_stream_t stream);
+
 /* Backward of W_eff = W / sigma(W) with u, v constant: in place on G = dL/dW_eff,
  * G <- G / sigma - (<G, W> / sigma^2) u v^T  (= dL/dW).  dot_scratch: one float. */
 IMX_API int imx_spectral_norm_weight_grad_f32(float* G, const float* W, const float* u, const float* v,
@@ -345,6 +353,24 @@ IMX_API int imx_channel_sum_nhwc_bf16(const imx_bf16* x, float* out, int NP, int
  * ref: autograd of imaginaire/layers/conv.py:77-91 (order 'CNA' blocks), nonlinearity.py:22 */
 IMX_API int imx_act_bwd_bias_nhwc_bf16(const imx_bf16* dy, const imx_bf16* y, imx_bf16* dx, float* bias_grad,
                                int64_t NP, int C, int act, imx_stream_t stream);
+
+/* ------------------------------------------------------------ optimizer -- */
+
+/* One Adam step (torch.optim.Adam arithmetic, no amsgrad) over n_tensors fp32 tensors:
+ *   g = grad + weight_decay * p;  m += (1-beta1)(g-m);  v = beta2 v + (1-beta2) g^2;
+ *   p -= lr/(1-beta1^step) * m / (sqrt(v)/sqrt(1-beta2^step) + eps)
+ * params / grads / exp_avg / exp_avg_sq: HOST arrays of n_tensors device pointers, numel: host
+ * array of element counts; `step` is the 1-based step number AFTER this update's increment.
+ * Hyper-parameters are doubles because 1 - beta2 has to be formed before rounding to fp32.
+ * The pointer tables are passed through kernel arguments: no allocation, no copies, one launch
+ * per ~96 tensors / 39 M elements.  28 bytes of HBM traffic per parameter.
+ * ref: get_optimizer_for_params 'adam' (apex FusedAdam / torch Adam),
+ *      imaginaire/utils/trainer.py:261-306 */
+IMX_API int imx_adam_multi_tensor_f32(const void* const* params, const void* const* grads,
+                              const void* const* exp_avg, const void* const* exp_avg_sq,
+                              const int64_t* numel, int n_tensors,
+                              double lr, double beta1, double beta2, double eps, double weight_decay,
+                              int64_t step, imx_stream_t stream);
 
 #ifdef __cplusplus
 }

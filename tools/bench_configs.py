@@ -1,0 +1,129 @@
+"""Measurements for the other BASELINE.json configurations; developer tool.
+
+    python tools/bench_configs.py config1   # unit-test SPADE generator forward, batch 1 (GPU + CPU oracle)
+    python tools/bench_configs.py config4   # flow-warp microbenchmark, 512x1024, B in {1,8,32} x C in {3,4,64}
+    python tools/bench_configs.py config5   # C3 generator at 512x1024, batch 4, forward only
+    python tools/bench_configs.py all
+
+One JSON line per measurement.  bench.py (config 3, the training step) stays the driver's contract.
+GPU times: CUDA events around REPS back-to-back calls after warm-up; inputs larger than L2 or
+rotated between calls where it matters.
+"""
+import json
+import os
+import sys
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import bench
+from imaginaire_b200.config import Config
+
+_PEAKS = bench.load_peaks()
+HBM_PEAK = _PEAKS['hbm']
+DEV = 'cuda:0'
+
+
+def gpu_time(fn, reps, warmup=2):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(reps):
+        fn()
+    e.record()
+    torch.cuda.synchronize()
+    return s.elapsed_time(e) / reps * 1e-3
+
+
+def config1():
+    from imaginaire_b200.generators.spade import Generator
+    from imaginaire_b200.utils.init_weight import weights_init
+    cfg = Config(os.path.join(bench.ROOT, 'configs', 'spade_unit_test.yaml'))
+    torch.manual_seed(0)
+    net = Generator(cfg.gen, cfg.data)
+    net.apply(weights_init('xavier', 0.02))
+    net = net.to(DEV).train()
+    data = {k: v.to(DEV) for k, v in bench.synthetic_batch(cfg, 1, 0).items()}
+    with torch.no_grad():
+        t = gpu_time(lambda: net(data), 10, 3)
+    torch.set_num_threads(os.cpu_count() or 1)
+    cpu = min(bench.cpu_reference_step(cfg, 1, 0)[0] for _ in range(3))
+    print(json.dumps({'config': 'config1: configs/unit_test/spade.yaml generator forward, batch 1, 256x256, 185-channel label',
+                      'gpu_ms': t * 1e3, 'gpu_img_s': 1.0 / t, 'cpu_oracle_ms': cpu * 1e3, 'cpu_cores': os.cpu_count(),
+                      'gflop_per_img': 420.0, 'gpu_tflops': 0.420 / t, 'mode': 'train-mode norms, no_grad'}))
+
+
+def synthetic_flow(b, h, w, gen):
+    """bilinear upsample of N(0, 8 px) drawn at 32x64."""
+    low = torch.randn(b, 2, 32, 64, generator=gen) * 8.0
+    return torch.nn.functional.interpolate(low, size=(h, w), mode='bilinear', align_corners=False).contiguous()
+
+
+def config4():
+    from imaginaire_b200 import ops
+    h, w = 512, 1024
+    g = torch.Generator().manual_seed(4)
+    for b in (1, 8, 32):
+        for c in (3, 4, 64):
+            if b * c * h * w * 4 > 6e9:
+                continue
+            img = torch.randn(b, c, h, w, generator=g).to(DEV)
+            flow = synthetic_flow(b, h, w, g).to(DEV)
+            go = torch.randn(b, c, h, w, generator=g).to(DEV)
+            fwd_bytes = (2 * c + 2) * b * h * w * 4
+            bwd_bytes = (3 * c + 4) * b * h * w * 4
+            reps = 20 if b * c <= 64 else 5
+            for name, f_fwd, f_bwd in (('resample2d', lambda: ops.resample2d_fwd(img, flow),
+                                        lambda: ops.resample2d_bwd(img, flow, go)),
+                                       ('resample (grid_sample form)', lambda: ops.gridsample_warp_fwd(img, flow),
+                                        lambda: ops.gridsample_warp_bwd(img, flow, go))):
+                tf = gpu_time(f_fwd, reps)
+                tb = gpu_time(f_bwd, reps)
+                print(json.dumps({'config': 'config4 warp %s B=%d C=%d 512x1024' % (name, b, c),
+                                  'fwd_us': tf * 1e6, 'fwd_GBps': fwd_bytes / tf / 1e9, 'fwd_frac_hbm': fwd_bytes / tf / 1e9 / HBM_PEAK,
+                                  'bwd_us': tb * 1e6, 'bwd_GBps': bwd_bytes / tb / 1e9, 'bwd_frac_hbm': bwd_bytes / tb / 1e9 / HBM_PEAK,
+                                  'note': 'B=1: latency, not bandwidth' if b == 1 else ''}))
+            del img, flow, go
+    # CPU restatement of resample2d beside it (C oracle, single thread), B=1 C=3
+    from oracle import warp_oracle as wo
+    import numpy as np
+    img = np.random.default_rng(0).standard_normal((1, 3, h, w), dtype=np.float32)
+    flow = synthetic_flow(1, h, w, g).numpy()
+    t0 = time.perf_counter()
+    wo.resample2d_forward(img, flow)
+    t = time.perf_counter() - t0
+    print(json.dumps({'config': 'config4 cpu oracle resample2d fwd B=1 C=3 512x1024', 'cpu_ms': t * 1e3, 'cores': 1,
+                      'GBps': (2 * 3 + 2) * h * w * 4 / t / 1e9}))
+
+
+def config5():
+    from imaginaire_b200.generators.spade import Generator
+    from imaginaire_b200.utils.init_weight import weights_init
+    cfg = Config(os.path.join(bench.ROOT, 'configs', 'spade_c3_256x512.yaml'))
+    cfg.data.train.augmentations.random_crop_h_w = '512, 1024'
+    torch.manual_seed(0)
+    net = Generator(cfg.gen, cfg.data)
+    net.apply(weights_init('xavier', 0.02))
+    net = net.to(DEV)
+    batch = 4
+    data = {k: v.to(DEV) for k, v in bench.synthetic_batch(cfg, batch, 0).items()}
+    for mode in ('train', 'eval'):
+        net.train(mode == 'train')
+        with torch.no_grad():
+            for _ in range(2):
+                out = net(data)        # train mode: also warms the running statistics used by eval
+            assert tuple(out['fake_images'].shape) == (batch, 3, 512, 1024)
+            assert bool(torch.isfinite(out['fake_images']).all())
+            t = gpu_time(lambda: net(data), 5, 1)
+        print(json.dumps({'config': 'config5: C3 generator, 512x1024, batch %d, forward only, %s-mode norms' % (batch, mode),
+                          'ms': t * 1e3, 'img_s': batch / t, 'gflop_per_img': 4745.0, 'tflops': 4.745 * batch / t,
+                          'frac_of_sustained_bf16': 4.745 * batch / t / _PEAKS['tf_sustained']}))
+
+
+if __name__ == '__main__':
+    which = sys.argv[1] if len(sys.argv) > 1 else 'all'
+    for name, fn in (('config1', config1), ('config4', config4), ('config5', config5)):
+        if which in (name, 'all'):
+            fn()

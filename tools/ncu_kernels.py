@@ -46,10 +46,14 @@ def hbm():
         y = ops.spade_modulate_fwd(x, mean, rstd, None, None, g, b, False, 1)
         ops.spade_modulate_bwd(x, y, mean, rstd, None, None, g, b, False, 1, n * h * w)
     img = torch.randn(8, 64, 512, 1024, device='cuda')
-    flow = torch.randn(8, 2, 512, 1024, device='cuda') * 4
-    for _ in range(3):
+    # SURVEY 8(d) config 4 flow: bilinear upsample of N(0, 8 px) drawn at 32 x 64
+    flow = torch.nn.functional.interpolate(torch.randn(8, 2, 32, 64, device='cuda') * 8.0, size=(512, 1024),
+                                           mode='bilinear', align_corners=False).contiguous()
+    go = torch.randn(8, 64, 512, 1024, device='cuda')
+    for _ in range(2):
         ops.resample2d_fwd(img, flow)
         ops.gridsample_warp_fwd(img, flow)
+        ops.resample2d_bwd(img, flow, go)
     torch.cuda.synchronize()
 
 
