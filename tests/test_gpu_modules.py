@@ -170,3 +170,37 @@ def test_generator_unit_test_vs_reference_golden():
         assert float(diff.max()) <= 0.15 and float(diff.mean()) <= 1.5e-2
         assert float(diff.mean()) <= 2.0 * emu_mean and float(diff.max()) <= 2.5 * emu_max
         assert H.rel_err(out['mu'].cpu(), d['mu']) < 3e-2
+
+
+def test_model_average_update_matches_reference_rule():
+    """ModelAverage.update_average (ref: imaginaire/utils/model_average.py:87-132, 183-197): plain
+    tensors lerp, spectrally normalised filters average W / sigma with sigma = u^T W v from the
+    CURRENT u, v (no power iteration).  The CUDA path batches every layer into two launches; the
+    expectation is the reference's per-layer torch arithmetic on the CPU."""
+    from imaginaire_b200.layers import Conv2dBlock, Res2dBlock
+    from imaginaire_b200.utils.model_average import ModelAverage
+    torch.manual_seed(7)
+    net = torch.nn.Sequential(Conv2dBlock(8, 16, 3, padding=1, weight_norm_type='spectral'),
+                              Res2dBlock(16, 24, weight_norm_type='spectral'),
+                              Conv2dBlock(24, 8, 1, weight_norm_type='none'))
+    cpu = ModelAverage(net, beta=0.9, start_iteration=0, remove_sn=True)
+    import copy
+    gpu = copy.deepcopy(cpu).to(_dev())
+    for step in range(3):
+        with torch.no_grad():
+            for (_, a), (_, b) in zip(cpu.module.state_dict().items(), gpu.module.state_dict().items()):
+                if a.is_floating_point():
+                    noise = torch.randn_like(a) * 0.1
+                    a.add_(noise)
+                    b.add_(noise.to(b.device))
+        cpu.update_average()
+        gpu.update_average()
+    sd_c, sd_g = cpu.averaged_model.state_dict(), gpu.averaged_model.state_dict()
+    assert list(sd_c.keys()) == list(sd_g.keys())
+    assert not any(k.endswith('weight_orig') for k in sd_g)          # remove_sn: W / sigma stored as `weight`
+    for k in sd_c:
+        if sd_c[k].is_floating_point():
+            assert H.rel_err(sd_g[k].cpu(), sd_c[k]) < 1e-5, k
+        else:
+            assert torch.equal(sd_g[k].cpu(), sd_c[k]), k
+    assert int(gpu.num_updates_tracked) == 3
