@@ -455,3 +455,69 @@ def conv2d_wgrad_noalloc(x, dy, cin, cout, kh, kw, stride=1, pad=0, out=None):
     _C.lib().call('imx_conv2d_igemm_wgrad_bf16_noalloc', _ptr(x), _ptr(dy), _ptr(out), n, h, w, cin, cin_p,
                   cout, cout_p, kh, kw, stride, pad, _stream())
     return out
+
+
+# ------------------------------------------------------------ FlowNet2 operators
+
+def _req_nchw_f32(t, name):
+    if not t.is_cuda:
+        raise RuntimeError('imaginaire_b200 ops run on CUDA tensors only (no CPU fallback); %s is on %s' % (name, t.device.type))
+    if t.dim() != 4 or t.dtype != torch.float32 or not t.is_contiguous():
+        raise RuntimeError('%s must be a contiguous 4-D float32 tensor' % name)
+
+
+def channelnorm_fwd(x, norm_deg=2):
+    _req_nchw_f32(x, 'input1')
+    b, c, h, w = x.shape
+    out = torch.empty((b, 1, h, w), dtype=torch.float32, device=x.device)
+    _C.lib().call('imx_channelnorm_fwd_f32', _ptr(x), _ptr(out), b, c, h, w, int(norm_deg), _stream())
+    return out
+
+
+def channelnorm_bwd(x, out, grad_out, norm_deg=2):
+    _req_nchw_f32(x, 'input1'); _req_nchw_f32(out, 'output'); _req_nchw_f32(grad_out, 'grad_output')
+    b, c, h, w = x.shape
+    gin = torch.empty_like(x)
+    _C.lib().call('imx_channelnorm_bwd_f32', _ptr(x), _ptr(out), _ptr(grad_out), _ptr(gin), b, c, h, w, int(norm_deg), _stream())
+    return gin
+
+
+def correlation_output_size(c, h, w, pad_size, kernel_size, max_displacement, stride1, stride2):
+    import ctypes
+    oc, oh, ow = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    _C.lib().call('imx_correlation_output_size', c, h, w, pad_size, kernel_size, max_displacement, stride1, stride2,
+                  ctypes.byref(oc), ctypes.byref(oh), ctypes.byref(ow))
+    _C.lib().launches -= 1      # host-side query, no kernel
+    return oc.value, oh.value, ow.value
+
+
+def _corr_scratch(x, pad_size):
+    b, c, h, w = x.shape
+    return torch.empty((b, h + 2 * pad_size, w + 2 * pad_size, c), dtype=torch.float32, device=x.device)
+
+
+def correlation_fwd(x1, x2, pad_size, kernel_size, max_displacement, stride1, stride2):
+    _req_nchw_f32(x1, 'input1'); _req_nchw_f32(x2, 'input2')
+    if x1.shape != x2.shape:
+        raise RuntimeError('correlation: the two inputs must have the same shape')
+    b, c, h, w = x1.shape
+    oc, oh, ow = correlation_output_size(c, h, w, pad_size, kernel_size, max_displacement, stride1, stride2)
+    out = torch.empty((b, oc, oh, ow), dtype=torch.float32, device=x1.device)
+    r1, r2 = _corr_scratch(x1, pad_size), _corr_scratch(x2, pad_size)
+    lib = _C.lib()
+    lib.call('imx_correlation_fwd_f32', _ptr(x1), _ptr(x2), _ptr(r1), _ptr(r2), _ptr(out), b, c, h, w, pad_size,
+             kernel_size, max_displacement, stride1, stride2, _stream())
+    lib.launches += 2
+    return out
+
+
+def correlation_bwd(x1, x2, grad_out, pad_size, kernel_size, max_displacement, stride1, stride2):
+    _req_nchw_f32(x1, 'input1'); _req_nchw_f32(x2, 'input2'); _req_nchw_f32(grad_out, 'grad_output')
+    b, c, h, w = x1.shape
+    g1, g2 = torch.empty_like(x1), torch.empty_like(x2)
+    r1, r2 = _corr_scratch(x1, pad_size), _corr_scratch(x2, pad_size)
+    lib = _C.lib()
+    lib.call('imx_correlation_bwd_f32', _ptr(x1), _ptr(x2), _ptr(grad_out), _ptr(r1), _ptr(r2), _ptr(g1), _ptr(g2),
+             b, c, h, w, pad_size, kernel_size, max_displacement, stride1, stride2, _stream())
+    lib.launches += 3
+    return g1, g2

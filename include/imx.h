@@ -354,6 +354,41 @@ IMX_API int imx_channel_sum_nhwc_bf16(const imx_bf16* x, float* out, int NP, int
 IMX_API int imx_act_bwd_bias_nhwc_bf16(const imx_bf16* dy, const imx_bf16* y, imx_bf16* dx, float* bias_grad,
                                int64_t NP, int C, int act, imx_stream_t stream);
 
+/* ------------------------------------------------- FlowNet2 operators -- */
+
+/* output[b,0,y,x] = sqrt(sum_c input[b,c,y,x]^2) and its gradient
+ * grad_input = grad_output * input / (output + 1e-9).  NCHW fp32 contiguous.  norm_deg must be
+ * 2 (the reference accepts the argument and ignores it).  The reference's Python side zero-fills
+ * the outputs first; these kernels write every element, so that is not required.
+ * ref: channelnorm_cuda.forward / backward, imaginaire/third_party/channelnorm/src/
+ *      channelnorm_cuda.cc:6-30, channelnorm_kernel.cu:18-96, channelnorm.py:8-32 */
+IMX_API int imx_channelnorm_fwd_f32(const float* input, float* output, int B, int C, int H, int W, int norm_deg,
+                            imx_stream_t stream);
+IMX_API int imx_channelnorm_bwd_f32(const float* input, const float* output, const float* grad_output,
+                            float* grad_input, int B, int C, int H, int W, int norm_deg, imx_stream_t stream);
+
+/* FlowNetC correlation (cost volume).  output[b, (tj,ti), y, x] = 1/(k*k*C) * sum over the
+ * k x k patch and channels of pad(input1)[y1+j, x1+i] * pad(input2)[y1+tj*stride2+j, ...], with
+ * (y1, x1) = (y, x) * stride1 + max_displacement, displacements tj, ti in
+ * [-max_displacement/stride2, +max_displacement/stride2].  Inputs NCHW fp32 [B,C,H,W]; rbot1 /
+ * rbot2: caller-owned scratch of B*(H+2*pad)*(W+2*pad)*C floats each (the reference's rInput1/2,
+ * which its callee resizes; here the caller sizes them, nothing is allocated); output
+ * [B, out_channels, out_h, out_w] from imx_correlation_output_size (host-side, no stream).
+ * The gradient needs stride1 == 1 and pad_size >= max_displacement; grad_input1/2 are fully
+ * written.  Geometries whose reads would leave the padded planes are refused (the reference
+ * reads out of bounds for kernel_size > 1).  corr_type_multiply is always 1 in the reference.
+ * ref: correlation_cuda.forward / backward, imaginaire/third_party/correlation/src/
+ *      correlation_cuda.cc:10-172, correlation_cuda_kernel.cu:46-336, correlation.py:8-105 */
+IMX_API int imx_correlation_output_size(int C, int H, int W, int pad_size, int kernel_size, int max_displacement,
+                                int stride1, int stride2, int* out_channels, int* out_h, int* out_w);
+IMX_API int imx_correlation_fwd_f32(const float* input1, const float* input2, float* rbot1, float* rbot2, float* output,
+                            int B, int C, int H, int W, int pad_size, int kernel_size, int max_displacement,
+                            int stride1, int stride2, imx_stream_t stream);
+IMX_API int imx_correlation_bwd_f32(const float* input1, const float* input2, const float* grad_output,
+                            float* rbot1, float* rbot2, float* grad_input1, float* grad_input2,
+                            int B, int C, int H, int W, int pad_size, int kernel_size, int max_displacement,
+                            int stride1, int stride2, imx_stream_t stream);
+
 /* ------------------------------------------------------------ optimizer -- */
 
 /* One Adam step (torch.optim.Adam arithmetic, no amsgrad) over n_tensors fp32 tensors:

@@ -440,3 +440,58 @@ def test_fused_adam_matches_torch_adam(betas, wd):
     cpu_p.grad = torch.ones(3)
     with pytest.raises(RuntimeError):
         FusedAdam([cpu_p]).step()       # no CPU fallback
+
+
+# ------------------------------------------------- FlowNet2 operators
+
+@pytest.mark.parametrize('shape', [(2, 3, 17, 23), (1, 2, 64, 96), (3, 64, 5, 7), (1, 1, 1, 1)])
+def test_channelnorm_bit_exact_vs_oracle(shape):
+    from oracle import flownet_ops_oracle as fo
+    from imaginaire_b200.third_party.channelnorm import ChannelNorm
+    g = torch.Generator().manual_seed(61)
+    x = torch.randn(*shape, generator=g)
+    xd = x.to(DEV).requires_grad_(True)
+    y = ChannelNorm()(xd)
+    ref = fo.channelnorm_forward(x.numpy())
+    assert np.array_equal(y.detach().cpu().numpy(), ref)
+    go = torch.randn(y.shape, generator=g)
+    y.backward(go.to(DEV))
+    assert np.array_equal(xd.grad.cpu().numpy(), fo.channelnorm_backward(x.numpy(), ref, go.numpy()))
+    with pytest.raises(Exception):
+        ChannelNorm(norm_deg=1)(xd)
+
+
+@pytest.mark.parametrize('case', [(2, 64, 12, 16, 20, 1, 20, 1, 2),      # FlowNetC geometry
+                                  (1, 40, 9, 11, 4, 1, 4, 1, 2),          # channels not a multiple of 32
+                                  (2, 32, 10, 14, 4, 1, 4, 1, 1),
+                                  (1, 16, 13, 15, 7, 3, 5, 1, 2)])        # 3x3 patches
+def test_correlation_bit_exact_vs_oracle(case):
+    """Forward and both gradients of the FlowNetC correlation.  The kernels keep the reference's
+    lane assignment and reduction order, the oracle emulates the 32 lanes: bit-exact."""
+    from oracle import flownet_ops_oracle as fo
+    from imaginaire_b200.third_party.correlation import Correlation
+    b, c, h, w, pad, k, md, s1, s2 = case
+    g = torch.Generator().manual_seed(62)
+    x1, x2 = torch.randn(b, c, h, w, generator=g), torch.randn(b, c, h, w, generator=g)
+    d1, d2 = x1.to(DEV).requires_grad_(True), x2.to(DEV).requires_grad_(True)
+    out = Correlation(pad_size=pad, kernel_size=k, max_displacement=md, stride1=s1, stride2=s2)(d1, d2)
+    ref = fo.correlation_forward(x1.numpy(), x2.numpy(), pad, k, md, s1, s2)
+    assert tuple(out.shape) == ref.shape
+    assert np.array_equal(out.detach().cpu().numpy(), ref)
+    go = torch.randn(out.shape, generator=g)
+    out.backward(go.to(DEV))
+    g1, g2 = fo.correlation_backward(x1.numpy(), x2.numpy(), go.numpy(), pad, k, md, s1, s2)
+    assert np.array_equal(d1.grad.cpu().numpy(), g1)
+    assert np.array_equal(d2.grad.cpu().numpy(), g2)
+
+
+def test_correlation_rejects_geometry_the_reference_reads_out_of_bounds_for():
+    from imaginaire_b200 import ops, _C
+    x = torch.randn(1, 8, 8, 8, device=DEV)
+    with pytest.raises(_C.ImxError):
+        ops.correlation_fwd(x, x, 4, 3, 4, 1, 2)          # 3x3 patches need pad >= max_displacement + 1
+    out = ops.correlation_fwd(x, x, 4, 1, 4, 2, 2)        # stride1 = 2 forward is fine ...
+    with pytest.raises(_C.ImxError):
+        ops.correlation_bwd(x, x, torch.zeros_like(out), 4, 1, 4, 2, 2)   # ... its gradient is not
+    with pytest.raises(RuntimeError):
+        ops.correlation_fwd(x.cpu(), x.cpu(), 4, 1, 4, 1, 2)              # no CPU fallback

@@ -118,3 +118,41 @@ def test_resample2d_oracle_backward_is_the_derivative():
         fp[0, ch, y, x] += 1e-2; fm[0, ch, y, x] -= 1e-2
         num = ((wo.resample2d_forward(img, fp) - wo.resample2d_forward(img, fm)) * gout).sum() / 2e-2
         assert abs(num - gflow[0, ch, y, x]) < 2e-2 * max(1.0, abs(num))
+
+
+# ------------------------------------------------- FlowNet2 operators
+
+def test_flownet_ops_oracle_known_answers():
+    """The reference has neither tests nor a buildable extension for channelnorm / correlation
+    ('parity unpinned'): the C restatement is held to the operators' mathematical definition,
+    evaluated independently in float64 (forward) and by torch autograd (gradients)."""
+    import numpy as np
+    import torch
+    from oracle import flownet_ops_oracle as fo
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal((2, 5, 6, 7), dtype=np.float32)
+    o = fo.channelnorm_forward(x)
+    assert np.abs(o - np.sqrt((x.astype(np.float64) ** 2).sum(1, keepdims=True))).max() < 1e-6
+    g = rng.standard_normal(o.shape, dtype=np.float32)
+    assert np.abs(fo.channelnorm_backward(x, o, g) - g * x / (o + 1e-9)).max() < 1e-6
+
+    x1 = rng.standard_normal((2, 40, 9, 11), dtype=np.float32)
+    x2 = rng.standard_normal((2, 40, 9, 11), dtype=np.float32)
+    pad, k, md, s1, s2 = 4, 1, 4, 1, 2
+    assert fo.correlation_output_size(40, 9, 11, pad, k, md, s1, s2) == (25, 9, 11)
+    assert fo.correlation_output_size(256, 48, 64, 20, 1, 20, 1, 2) == (441, 48, 64)     # FlowNetC
+    out = fo.correlation_forward(x1, x2, pad, k, md, s1, s2)
+    t1 = torch.tensor(x1, dtype=torch.float64, requires_grad=True)
+    t2 = torch.tensor(x2, dtype=torch.float64, requires_grad=True)
+    q1 = torch.nn.functional.pad(t1, (pad,) * 4)
+    q2 = torch.nn.functional.pad(t2, (pad,) * 4)
+    d, (hh, ww) = md // s2, out.shape[2:]
+    ref = torch.stack([(q1[:, :, md:md + hh, md:md + ww] *
+                        q2[:, :, md + tj * s2:md + tj * s2 + hh, md + ti * s2:md + ti * s2 + ww]).sum(1) / 40
+                       for tj in range(-d, d + 1) for ti in range(-d, d + 1)], 1)
+    assert np.abs(out - ref.detach().numpy()).max() < 1e-6
+    go = rng.standard_normal(out.shape, dtype=np.float32)
+    ref.backward(torch.tensor(go, dtype=torch.float64))
+    g1, g2 = fo.correlation_backward(x1, x2, go, pad, k, md, s1, s2)
+    assert np.abs(g1 - t1.grad.numpy()).max() < 1e-6
+    assert np.abs(g2 - t2.grad.numpy()).max() < 1e-6
