@@ -354,7 +354,11 @@ def run_ours(args):
     roofline = {
         'bound': 'tensor', 'kernel': 'conv_igemm_kernel / conv_wgrad_kernel (tcgen05 implicit GEMM), all launches of one iteration',
         'achieved': achieved, 'peak': peaks['tf_sustained'], 'unit': 'TFLOP/s', 'frac': achieved / peaks['tf_sustained'],
-        'traffic': None, 'peak_source': peaks['source'] + ' bf16_tflops_sustained (kernel timed inside a long step)',
+        # dram__bytes_read.sum + dram__bytes_write.sum of the family's most frequent launch (conv_igemm_kernel<256,0,1>,
+        # 3x3 512->512 at 8x128x256) from profiles/r01b_ncu_full_conv_summary.md; its algorithmic traffic is 541 MB
+        # (x 268 + filter 4.7 + y 268; part of y was still in L2 when the kernel ended)
+        'traffic': 273.9e6 + 223.5e6, 'traffic_unit': 'bytes per launch (ncu --set full, one launch of the dominant shape)',
+        'peak_source': peaks['source'] + ' bf16_tflops_sustained (kernel timed inside a long step)',
         'conv_share_of_step': conv_ms / ms_per_step if ms_per_step > 0 else None,
         'by_kind': {k: {'tflops': v[0] / (v[1] * 1e-3) / 1e12 if v[1] > 0 else 0.0, 'ms': v[1], 'launches': v[2]}
                     for k, v in by.items()},
