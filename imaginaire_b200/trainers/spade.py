@@ -39,7 +39,9 @@ class Trainer:
     # ----------------------------------------------------------- generator
     def gen_forward(self, data):
         net_G_output = self.net_G(data)
-        net_D_output = self.net_D(data, net_G_output)
+        # the discriminator is frozen here: no gradient exchange to set up, so the data-parallel
+        # wrapper is bypassed (same computation)
+        net_D_output = self.net_D.module(data, net_G_output)
         losses = self.gen_losses
         losses['GAN'] = self.criteria['GAN'](net_D_output['fake_outputs'], True, dis_update=False)
         losses['FeatureMatching'] = self.criteria['FeatureMatching'](net_D_output['fake_features'],
@@ -68,7 +70,7 @@ class Trainer:
     # -------------------------------------------------------- discriminator
     def dis_forward(self, data):
         with torch.no_grad():
-            net_G_output = self.net_G(data)
+            net_G_output = self.net_G.module(data)      # no_grad: nothing for the DDP wrapper to do
             net_G_output['fake_images'] = net_G_output['fake_images'].detach()
         net_D_output = self.net_D(data, net_G_output)
         fake = self.criteria['GAN'](net_D_output['fake_outputs'], False, dis_update=True)

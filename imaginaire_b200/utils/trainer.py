@@ -6,6 +6,7 @@ apex is replaced as SURVEY.md Appendix C prescribes: mixed precision is the kern
 bf16-storage / fp32-accumulate arithmetic (no loss scaling), apex FusedAdam becomes
 imaginaire_b200.optim.FusedAdam (csrc/optim.cu), apex DDP becomes torch DDP over NCCL.
 """
+import os
 import random
 
 import numpy as np
@@ -62,7 +63,8 @@ def wrap_model_and_optimizer(cfg, net_G, net_D, opt_G, opt_D):
         net_G = ModelAverage(net_G, cfg.trainer.model_average_beta,
                              cfg.trainer.model_average_start_iteration,
                              getattr(cfg.trainer, 'model_average_remove_sn', True))
-    return _wrap_model(net_G), _wrap_model(net_D), opt_G, opt_D
+    find_unused = getattr(cfg.trainer, 'ddp_find_unused_parameters', None)
+    return _wrap_model(net_G, find_unused), _wrap_model(net_D, find_unused), opt_G, opt_D
 
 
 class WrappedModel(torch.nn.Module):
@@ -76,10 +78,20 @@ class WrappedModel(torch.nn.Module):
         return self.module(*args, **kwargs)
 
 
-def _wrap_model(model):
+def _wrap_model(model, find_unused=None):
+    """find_unused: None = the reference's setting (True, utils/trainer.py:203-214) unless the
+    environment variable IMX_DDP_FIND_UNUSED=0 says that every trainable parameter takes part in every
+    backward (true for the SPADE trainer here, which calls a frozen network through .module, not
+    through the DDP wrapper): the per-iteration autograd-graph walk is then skipped."""
     if get_world_size() > 1:
-        return DistributedDataParallel(model, device_ids=[torch.cuda.current_device()],
-                                       output_device=torch.cuda.current_device(),
-                                       find_unused_parameters=True, broadcast_buffers=False,
-                                       gradient_as_bucket_view=True, bucket_cap_mb=64)
+        if find_unused is None:
+            find_unused = os.environ.get('IMX_DDP_FIND_UNUSED', '1') != '0'
+        ddp = DistributedDataParallel(model, device_ids=[torch.cuda.current_device()],
+                                      output_device=torch.cuda.current_device(),
+                                      find_unused_parameters=bool(find_unused), broadcast_buffers=False,
+                                      gradient_as_bucket_view=True, bucket_cap_mb=int(os.environ.get('IMX_DDP_BUCKET_MB', '256')))
+        if os.environ.get('IMX_DDP_BF16', '0') == '1':
+            from torch.distributed.algorithms.ddp_comm_hooks import default_hooks
+            ddp.register_comm_hook(None, default_hooks.bf16_compress_hook)
+        return ddp
     return WrappedModel(model)

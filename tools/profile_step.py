@@ -9,7 +9,12 @@ from imaginaire_b200.trainers.spade import Trainer
 from imaginaire_b200.utils.trainer import get_model_optimizer_and_scheduler
 
 cfg = Config(os.path.join(bench.ROOT, 'configs', bench.CONFIG_NAME))
-dev = torch.device('cuda:0')
+world, rank, local = int(os.environ.get('WORLD_SIZE', 1)), int(os.environ.get('RANK', 0)), int(os.environ.get('LOCAL_RANK', 0))
+torch.cuda.set_device(local)
+dev = torch.device('cuda', local)
+if world > 1:
+    import torch.distributed as dist
+    dist.init_process_group('nccl', init_method='env://')
 net_G, net_D, opt_G, opt_D = get_model_optimizer_and_scheduler(cfg, seed=0, device=dev)
 trainer = Trainer(cfg, net_G, net_D, opt_G, opt_D)
 data = {k: v.to(dev) for k, v in bench.synthetic_batch(cfg, int(sys.argv[1]) if len(sys.argv) > 1 else 8, 100).items()}
@@ -19,6 +24,8 @@ torch.cuda.synchronize()
 with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
     trainer.step(dict(data))
     torch.cuda.synchronize()
+if rank != 0:
+    sys.exit(0)
 rows = []
 for e in prof.key_averages():
     t = getattr(e, 'device_time_total', None)
