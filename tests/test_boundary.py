@@ -109,3 +109,31 @@ def test_reference_yaml_files_load_unchanged():
     cfg = Config('/root/reference/configs/unit_test/spade.yaml')
     net = Generator(cfg.gen, cfg.data)
     assert sum(p.numel() for p in net.parameters()) == 109247811
+
+
+def _flow_generator_cfgs():
+    import types
+    ns = types.SimpleNamespace
+    data_cfg = ns(input_types=[{'images': ns(num_channels=3)}, {'seg_maps': ns(num_channels=12)}],
+                  input_image=['images'], input_labels=['seg_maps'], num_frames_G=3)
+    flow_cfg = ns(num_filters=16, max_num_filters=64, num_downsamples=2, kernel_size=3, num_res_blocks=2,
+                  flow_output_multiplier=20, activation_norm_type='sync_batch', weight_norm_type='spectral')
+    return flow_cfg, data_cfg
+
+
+def test_flow_generator_seeded_build_reproduces_reference_weights():
+    """vid2vid FlowGenerator (ref: imaginaire/generators/vid2vid.py:390-481): same state-dict keys in
+    the same order and, built with the same seed + the trainer's weights_init, bit-identical
+    parameters to the reference module (golden made by oracle/make_golden_vid2vid.py)."""
+    from imaginaire_b200.generators.vid2vid import FlowGenerator
+    from imaginaire_b200.utils.init_weight import weights_init
+    d = H.load_golden('flow_generator_a.npz')
+    torch.manual_seed(11)
+    net = FlowGenerator(*_flow_generator_cfgs())
+    net.apply(weights_init('xavier', 0.02))
+    sd = net.state_dict()
+    assert list(sd.keys()) == [str(k) for k in d['keys']]
+    ref = H.split_sd(d, 'sd.')
+    for k in sd:
+        assert torch.equal(sd[k], ref[k]), k
+    net.load_state_dict(ref, strict=True)

@@ -98,6 +98,40 @@ def config4():
                       'GBps': (2 * 3 + 2) * h * w * 4 / t / 1e9}))
 
 
+def config4_flow_branch():
+    """vid2vid flow branch at 512x1024 (Cityscapes-shaped: 35 label channels, 3 frames): FlowGenerator
+    (defaults of configs/projects/vid2vid/cityscapes/ampO1.yaml: 32 filters, 5 downsamples, 6 res blocks) ->
+    flow, mask -> warp of the previous frame -> composite; forward + backward, batch 1 and 4."""
+    import types
+    from imaginaire_b200.generators.vid2vid import FlowGenerator, warp_prev_frame
+    from imaginaire_b200.utils.init_weight import weights_init
+    ns = types.SimpleNamespace
+    data_cfg = ns(input_types=[{'images': ns(num_channels=3)}, {'seg_maps': ns(num_channels=35)}],
+                  input_image=['images'], input_labels=['seg_maps'], num_frames_G=3)
+    torch.manual_seed(0)
+    net = FlowGenerator(ns(), data_cfg)
+    net.apply(weights_init('xavier', 0.02))
+    net = net.to(DEV).train()
+    h, w = 512, 1024
+    for b in (1, 4):
+        g = torch.Generator().manual_seed(5)
+        idx = torch.randint(0, 35, (b, 3, h // 8, w // 8), generator=g).repeat_interleave(8, 2).repeat_interleave(8, 3)
+        label = torch.zeros(b, 3, 35, h, w).scatter_(2, idx.unsqueeze(2), 1.0).view(b, 105, h, w).to(DEV)
+        img_prev = (torch.rand(b, 6, h, w, generator=g) * 2 - 1).to(DEV)
+        raw = (torch.rand(b, 3, h, w, generator=g) * 2 - 1).to(DEV)
+
+        def step():
+            flow, mask = net(label, img_prev)
+            warp = warp_prev_frame(img_prev[:, -3:], flow)
+            final = raw * mask + warp * (1 - mask)
+            final.square().mean().backward()
+        with torch.no_grad():
+            tf = gpu_time(lambda: net(label, img_prev), 5, 2)
+        t = gpu_time(step, 5, 2)
+        print(json.dumps({'config': 'config4 vid2vid flow branch (FlowGenerator + warp + composite) 512x1024 B=%d' % b,
+                          'fwd_ms': tf * 1e3, 'fwd_bwd_ms': t * 1e3, 'frames_per_s_train': b / t}))
+
+
 def config5():
     from imaginaire_b200.generators.spade import Generator
     from imaginaire_b200.utils.init_weight import weights_init
@@ -124,6 +158,6 @@ def config5():
 
 if __name__ == '__main__':
     which = sys.argv[1] if len(sys.argv) > 1 else 'all'
-    for name, fn in (('config1', config1), ('config4', config4), ('config5', config5)):
+    for name, fn in (('config1', config1), ('config4', config4), ('config4', config4_flow_branch), ('config5', config5)):
         if which in (name, 'all'):
             fn()
