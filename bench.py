@@ -275,6 +275,8 @@ def run_ours(args):
     dev = torch.device('cuda', local_rank)
     if world > 1:
         os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        # collectives on a high-priority stream: their CTAs are placed before the next persistent conv kernel's
+        os.environ.setdefault('TORCH_NCCL_HIGH_PRIORITY', '1')
         dist.init_process_group('nccl', init_method='env://')
     _C.lib()   # fails loudly if the CUDA library is missing
 
