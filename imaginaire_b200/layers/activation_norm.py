@@ -177,8 +177,12 @@ class SpatiallyAdaptiveNorm(nn.Module):
     # -- conditioning map at the feature resolution, once per resolution per forward ------
     @staticmethod
     def _resized_cond(cond, h, w):
-        if ops.is_nhwc_bf16(cond) and cond.shape[2] == h and cond.shape[3] == w:
-            return cond
+        if ops.is_nhwc_bf16(cond):
+            if cond.shape[2] == h and cond.shape[3] == w:
+                return cond
+            # feature maps of an embedding network used below their own resolution (vid2vid's
+            # coarsest SPADE layers): nearest resize in place of the layout (differentiable)
+            return F.interpolate(cond, size=(h, w), mode='nearest')
         if cond.requires_grad:
             # learned conditioning maps (vid2vid label embeddings): keep it differentiable
             return NF.to_nhwc(F.interpolate(cond.float(), size=(h, w), mode='nearest'))

@@ -235,3 +235,34 @@ def test_flow_generator_and_warp_vs_reference_golden():
     # the warp itself is exact: same flow in, bit-identical to the reference's resample()
     warp = warp_prev_frame(img_prev[:, -3:], torch.from_numpy(d['flow']).to(_dev()))
     assert torch.equal(warp.cpu(), torch.from_numpy(d['warp']))
+
+
+def test_vid2vid_generator_first_and_temporal_frame_vs_reference_golden():
+    """The vid2vid generator (ref: imaginaire/generators/vid2vid.py:39-388) in miniature: label
+    embedder -> SPADE up-blocks with 1x1 projections on embedded labels (multi-cond lists), first
+    frame from z = 0, and the temporal frame: previous-frame encoder, flow network, warp,
+    multi-SPADE combine.  Golden from the reference modules on CPU (flow_network_temp restored as
+    upstream has it).  Outputs are tanh of a randomly initialised net (|y| ~ 0.02): errors are
+    taken relative to the output scale."""
+    from imaginaire_b200.generators.vid2vid import Generator
+    from oracle.make_golden_vid2vid import generator_configs
+    d = H.load_golden('vid2vid_generator_a.npz')
+    net = Generator(*generator_configs())
+    assert sorted(net.state_dict().keys()) == [str(k) for k in d['keys']]
+    net.load_state_dict(H.split_sd(d, 'sd.'), strict=True)
+    net = net.to(_dev()).train()
+    labels = torch.from_numpy(d['labels']).to(_dev())
+    prev_images = torch.from_numpy(d['prev_images']).to(_dev())
+    with torch.no_grad():
+        first = net({'label': labels[:, 0], 'prev_labels': None, 'prev_images': None})
+        temporal = net({'label': labels[:, 2], 'prev_labels': labels[:, :2], 'prev_images': prev_images})
+    for name, out, ref in (('first', first['fake_images'], d['first_fake']),
+                           ('temporal', temporal['fake_images'], d['temporal_fake']),
+                           ('flow', temporal['fake_flow_maps'], d['temporal_flow']),
+                           ('warp', temporal['warped_images'], d['temporal_warp'])):
+        ref = torch.from_numpy(ref)
+        assert out.shape == ref.shape and out.dtype == torch.float32, name
+        assert H.rel_err(out.cpu(), ref) < 8e-2, (name, H.rel_err(out.cpu(), ref))
+        assert float((out.cpu() - ref).abs().mean() / ref.abs().mean()) < 4e-2, name
+    assert float((temporal['fake_occlusion_masks'].cpu() - torch.from_numpy(d['temporal_mask'])).abs().max()) < 2e-2
+    assert first['fake_flow_maps'] is None and first['warped_images'] is None
