@@ -132,6 +132,47 @@ def config4_flow_branch():
                           'fwd_ms': tf * 1e3, 'fwd_bwd_ms': t * 1e3, 'frames_per_s_train': b / t}))
 
 
+def config4_generator():
+    """vid2vid generator of configs/projects/vid2vid/cityscapes/ampO1.yaml (num_layers 7, 32 filters, instance-norm
+    SPADE with 1x1 projections on embedded labels, unet image embedder, multi-SPADE combine), 512x1024, 35 labels,
+    temporal frame (previous-frame encoder + flow network + warp + generator), forward and forward+backward."""
+    import types
+    from imaginaire_b200.generators.vid2vid import Generator
+    from imaginaire_b200.utils.init_weight import weights_init
+    ns = types.SimpleNamespace
+    data_cfg = ns(input_types=[{'images': ns(num_channels=3)}, {'seg_maps': ns(num_channels=35)}],
+                  input_image=['images'], input_labels=['seg_maps'], num_frames_G=3,
+                  val=ns(augmentations=ns(center_crop_h_w='512, 1024')))
+    emb = lambda arch: ns(use_embed=True, arch=arch, num_filters=32, num_downsamples=5, kernel_size=3,
+                          weight_norm_type='spectral')
+    flow = ns(num_filters=32, max_num_filters=1024, num_downsamples=5, num_res_blocks=6, activation_norm_type='instance',
+              weight_norm_type='spectral', flow_output_multiplier=40, generate_raw_output=False,
+              multi_spade_combine=ns(num_layers=3, embed=emb('unet')))
+    gen_cfg = ns(num_layers=7, num_downsamples_img=4, num_filters=32, max_num_filters=1024, kernel_size=3,
+                 activation_norm_type='spatially_adaptive',
+                 activation_norm_params=ns(activation_norm_type='instance', num_filters=0, kernel_size=1),
+                 weight_norm_type='spectral', style_dims=256, use_segmap_as_input=True, flow=flow, embed=emb('encoderdecoder'))
+    torch.manual_seed(0)
+    net = Generator(gen_cfg, data_cfg)
+    net.apply(weights_init('xavier', 0.02))
+    net = net.to(DEV).train()
+    h, w, b = 512, 1024, 1
+    g = torch.Generator().manual_seed(6)
+    idx = torch.randint(0, 35, (b, 3, h // 8, w // 8), generator=g).repeat_interleave(8, 2).repeat_interleave(8, 3)
+    labels = torch.zeros(b, 3, 35, h, w).scatter_(2, idx.unsqueeze(2), 1.0).to(DEV)
+    imgs = (torch.rand(b, 2, 3, h, w, generator=g) * 2 - 1).to(DEV)
+    first = {'label': labels[:, 0], 'prev_labels': None, 'prev_images': None}
+    temporal = {'label': labels[:, 2], 'prev_labels': labels[:, :2], 'prev_images': imgs}
+    with torch.no_grad():
+        t_first = gpu_time(lambda: net(first), 5, 2)
+        t_temp = gpu_time(lambda: net(temporal), 5, 2)
+    t_train = gpu_time(lambda: net(temporal)['fake_images'].square().mean().backward(), 5, 2)
+    print(json.dumps({'config': 'config4 vid2vid generator (cityscapes ampO1 architecture) 512x1024 B=1',
+                      'params_M': sum(p.numel() for p in net.parameters()) / 1e6,
+                      'first_frame_fwd_ms': t_first * 1e3, 'temporal_frame_fwd_ms': t_temp * 1e3,
+                      'temporal_frame_fwd_bwd_ms': t_train * 1e3, 'frames_per_s_inference': 1.0 / t_temp}))
+
+
 def config5():
     from imaginaire_b200.generators.spade import Generator
     from imaginaire_b200.utils.init_weight import weights_init
@@ -158,6 +199,6 @@ def config5():
 
 if __name__ == '__main__':
     which = sys.argv[1] if len(sys.argv) > 1 else 'all'
-    for name, fn in (('config1', config1), ('config4', config4), ('config4', config4_flow_branch), ('config5', config5)):
+    for name, fn in (('config1', config1), ('config4', config4), ('config4', config4_flow_branch), ('config4', config4_generator), ('config5', config5)):
         if which in (name, 'all'):
             fn()
