@@ -366,6 +366,10 @@ def run_ours(args):
                     for k, v in by.items()},
     }
 
+    if os.environ.get('IMX_BENCH_CHECKSUM') and rank == 0:
+        gsum = sum(float(p.detach().double().abs().sum()) for p in net_G.parameters())
+        dsum = sum(float(p.detach().double().abs().sum()) for p in net_D.parameters())
+        print('checksum G %.9e D %.9e' % (gsum, dsum), file=sys.stderr, flush=True)
     value = world * batch * args.steps / (ms * 1e-3)
     e2e_value = world * batch * args.steps / (ms_e2e * 1e-3)
     line = {

@@ -281,6 +281,56 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restr
     }
 }
 
+constexpr int kMaxPeers = 8;
+struct PeerPtrs { const float* p[kMaxPeers]; };
+
+// Data-parallel weight gradient without a separate collective: every rank's split-K partials live
+// in peer-mapped (NVLink) memory; this rank sums, over ALL ranks and splits, the output channels
+// [co_begin, co_end) it owns and writes scale * sum into its own gradient tensor (PyTorch layout).
+// The other ranks' channel ranges are fetched later by gather_rows_peers_kernel.
+__global__ void wgrad_reduce_peers_kernel(PeerPtrs ws, int world, float* __restrict__ dw, int co_begin, int co_end,
+                                          int Cin, int taps, int splits, int co_r, int ci_r, float scale, int accumulate) {
+    const long total = (long)(co_end - co_begin) * Cin * taps;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int ci = (int)(i % Cin);
+        long t = i / Cin;
+        const int tap = (int)(t % taps);
+        const int co = co_begin + (int)(t / taps);
+        float acc = 0.0f;
+        for (int q = 0; q < world; ++q) {
+            const float* w = ws.p[q];
+            for (int s = 0; s < splits; ++s) acc += __ldg(w + (((size_t)s * taps + tap) * co_r + co) * ci_r + ci);
+        }
+        float* dst = dw + ((size_t)co * Cin + ci) * taps + tap;
+        *dst = accumulate ? fmaf(scale, acc, *dst) : scale * acc;
+    }
+}
+
+struct GatherDesc { long long offset, rows, row_elems; };   // mirrored by imaginaire_b200/grad_sync.py (3 x int64)
+
+// All-gather of the reduced gradients: tensor d (rows x row_elems floats at `offset` of the
+// symmetric arena) takes rows [q*rows/world, (q+1)*rows/world) from peer q's arena, for every q
+// other than this rank.  grid = (blocks, n_tensors).
+__global__ void gather_rows_peers_kernel(PeerPtrs arena, float* __restrict__ mine, const GatherDesc* __restrict__ descs,
+                                         int world, int rank) {
+    const GatherDesc d = descs[blockIdx.y];
+    for (int q = 0; q < world; ++q) {
+        if (q == rank) continue;
+        const long long lo = d.rows * q / world * d.row_elems, hi = d.rows * (q + 1) / world * d.row_elems;
+        const float* src = arena.p[q] + d.offset;
+        float* dst = mine + d.offset;
+        const long long n = hi - lo;
+        if (n <= 0) continue;
+        const bool vec = (((uintptr_t)(src + lo) | (uintptr_t)(dst + lo)) & 15) == 0;
+        const long long n4 = vec ? n / 4 : 0;
+        const long long stride = (long long)gridDim.x * blockDim.x;
+        for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += stride)
+            reinterpret_cast<float4*>(dst + lo)[i] = __ldcs(reinterpret_cast<const float4*>(src + lo) + i);
+        for (long long i = n4 * 4 + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += stride)
+            dst[lo + i] = __ldcs(src + lo + i);
+    }
+}
+
 struct Plan {
     int BN, Ho, Wo, tw, th, tw_log2, tiles_x, tiles_y, ptiles, co_tiles, ci_tiles, splits;
     long ws_floats;
@@ -362,20 +412,15 @@ extern "C" int64_t imx_conv2d_wgrad_workspace_bytes(int N, int H, int W, int Cin
     return pl.ws_floats * 4;
 }
 
-extern "C" int imx_conv2d_igemm_wgrad_bf16(const imx_bf16* x, const imx_bf16* dy, float* dw,
-                                           void* workspace, int64_t workspace_bytes,
-                                           int N, int H, int W, int Cin, int Cin_p,
-                                           int Cout, int Cout_p, int KH, int KW,
-                                           int stride, int pad, imx_stream_t stream) {
-    IMX_REQUIRE(x && dy && dw, "conv2d_wgrad: null pointer");
+namespace {
+
+// The split-K GEMM: fills workspace[split][tap][co_r][ci_r] (fp32) and reports the plan.
+int wgrad_gemm(const imx_bf16* x, const imx_bf16* dy, void* workspace, int64_t workspace_bytes, int N, int H, int W,
+               int Cin, int Cin_p, int Cout, int Cout_p, int KH, int KW, int stride, int pad, cudaStream_t s,
+               WgradArgs& a, Plan& pl) {
+    IMX_REQUIRE(x && dy, "conv2d_wgrad: null pointer");
     int rc = check_wgrad_args(N, H, W, Cin, Cin_p, Cout, Cout_p, KH, KW, stride, pad);
     if (rc) return rc;
-    cudaStream_t s = (cudaStream_t)stream;
-    if (N == 0) {
-        cudaError_t e = cudaMemsetAsync(dw, 0, (size_t)Cout * Cin * KH * KW * 4, s);
-        return e == cudaSuccess ? IMX_OK : imx::set_error((int)e, "conv2d_wgrad: memset failed");
-    }
-    Plan pl;
     rc = make_plan(pl, N, H, W, Cin_p, Cout_p, KH, KW, stride, pad);
     if (rc) return rc;
     IMX_REQUIRE(workspace && workspace_bytes >= pl.ws_floats * 4,
@@ -383,7 +428,7 @@ extern "C" int imx_conv2d_igemm_wgrad_bf16(const imx_bf16* x, const imx_bf16* dy
                 (long long)pl.ws_floats * 4);
     IMX_REQUIRE(aligned16(x) && aligned16(dy) && aligned16(workspace), "conv2d_wgrad: pointers must be 16-byte aligned");
 
-    WgradArgs a{};
+    a = WgradArgs{};
     a.N = N; a.Ho = pl.Ho; a.Wo = pl.Wo;
     a.KH = KH; a.KW = KW; a.stride = stride; a.pad = pad;
     a.tw = pl.tw; a.th = pl.th; a.tw_log2 = pl.tw_log2;
@@ -409,16 +454,98 @@ extern "C" int imx_conv2d_igemm_wgrad_bf16(const imx_bf16* x, const imx_bf16* dy
     if (rc) return rc;
 
     switch (pl.BN) {
-        case 256: rc = launch_wgrad<256>(tdy, tx, a, s); break;
-        case 128: rc = launch_wgrad<128>(tdy, tx, a, s); break;
-        default: rc = launch_wgrad<64>(tdy, tx, a, s); break;
+        case 256: return launch_wgrad<256>(tdy, tx, a, s);
+        case 128: return launch_wgrad<128>(tdy, tx, a, s);
+        default: return launch_wgrad<64>(tdy, tx, a, s);
     }
+}
+
+}  // namespace
+
+extern "C" int imx_conv2d_igemm_wgrad_bf16(const imx_bf16* x, const imx_bf16* dy, float* dw,
+                                           void* workspace, int64_t workspace_bytes,
+                                           int N, int H, int W, int Cin, int Cin_p,
+                                           int Cout, int Cout_p, int KH, int KW,
+                                           int stride, int pad, imx_stream_t stream) {
+    IMX_REQUIRE(dw, "conv2d_wgrad: null pointer");
+    cudaStream_t s = (cudaStream_t)stream;
+    if (N == 0) {
+        int rc = check_wgrad_args(N, H, W, Cin, Cin_p, Cout, Cout_p, KH, KW, stride, pad);
+        if (rc) return rc;
+        cudaError_t e = cudaMemsetAsync(dw, 0, (size_t)Cout * Cin * KH * KW * 4, s);
+        return e == cudaSuccess ? IMX_OK : imx::set_error((int)e, "conv2d_wgrad: memset failed");
+    }
+    WgradArgs a;
+    Plan pl;
+    int rc = wgrad_gemm(x, dy, workspace, workspace_bytes, N, H, W, Cin, Cin_p, Cout, Cout_p, KH, KW, stride, pad, s, a, pl);
     if (rc) return rc;
     const long total = (long)Cout * Cin * KH * KW;
     long blocks = (total + 255) / 256;
     if (blocks > 16L * imx::kNumSMs) blocks = 16L * imx::kNumSMs;
     wgrad_reduce_kernel<<<(int)blocks, 256, 0, s>>>(a.ws, dw, Cout, Cin, KH * KW, pl.splits, a.co_r, a.ci_r);
     return imx::check_launch("conv2d_wgrad_reduce");
+}
+
+// Data-parallel variant, step 1: only the split-K GEMM.  plan_out = {splits, co_r, ci_r}.
+extern "C" int imx_conv2d_igemm_wgrad_partials_bf16(const imx_bf16* x, const imx_bf16* dy,
+                                                    void* workspace, int64_t workspace_bytes, int* plan_out,
+                                                    int N, int H, int W, int Cin, int Cin_p,
+                                                    int Cout, int Cout_p, int KH, int KW,
+                                                    int stride, int pad, imx_stream_t stream) {
+    IMX_REQUIRE(plan_out, "conv2d_wgrad_partials: null pointer");
+    IMX_REQUIRE(N > 0, "conv2d_wgrad_partials: empty batch");
+    WgradArgs a;
+    Plan pl;
+    int rc = wgrad_gemm(x, dy, workspace, workspace_bytes, N, H, W, Cin, Cin_p, Cout, Cout_p, KH, KW, stride, pad,
+                        (cudaStream_t)stream, a, pl);
+    if (rc) return rc;
+    plan_out[0] = pl.splits; plan_out[1] = a.co_r; plan_out[2] = a.ci_r;
+    return IMX_OK;
+}
+
+// Step 2: see wgrad_reduce_peers_kernel.  ws_peers: HOST array of `world` device pointers (this
+// rank's own workspace included, any order as long as every rank passes all of them).
+extern "C" int imx_wgrad_reduce_peers_f32(const void* const* ws_peers, int world, float* dw, int co_begin, int co_end,
+                                          int Cout, int Cin, int taps, int splits, int co_r, int ci_r,
+                                          float scale, int accumulate, imx_stream_t stream) {
+    IMX_REQUIRE(ws_peers && dw, "wgrad_reduce_peers: null pointer");
+    IMX_REQUIRE(world >= 1 && world <= kMaxPeers, "wgrad_reduce_peers: world size %d outside [1, %d]", world, kMaxPeers);
+    IMX_REQUIRE(0 <= co_begin && co_begin <= co_end && co_end <= Cout && Cout <= co_r && Cin <= ci_r && taps > 0 && splits > 0,
+                "wgrad_reduce_peers: bad geometry");
+    PeerPtrs pp{};
+    for (int q = 0; q < world; ++q) {
+        IMX_REQUIRE(ws_peers[q], "wgrad_reduce_peers: null peer pointer %d", q);
+        pp.p[q] = reinterpret_cast<const float*>(ws_peers[q]);
+    }
+    const long total = (long)(co_end - co_begin) * Cin * taps;
+    if (total == 0) return IMX_OK;
+    long blocks = (total + 255) / 256;
+    if (blocks > 16L * imx::kNumSMs) blocks = 16L * imx::kNumSMs;
+    wgrad_reduce_peers_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(pp, world, dw, co_begin, co_end, Cin, taps, splits,
+                                                                            co_r, ci_r, scale, accumulate);
+    return imx::check_launch("wgrad_reduce_peers");
+}
+
+// Step 3 (once per backward): see gather_rows_peers_kernel.  arena_peers: HOST array of `world`
+// device pointers to every rank's gradient arena (same layout), descs: DEVICE array of n_tensors
+// {offset, rows, row_elems} records (int64).
+extern "C" int imx_gather_rows_peers_f32(const void* const* arena_peers, int world, int rank, const void* descs,
+                                         int n_tensors, int64_t max_elems, imx_stream_t stream) {
+    IMX_REQUIRE(world >= 1 && world <= kMaxPeers && rank >= 0 && rank < world, "gather_rows_peers: bad world / rank");
+    IMX_REQUIRE(n_tensors >= 0 && n_tensors <= 65535, "gather_rows_peers: bad tensor count");
+    if (n_tensors == 0 || world == 1) return IMX_OK;
+    IMX_REQUIRE(arena_peers && descs && max_elems > 0, "gather_rows_peers: null pointer");
+    PeerPtrs pp{};
+    for (int q = 0; q < world; ++q) {
+        IMX_REQUIRE(arena_peers[q], "gather_rows_peers: null peer pointer %d", q);
+        pp.p[q] = reinterpret_cast<const float*>(arena_peers[q]);
+    }
+    long blocks = (max_elems / world / 4 + 255) / 256;
+    if (blocks > 8L * imx::kNumSMs) blocks = 8L * imx::kNumSMs;
+    if (blocks < 1) blocks = 1;
+    gather_rows_peers_kernel<<<dim3((unsigned)blocks, n_tensors), 256, 0, (cudaStream_t)stream>>>(
+        pp, const_cast<float*>(pp.p[rank]), reinterpret_cast<const GatherDesc*>(descs), world, rank);
+    return imx::check_launch("gather_rows_peers");
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -8,7 +8,7 @@ to a multiple of 8 (padding channels are zero).
 import torch
 import torch.distributed as dist
 
-from . import ops
+from . import grad_sync, ops
 
 ACT_CODES = ops.ACT_CODES
 
@@ -175,7 +175,14 @@ class _Conv2d(torch.autograd.Function):
         dx = dw = db = dres = None
         if ctx.needs_input_grad[0]:
             dx = conv2d_dgrad(dy, weight, ctx.stride, ctx.pad, h, w, x.shape[1], inv_sigma)
-        if ctx.needs_input_grad[1]:
+        sync = grad_sync.lookup(weight) if (grad_sync._ACTIVE and ctx.needs_input_grad[1]) else None
+        if sync is not None and not _small_cin(x.shape[1], kh, kw) and \
+                not (dy.shape[1] == 8 and _small_cout(cout, kh, kw, ctx.stride, ctx.pad)):
+            # data-parallel run: the split-K reduction also sums over the ranks (grad_sync.py); the
+            # finished gradient is installed as weight.grad by PeerGradSync.finish()
+            sync.wgrad(weight, x, dy, cin, cout, kh, kw, ctx.stride, ctx.pad,
+                       sn=(weight.detach(), u, v, inv_sigma) if inv_sigma is not None else None)
+        elif ctx.needs_input_grad[1]:
             dw = _conv2d_wgrad(x, dy, cin, cout, kh, kw, ctx.stride, ctx.pad)   # d/d(w * inv_sigma)
             if inv_sigma is not None:
                 # W_eff = W / sigma, sigma = u^T W v (u, v constants):

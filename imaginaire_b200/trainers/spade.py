@@ -9,6 +9,7 @@ update, and once backward.
 """
 import torch
 
+from .. import grad_sync
 from ..losses import FeatureMatchingLoss, GANLoss, GaussianKLLoss, PerceptualLoss
 from ..utils.model_average import requires_grad
 
@@ -62,6 +63,7 @@ class Trainer:
         requires_grad(self.net_D, False)
         total = self.gen_forward(data)
         total.backward()
+        grad_sync.finish_all()      # no-op unless the peer-memory gradient path is active
         self.opt_G.step()
         if self.cfg.trainer.model_average:
             self.net_G.module.update_average()
@@ -86,6 +88,7 @@ class Trainer:
         requires_grad(self.net_D, True)
         total = self.dis_forward(data)
         total.backward()
+        grad_sync.finish_all()
         self.opt_D.step()
         return total.detach()
 

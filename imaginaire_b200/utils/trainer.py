@@ -64,7 +64,9 @@ def wrap_model_and_optimizer(cfg, net_G, net_D, opt_G, opt_D):
                              cfg.trainer.model_average_start_iteration,
                              getattr(cfg.trainer, 'model_average_remove_sn', True))
     find_unused = getattr(cfg.trainer, 'ddp_find_unused_parameters', None)
-    return _wrap_model(net_G, find_unused), _wrap_model(net_D, find_unused), opt_G, opt_D
+    # the discriminator is applied to real and fake images and its FPSE heads to three pyramid levels
+    # each: up to 6 applications of one filter per backward, each with its own gradient slot
+    return _wrap_model(net_G, find_unused, 1), _wrap_model(net_D, find_unused, 8), opt_G, opt_D
 
 
 class WrappedModel(torch.nn.Module):
@@ -78,7 +80,7 @@ class WrappedModel(torch.nn.Module):
         return self.module(*args, **kwargs)
 
 
-def _wrap_model(model, find_unused=None):
+def _wrap_model(model, find_unused=None, max_uses=1):
     """find_unused: None = the reference's setting (True, utils/trainer.py:203-214) unless the
     environment variable IMX_DDP_FIND_UNUSED=0 says that every trainable parameter takes part in every
     backward (true for the SPADE trainer here, which calls a frozen network through .module, not
@@ -86,6 +88,27 @@ def _wrap_model(model, find_unused=None):
     if get_world_size() > 1:
         if find_unused is None:
             find_unused = os.environ.get('IMX_DDP_FIND_UNUSED', '1') != '0'
+        if os.environ.get('IMX_PEER_GRADS', '1') != '0' and get_world_size() <= 8:
+            # filter gradients are averaged over NVLink peer memory inside the weight-gradient reduction
+            # (grad_sync.py); DDP keeps the small rest.  If symmetric memory cannot be set up on any rank,
+            # every rank falls back to plain DDP.
+            import torch.distributed as dist
+            from .. import grad_sync
+            filters = grad_sync.eligible_filters(model)
+            sync, ok = None, torch.ones(1, device='cuda')
+            if filters:
+                try:
+                    sync = grad_sync.PeerGradSync(
+                        [p for _, p in filters], max_uses=max_uses,
+                        workspace_bytes=int(float(os.environ.get('IMX_PEER_GRADS_WS_GB', '16')) * (1 << 30)))
+                except Exception as e:     # noqa: BLE001 - any failure means "use NCCL for everything"
+                    print('peer-memory gradient path unavailable (%s); using DDP for all parameters' % repr(e)[:200])
+                    ok.zero_()
+                dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+                if float(ok) > 0:
+                    DistributedDataParallel._set_params_and_buffers_to_ignore_for_model(model, [n for n, _ in filters])
+                elif sync is not None:
+                    sync.close()
         ddp = DistributedDataParallel(model, device_ids=[torch.cuda.current_device()],
                                       output_device=torch.cuda.current_device(),
                                       find_unused_parameters=bool(find_unused), broadcast_buffers=False,

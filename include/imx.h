@@ -317,6 +317,33 @@ IMX_API int64_t imx_conv2d_wgrad_workspace_bytes(int N, int H, int W, int Cin, i
                                          int Cout, int Cout_p, int KH, int KW,
                                          int stride, int pad);
 
+/* Data-parallel weight gradient without a separate gradient collective: the
+ * split-K partial sums of every rank live in peer-mapped NVLink memory (e.g.
+ * torch.distributed._symmetric_memory), and the reduction over splits doubles as the reduction
+ * over ranks.
+ *   1. imx_conv2d_igemm_wgrad_partials_bf16: the GEMM of imx_conv2d_igemm_wgrad_bf16 only; fills
+ *      workspace[split][tap][co_r][ci_r] and returns plan_out = {splits, co_r, ci_r} (host ints).
+ *   2. (all ranks reach a barrier), then imx_wgrad_reduce_peers_f32 on every rank: sums the output
+ *      channels [co_begin, co_end) over ALL ranks' workspaces (ws_peers: HOST array of `world`
+ *      device pointers) and splits, writes scale * sum (or adds it, accumulate != 0) into dw
+ *      ([Cout][Cin][KH][KW] fp32, this rank's copy).
+ *   3. once per backward, after another barrier, imx_gather_rows_peers_f32 copies the channel
+ *      ranges owned by the other ranks from their gradient arenas (arena_peers: HOST array of
+ *      device pointers, identical layout on every rank; descs: DEVICE array of int64 triples
+ *      {offset, rows, row_elems}; rank q owns rows [q*rows/world, (q+1)*rows/world)).
+ * Replaces DDP's bucketed NCCL all-reduce for the convolution filters (the reference: apex /
+ * torch DDP in imaginaire/utils/trainer.py:193-216); no counterpart kernel in the reference. */
+IMX_API int imx_conv2d_igemm_wgrad_partials_bf16(const imx_bf16* x, const imx_bf16* dy,
+                                         void* workspace, int64_t workspace_bytes, int* plan_out,
+                                         int N, int H, int W, int Cin, int Cin_p,
+                                         int Cout, int Cout_p, int KH, int KW,
+                                         int stride, int pad, imx_stream_t stream);
+IMX_API int imx_wgrad_reduce_peers_f32(const void* const* ws_peers, int world, float* dw, int co_begin, int co_end,
+                               int Cout, int Cin, int taps, int splits, int co_r, int ci_r,
+                               float scale, int accumulate, imx_stream_t stream);
+IMX_API int imx_gather_rows_peers_f32(const void* const* arena_peers, int world, int rank, const void* descs,
+                              int n_tensors, int64_t max_elems, imx_stream_t stream);
+
 /* The weight gradient again, for callers that are not able to allocate device memory (no
  * counterpart in the reference: its extensions always let torch allocate).  Think of a host
  * that reserves its whole device-memory budget at start-up and forbids cudaMalloc afterwards,

@@ -495,3 +495,46 @@ def test_correlation_rejects_geometry_the_reference_reads_out_of_bounds_for():
         ops.correlation_bwd(x, x, torch.zeros_like(out), 4, 1, 4, 2, 2)   # ... its gradient is not
     with pytest.raises(RuntimeError):
         ops.correlation_fwd(x.cpu(), x.cpu(), 4, 1, 4, 1, 2)              # no CPU fallback
+
+
+# ------------------------------------------------- data-parallel weight gradient over peer memory
+
+@pytest.mark.parametrize('case', [(2, 64, 96, 16, 24, 3, 1, 1, 2), (1, 40, 72, 13, 11, 5, 1, 2, 3), (2, 128, 256, 8, 8, 1, 1, 0, 8)])
+def test_wgrad_peer_reduce_and_gather_equal_the_averaged_gradient(case):
+    """imx_conv2d_igemm_wgrad_partials_bf16 + imx_wgrad_reduce_peers_f32 + imx_gather_rows_peers_f32
+    (grad_sync.py's data-parallel path) with the 'ranks' emulated by separate buffers on one GPU:
+    every rank must end up with the mean of the per-rank gradients of the ordinary entry point."""
+    import ctypes
+    from imaginaire_b200 import ops, _C
+    n, cin, cout, h, w, k, s, p, world = case
+    lib = _C.lib()
+    g = torch.Generator().manual_seed(71)
+    cin_p, cout_p = ops.round_up(cin, 8), ops.round_up(cout, 8)
+    ho, wo_ = (h + 2 * p - k) // s + 1, (w + 2 * p - k) // s + 1
+    xs = [nhwc(torch.randn(n, cin_p, h, w, generator=g)) for _ in range(world)]
+    dys = [nhwc(torch.randn(n, cout_p, ho, wo_, generator=g)) for _ in range(world)]
+    ref = sum(ops.conv2d_wgrad(x, dy, cin, cout, k, k, s, p) for x, dy in zip(xs, dys)) / world
+    nbytes = lib.raw('imx_conv2d_wgrad_workspace_bytes')(n, h, w, cin, cin_p, cout, cout_p, k, k, s, p)
+    wss = [torch.empty(int(nbytes), dtype=torch.uint8, device=DEV) for _ in range(world)]
+    stream = torch.cuda.current_stream().cuda_stream
+    plan = (ctypes.c_int * 3)()
+    for x, dy, ws in zip(xs, dys, wss):
+        lib.call('imx_conv2d_igemm_wgrad_partials_bf16', x.data_ptr(), dy.data_ptr(), ws.data_ptr(), int(nbytes), plan,
+                 n, h, w, cin, cin_p, cout, cout_p, k, k, s, p, stream)
+    numel = cout * cin * k * k
+    slot = 64                                      # the tensor sits at an offset inside each 'arena'
+    arenas = [torch.full((slot + numel,), float('nan'), device=DEV) for _ in range(world)]
+    peers = (ctypes.c_void_p * world)(*[ws.data_ptr() for ws in wss])
+    for r in range(world):
+        lib.call('imx_wgrad_reduce_peers_f32', peers, world, arenas[r].data_ptr() + 4 * slot, r * cout // world,
+                 (r + 1) * cout // world, cout, cin, k * k, int(plan[0]), int(plan[1]), int(plan[2]), 1.0 / world, 0, stream)
+    descs = torch.tensor([[slot, cout, cin * k * k]], dtype=torch.int64).to(DEV)
+    apeers = (ctypes.c_void_p * world)(*[a.data_ptr() for a in arenas])
+    for r in range(world):
+        lib.call('imx_gather_rows_peers_f32', apeers, world, r, descs.data_ptr(), 1, numel, stream)
+    torch.cuda.synchronize()
+    for r in range(world):
+        got = arenas[r][slot:].view(cout, cin, k, k)
+        assert bool(torch.isfinite(got).all())
+        assert H.rel_err(got.cpu(), ref.cpu()) < 2e-6, r
+        assert torch.equal(arenas[r][slot:], arenas[0][slot:])          # every rank holds the same bits
