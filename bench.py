@@ -342,6 +342,9 @@ def run_ours(args):
         ms, ms_e2e = float(t[0]), float(t[1])
 
     # ---- roofline of the dominant kernel family: one more iteration with per-launch CUDA events ----
+    # An un-probed iteration is queued first and NOT waited for, so the device stays backlogged while the probed
+    # one is enqueued: each start event then fires when the previous kernel ends, not when the host got there.
+    one_step(resident)
     probe = ConvProbe()
     probe.install()
     one_step(resident)
