@@ -137,3 +137,38 @@ def test_flow_generator_seeded_build_reproduces_reference_weights():
     for k in sd:
         assert torch.equal(sd[k], ref[k]), k
     net.load_state_dict(ref, strict=True)
+
+
+def test_host_side_planners_and_validation_of_the_later_entry_points():
+    """Entry points that decide or validate on the host can be exercised without a GPU."""
+    import ctypes
+    from imaginaire_b200 import _C
+    lib = _C.lib()
+    # correlation geometry (ref: correlation_cuda.cc:25-35): FlowNetC's cost volume
+    oc, oh, ow = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    assert lib.raw('imx_correlation_output_size')(256, 48, 64, 20, 1, 20, 1, 2, ctypes.byref(oc), ctypes.byref(oh),
+                                                  ctypes.byref(ow)) == 0
+    assert (oc.value, oh.value, ow.value) == (441, 48, 64)
+    # a 3x3 patch with pad == max_displacement would read before the padded plane (the reference does)
+    assert lib.raw('imx_correlation_output_size')(8, 8, 8, 4, 3, 4, 1, 2, ctypes.byref(oc), ctypes.byref(oh),
+                                                  ctypes.byref(ow)) != 0
+    assert 'outside the padded input' in lib.last_error()
+    # split-K planner: a 16x32 layer with 2048 -> 128 channels wants a workspace, a 128x256 layer does not
+    f = lib.raw('imx_conv2d_fprop_workspace_bytes')
+    assert f(8, 16, 32, 2048, 128, 128, 5, 5, 1, 2, 0) == 8 * 16 * 32 * 128 * 4
+    assert f(8, 128, 256, 512, 512, 512, 3, 3, 1, 1, 0) == 0
+    assert f(8, 16, 32, 2048, 128, 128, 5, 5, 1, 2, 32) == 0          # statistics epilogue: never split
+    assert f(8, 16, 32, 2047, 128, 128, 5, 5, 1, 2, 0) < 0            # Cin_p must be a multiple of 8
+    # optimizer: nothing to do is fine, nonsense hyper-parameters are not
+    assert lib.raw('imx_adam_multi_tensor_f32')(None, None, None, None, None, 0, 1e-3, 0.9, 0.999, 1e-8, 0.0, 1, None) == 0
+    one = (ctypes.c_void_p * 1)(8)
+    n = (ctypes.c_int64 * 1)(4)
+    assert lib.raw('imx_adam_multi_tensor_f32')(one, one, one, one, n, 1, 1e-3, 1.5, 0.999, 1e-8, 0.0, 1, None) != 0
+    assert lib.raw('imx_adam_multi_tensor_f32')(one, one, one, one, n, 1, 1e-3, 0.9, 0.999, 1e-8, 0.0, 0, None) != 0
+    # small-channel helpers
+    assert lib.raw('imx_shift_add_taps_f32')(8, None, 8, 1, 8, 8, 80, 5, 5, 1, 3, None) != 0
+    assert "'same' convolution" in lib.last_error()
+    assert lib.raw('imx_shift_add_taps_f32')(8, None, 8, 1, 8, 8, 80, 5, 5, 2, 9, None) != 0
+    # peer-memory gradient path
+    assert lib.raw('imx_wgrad_reduce_peers_f32')(one, 9, 8, 0, 1, 1, 1, 1, 1, 128, 64, 1.0, 0, None) != 0
+    assert lib.raw('imx_gather_rows_peers_f32')(one, 1, 0, None, 0, 1, None) == 0
