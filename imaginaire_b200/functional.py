@@ -110,15 +110,6 @@ def _packed_weight(weight, inner_p, transpose_flip, inv_sigma=None):
     return packed
 
 
-def _act_backward(dy, y, act):
-    """Gradient through an activation that was fused into a conv epilogue (y = act(pre))."""
-    if act == ops.ACT_LRELU:
-        return torch.where(y > 0, dy, dy * 0.2)
-    if act == ops.ACT_RELU:
-        return torch.where(y > 0, dy, torch.zeros_like(dy))
-    return dy
-
-
 def spectral_sigma(weight_orig, u_buf, v_buf, training, n_power_iterations=1, eps=1e-12, out=None):
     """Spectral norm of a filter with torch.nn.utils.spectral_norm's semantics (the reference's
     weight norm, imaginaire/layers/weight_norm.py:85): in training mode run the power iteration
