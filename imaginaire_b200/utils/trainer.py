@@ -100,7 +100,7 @@ def _wrap_model(model, find_unused=None, max_uses=1):
                 try:
                     sync = grad_sync.PeerGradSync(
                         [p for _, p in filters], max_uses=max_uses,
-                        workspace_bytes=int(float(os.environ.get('IMX_PEER_GRADS_WS_GB', '16')) * (1 << 30)))
+                        workspace_bytes=int(float(os.environ.get('IMX_PEER_GRADS_WS_GB', '16' if max_uses == 1 else '8')) * (1 << 30)))
                 except Exception as e:     # noqa: BLE001 - any failure means "use NCCL for everything"
                     print('peer-memory gradient path unavailable (%s); using DDP for all parameters' % repr(e)[:200])
                     ok.zero_()
