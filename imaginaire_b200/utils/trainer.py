@@ -33,11 +33,9 @@ def set_random_seed(seed, by_rank=False):
 def get_optimizer(opt_cfg, params):
     if opt_cfg.type != 'adam':
         raise NotImplementedError('only adam is wired up for the SPADE step')
-    params = list(params)
-    kwargs = dict(lr=opt_cfg.lr, eps=getattr(opt_cfg, 'eps', 1e-8), betas=(opt_cfg.adam_beta1, opt_cfg.adam_beta2))
-    if params and all(p.is_cuda for p in params):
-        return FusedAdam(params, **kwargs)            # the library's multi-tensor kernel
-    return torch.optim.Adam(params, **kwargs)         # CPU-side unit tests of the host logic
+    # the library's multi-tensor kernel; like every other product path it refuses CPU parameters at step()
+    return FusedAdam(list(params), lr=opt_cfg.lr, eps=getattr(opt_cfg, 'eps', 1e-8),
+                     betas=(opt_cfg.adam_beta1, opt_cfg.adam_beta2))
 
 
 def get_model_optimizer_and_scheduler(cfg, seed=0, device='cuda'):
