@@ -79,9 +79,7 @@ class ModelAverage(nn.Module):
         if not sn_layers:
             return
         if not sn_layers[0][1].is_cuda:
-            for t, w, u, v in sn_layers:
-                t.mul_(beta).add_(self.sn_compute_weight(w, u, v), alpha=1.0 - beta)
-            return
+            raise RuntimeError('ModelAverage.update_average runs on CUDA modules only (no CPU fallback)')
         # sigma = u^T W v of every spectral layer in one batched call (no power iteration), then
         # target = beta * target + (1 - beta) * W / sigma.   ref: model_average.py:183-197
         self._batched_sn_update(sn_layers, beta)

@@ -186,6 +186,21 @@ def test_model_average_update_matches_reference_rule():
     cpu = ModelAverage(net, beta=0.9, start_iteration=0, remove_sn=True)
     import copy
     gpu = copy.deepcopy(cpu).to(_dev())
+
+    def reference_update(ma, beta):
+        """The reference's rule, tensor by tensor, in torch on the CPU (model_average.py:87-132, 183-197)."""
+        src, tgt = ma.module.state_dict(), ma.averaged_model.state_dict()
+        with torch.no_grad():
+            for key, t in tgt.items():
+                if key.endswith('weight') and key + '_orig' in src:
+                    w, u, v = src[key + '_orig'], src[key + '_u'], src[key + '_v']
+                    sigma = torch.sum(u * torch.mv(w.reshape(w.shape[0], -1), v))
+                    t.mul_(beta).add_(w / sigma, alpha=1.0 - beta)
+                elif t.is_floating_point():
+                    t.mul_(beta).add_(src[key], alpha=1.0 - beta)
+                else:
+                    t.copy_(src[key])
+
     for step in range(3):
         with torch.no_grad():
             for (_, a), (_, b) in zip(cpu.module.state_dict().items(), gpu.module.state_dict().items()):
@@ -193,7 +208,7 @@ def test_model_average_update_matches_reference_rule():
                     noise = torch.randn_like(a) * 0.1
                     a.add_(noise)
                     b.add_(noise.to(b.device))
-        cpu.update_average()
+        reference_update(cpu, 0.9)
         gpu.update_average()
     sd_c, sd_g = cpu.averaged_model.state_dict(), gpu.averaged_model.state_dict()
     assert list(sd_c.keys()) == list(sd_g.keys())
@@ -204,6 +219,8 @@ def test_model_average_update_matches_reference_rule():
         else:
             assert torch.equal(sd_g[k].cpu(), sd_c[k]), k
     assert int(gpu.num_updates_tracked) == 3
+    with pytest.raises(RuntimeError):
+        cpu.update_average()                                           # no CPU fallback in the product
 
 
 def test_flow_generator_and_warp_vs_reference_golden():
