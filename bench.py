@@ -310,6 +310,13 @@ def run_ours(args):
 
     lib = _C.lib()
     sampler = ClockSampler(local_rank)
+    # Python's cyclic garbage collector pauses each rank at its own moments; with a barrier-coupled step
+    # (SyncBN) every pause of any rank stalls all of them.  Collect once now, then keep the collector off
+    # for the timed regions (a training loop would call gc.collect() every few hundred iterations).
+    import gc
+    gc.collect()
+    if os.environ.get('IMX_BENCH_GC', '0') != '1':
+        gc.disable()
     # ---- timed region 1: inputs resident in HBM ----
     barrier()
     if not args.no_clocks:
