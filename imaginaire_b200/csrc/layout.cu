@@ -132,92 +132,37 @@ __global__ void nhwc_to_nchw_kernel(const __nv_bfloat16* __restrict__ src, float
 // shared memory so that the fp32 filter is read in contiguous runs and the bf16 rows are
 // written as contiguous 256-byte segments.  grid = (ceil(Cp / kPackTile), rows).
 constexpr int kPackTile = 128;
-constexpr int kPackPitch = kPackTile + 1;
 constexpr int kPackMaxTaps = 49;   // up to 7x7; larger kernels take the scalar path
 
-// kTaps > 0: compile-time tap count (1, 9, 16, 25: the index divisions become multiply-shifts);
-// 0: runtime.  A block handles `rows_per_block` consecutive rows r: in the flipped layout the
-// source runs of consecutive r (= ci) are adjacent in memory, so reading them together turns
-// 36-byte runs into rows_per_block x 36-byte runs.
-template <bool kFlip, int kTaps>
+template <bool kFlip>
 __global__ void __launch_bounds__(256)
 pack_weight_tiled_kernel(const float* __restrict__ w, const float* __restrict__ inv_sigma,
-                         __nv_bfloat16* __restrict__ packed, int Cout, int Cin, int taps_rt, int Cp,
-                         int rows, int rows_per_block) {
-    extern __shared__ float tile[];   // [rows_per_block][taps][kPackPitch]: already in output order
-    const int taps = kTaps > 0 ? kTaps : taps_rt;
+                         __nv_bfloat16* __restrict__ packed, int Cout, int Cin, int taps, int Cp) {
+    extern __shared__ float tile[];   // [kPackTile][taps + 1]
     const float s = inv_sigma ? __ldg(inv_sigma) : 1.0f;
-    const int r0 = blockIdx.y * rows_per_block;     // first co (plain) or ci (flip) of this block
-    const int nr = min(rows_per_block, rows - r0);
+    const int r = blockIdx.y;                       // co (plain) or ci (flip)
     const int i0 = blockIdx.x * kPackTile;          // first inner index of the tile: ci (plain) or co (flip)
     const int inner = kFlip ? Cout : Cin;
-    const int n_in = max(0, min(kPackTile, inner - i0));   // valid inner entries (0 for pure padding tiles)
-    const int slab = taps * kPackPitch;
-    // ---- global -> shared: contiguous source runs, 8 independent loads in flight per thread; the
-    //      transposition happens in the shared-memory store (odd pitch: conflict-free)
-    auto put = [&](int rr, int j, int t, float v) { tile[rr * slab + (kFlip ? taps - 1 - t : t) * kPackPitch + j] = v * s; };
+    const int n_in = min(kPackTile, inner - i0);    // valid inner entries (may be <= 0 for pure padding tiles)
+    const int pitch = taps + 1;
     if (!kFlip) {
-        const int run = n_in * taps;                // per row r: w[r][i0 .. i0+n_in)[0..taps)
-        const int total = nr * run;
-        for (int e = threadIdx.x; e < total; e += 8 * 256) {
-            float v[8];
-            int rr[8], qq[8];
-#pragma unroll
-            for (int u = 0; u < 8; ++u) {
-                const int q = e + u * 256;
-                rr[u] = q / run; qq[u] = q - rr[u] * run;
-                v[u] = q < total ? __ldg(w + ((size_t)(r0 + rr[u]) * Cin + i0) * taps + qq[u]) : 0.0f;
-            }
-#pragma unroll
-            for (int u = 0; u < 8; ++u)
-                if (e + u * 256 < total) put(rr[u], qq[u] / taps, qq[u] % taps, v[u]);
-        }
+        // contiguous run w[r][i0 .. i0+n_in)[0..taps)
+        const float* src = w + ((size_t)r * Cin + i0) * taps;
+        for (int e = threadIdx.x; e < n_in * taps; e += 256) tile[(e / taps) * pitch + e % taps] = __ldg(src + e) * s;
     } else {
-        const int run = nr * taps;                  // per co j: w[i0 + j][r0 .. r0+nr)[0..taps)
-        const int total = n_in * run;
-        for (int e = threadIdx.x; e < total; e += 8 * 256) {
-            float v[8];
-            int jj[8], qq[8];
-#pragma unroll
-            for (int u = 0; u < 8; ++u) {
-                const int q = e + u * 256;
-                jj[u] = q / run; qq[u] = q - jj[u] * run;
-                v[u] = q < total ? __ldg(w + ((size_t)(i0 + jj[u]) * Cin + r0) * taps + qq[u]) : 0.0f;
-            }
-#pragma unroll
-            for (int u = 0; u < 8; ++u)
-                if (e + u * 256 < total) put(qq[u] / taps, jj[u], qq[u] % taps, v[u]);
+        // for each co in the tile a run of `taps` floats at w[co][r][:]
+        for (int e = threadIdx.x; e < n_in * taps; e += 256) {
+            const int j = e / taps, t = e - j * taps;
+            tile[j * pitch + t] = __ldg(w + ((size_t)(i0 + j) * Cin + r) * taps + t) * s;
         }
     }
     __syncthreads();
-    // ---- shared -> global: two consecutive channels per thread (4-byte stores, 128 B per warp)
-    const int n_out = min(kPackTile, Cp - i0);      // multiple of 8
-    const int half = n_out >> 1;
-    const int per_row = taps * half;
-    for (int e = threadIdx.x; e < nr * per_row; e += 256) {
-        const int rr = e / per_row, q = e - rr * per_row;
-        const int t = q / half, j = (q - t * half) * 2;
-        const float* src = tile + rr * slab + t * kPackPitch + j;
-        const float a = j < n_in ? src[0] : 0.0f, b = j + 1 < n_in ? src[1] : 0.0f;
-        *reinterpret_cast<__nv_bfloat162*>(packed + ((size_t)(r0 + rr) * taps + t) * Cp + i0 + j) = __floats2bfloat162_rn(a, b);
+    const int n_out = min(kPackTile, Cp - i0);
+    for (int e = threadIdx.x; e < taps * n_out; e += 256) {
+        const int t = e / n_out, j = e - t * n_out;
+        const float v = j < n_in ? tile[j * pitch + (kFlip ? taps - 1 - t : t)] : 0.0f;
+        packed[((size_t)r * taps + t) * Cp + i0 + j] = __float2bfloat16_rn(v);
     }
-}
-
-template <bool kFlip>
-int launch_pack_tiled(const float* w, const float* inv_sigma, __nv_bfloat16* packed, int Cout, int Cin, int taps, int Cp,
-                      int rows, cudaStream_t st) {
-    int rpb = (44 * 1024) / (kPackPitch * taps * 4);           // rows per block within 44 KB of shared memory
-    rpb = rpb < 1 ? 1 : (rpb > 8 ? 8 : rpb);
-    const size_t smem = (size_t)rpb * kPackPitch * taps * sizeof(float);
-    dim3 grid((Cp + kPackTile - 1) / kPackTile, (rows + rpb - 1) / rpb);
-    switch (taps) {
-        case 1: pack_weight_tiled_kernel<kFlip, 1><<<grid, 256, smem, st>>>(w, inv_sigma, packed, Cout, Cin, taps, Cp, rows, rpb); break;
-        case 9: pack_weight_tiled_kernel<kFlip, 9><<<grid, 256, smem, st>>>(w, inv_sigma, packed, Cout, Cin, taps, Cp, rows, rpb); break;
-        case 16: pack_weight_tiled_kernel<kFlip, 16><<<grid, 256, smem, st>>>(w, inv_sigma, packed, Cout, Cin, taps, Cp, rows, rpb); break;
-        case 25: pack_weight_tiled_kernel<kFlip, 25><<<grid, 256, smem, st>>>(w, inv_sigma, packed, Cout, Cin, taps, Cp, rows, rpb); break;
-        default: pack_weight_tiled_kernel<kFlip, 0><<<grid, 256, smem, st>>>(w, inv_sigma, packed, Cout, Cin, taps, Cp, rows, rpb); break;
-    }
-    return imx::check_launch("pack_conv_weight");
 }
 
 // Scalar fallback for very large kernels.
@@ -350,9 +295,15 @@ extern "C" int imx_pack_conv_weight_bf16(const float* w, const float* inv_sigma,
     const int taps = KH * KW;
     const int rows = transpose_flip ? Cin : Cout;
     if (taps <= kPackMaxTaps && rows <= 65535) {
-        __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(packed);
-        return transpose_flip ? launch_pack_tiled<true>(w, inv_sigma, out, Cout, Cin, taps, Cin_p, rows, (cudaStream_t)stream)
-                              : launch_pack_tiled<false>(w, inv_sigma, out, Cout, Cin, taps, Cin_p, rows, (cudaStream_t)stream);
+        dim3 grid((Cin_p + kPackTile - 1) / kPackTile, rows);
+        const size_t smem = (size_t)kPackTile * (taps + 1) * sizeof(float);
+        if (transpose_flip)
+            pack_weight_tiled_kernel<true><<<grid, 256, smem, (cudaStream_t)stream>>>(
+                w, inv_sigma, reinterpret_cast<__nv_bfloat16*>(packed), Cout, Cin, taps, Cin_p);
+        else
+            pack_weight_tiled_kernel<false><<<grid, 256, smem, (cudaStream_t)stream>>>(
+                w, inv_sigma, reinterpret_cast<__nv_bfloat16*>(packed), Cout, Cin, taps, Cin_p);
+        return imx::check_launch("pack_conv_weight");
     }
     const long total = (long)rows * taps * Cin_p;
     pack_weight_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(
