@@ -257,6 +257,130 @@ extern "C" int imx_upsample2x_bwd_nhwc_bf16(const imx_bf16* src, imx_bf16* dst,
     return imx::check_launch("upsample2x_bwd");
 }
 
+// ---------------------------------------------------------------------------------------------
+// Bilinear x2 upsampling (align_corners = False) fused with the lateral addition of a feature
+// pyramid: out = up2x(src) + lat.  ref: FPSE discriminator top-down path,
+// imaginaire/discriminators/fpse.py:119-122 (nn.Upsample(scale_factor=2, mode='bilinear') + lateral).
+// For scale 2 the taps are fixed: an even output row 2k reads rows k-1, k with weights .25, .75
+// (row 0 reads row 0 only), an odd row 2k+1 reads rows k, k+1 with weights .75, .25 (the last
+// row reads row h-1 only); columns alike.
+namespace {
+
+__device__ __forceinline__ void up2x_taps(int o, int n, int& i0, int& i1, float& w0, float& w1) {
+    const int k = o >> 1;
+    if (o & 1) { i0 = k; i1 = min(k + 1, n - 1); w0 = 0.75f; w1 = 0.25f; }
+    else { i0 = max(k - 1, 0); i1 = k; w0 = 0.25f; w1 = 0.75f; }
+}
+
+__device__ __forceinline__ void unpack8u(const uint4& v, float (&f)[8]) {
+    f[0] = imx::bf16_lo(v.x); f[1] = imx::bf16_hi(v.x); f[2] = imx::bf16_lo(v.y); f[3] = imx::bf16_hi(v.y);
+    f[4] = imx::bf16_lo(v.z); f[5] = imx::bf16_hi(v.z); f[6] = imx::bf16_lo(v.w); f[7] = imx::bf16_hi(v.w);
+}
+
+__global__ void bilinear_up2x_add_kernel(const uint4* __restrict__ src, const uint4* __restrict__ lat,
+                                         uint4* __restrict__ out, int N, int h, int w, int cg) {
+    const int H = 2 * h, W = 2 * w;
+    const long total = (long)N * H * W * cg;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int c8 = (int)(i % cg);
+        long p = i / cg;
+        const int ox = (int)(p % W); p /= W;
+        const int oy = (int)(p % H);
+        const int n = (int)(p / H);
+        int y0, y1, x0, x1;
+        float wy0, wy1, wx0, wx1;
+        up2x_taps(oy, h, y0, y1, wy0, wy1);
+        up2x_taps(ox, w, x0, x1, wx0, wx1);
+        const uint4* b = src + (size_t)n * h * w * cg + c8;
+        float a[8], t[8], acc[8];
+        unpack8u(__ldg(b + ((size_t)y0 * w + x0) * cg), a);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] = wy0 * wx0 * a[k];
+        unpack8u(__ldg(b + ((size_t)y0 * w + x1) * cg), t);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] = fmaf(wy0 * wx1, t[k], acc[k]);
+        unpack8u(__ldg(b + ((size_t)y1 * w + x0) * cg), t);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] = fmaf(wy1 * wx0, t[k], acc[k]);
+        unpack8u(__ldg(b + ((size_t)y1 * w + x1) * cg), t);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] = fmaf(wy1 * wx1, t[k], acc[k]);
+        if (lat) {
+            unpack8u(imx::ldg_stream(lat + i), t);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc[k] += t[k];
+        }
+        imx::stg_stream(out + i, make_uint4(imx::pack_bf16(acc[0], acc[1]), imx::pack_bf16(acc[2], acc[3]),
+                                            imx::pack_bf16(acc[4], acc[5]), imx::pack_bf16(acc[6], acc[7])));
+    }
+}
+
+// Gradient with respect to src: source pixel k receives from output rows 2k-1 (.25), 2k (.75, or 1
+// for k = 0), 2k+1 (.75, or 1 for k = h-1), 2k+2 (.25); columns alike.
+__device__ __forceinline__ void up2x_bwd_taps(int k, int n, int (&o)[4], float (&wt)[4]) {
+    o[0] = 2 * k - 1; wt[0] = k >= 1 ? 0.25f : 0.0f;
+    o[1] = 2 * k;     wt[1] = k == 0 ? 1.0f : 0.75f;
+    o[2] = 2 * k + 1; wt[2] = k == n - 1 ? 1.0f : 0.75f;
+    o[3] = 2 * k + 2; wt[3] = k <= n - 2 ? 0.25f : 0.0f;
+}
+
+__global__ void bilinear_up2x_bwd_kernel(const uint4* __restrict__ dout, uint4* __restrict__ dsrc, int N, int h, int w, int cg) {
+    const int H = 2 * h, W = 2 * w;
+    const long total = (long)N * h * w * cg;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int c8 = (int)(i % cg);
+        long p = i / cg;
+        const int x = (int)(p % w); p /= w;
+        const int y = (int)(p % h);
+        const int n = (int)(p / h);
+        int oy[4], ox[4];
+        float wy[4], wx[4];
+        up2x_bwd_taps(y, h, oy, wy);
+        up2x_bwd_taps(x, w, ox, wx);
+        const uint4* b = dout + (size_t)n * H * W * cg + c8;
+        float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+            if (wy[a] == 0.0f) continue;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                if (wx[c] == 0.0f) continue;
+                float t[8];
+                unpack8u(__ldg(b + ((size_t)oy[a] * W + ox[c]) * cg), t);
+                const float wgt = wy[a] * wx[c];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) acc[k] = fmaf(wgt, t[k], acc[k]);
+            }
+        }
+        imx::stg_stream(dsrc + i, make_uint4(imx::pack_bf16(acc[0], acc[1]), imx::pack_bf16(acc[2], acc[3]),
+                                             imx::pack_bf16(acc[4], acc[5]), imx::pack_bf16(acc[6], acc[7])));
+    }
+}
+
+}  // namespace
+
+extern "C" int imx_bilinear_up2x_add_nhwc_bf16(const imx_bf16* src, const imx_bf16* lateral, imx_bf16* out,
+                                               int N, int h, int w, int C, imx_stream_t stream) {
+    IMX_REQUIRE(src && out, "bilinear_up2x_add: null pointer");
+    IMX_REQUIRE(N >= 0 && h >= 0 && w >= 0 && C >= 0 && C % 8 == 0, "bilinear_up2x_add: bad size (C %% 8 must be 0)");
+    const long total = (long)N * 4 * h * w * (C / 8);
+    if (total == 0) return IMX_OK;
+    bilinear_up2x_add_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const uint4*>(src), reinterpret_cast<const uint4*>(lateral), reinterpret_cast<uint4*>(out), N, h, w, C / 8);
+    return imx::check_launch("bilinear_up2x_add");
+}
+
+extern "C" int imx_bilinear_up2x_bwd_nhwc_bf16(const imx_bf16* grad_out, imx_bf16* grad_src,
+                                               int N, int h, int w, int C, imx_stream_t stream) {
+    IMX_REQUIRE(grad_out && grad_src, "bilinear_up2x_bwd: null pointer");
+    IMX_REQUIRE(N >= 0 && h >= 0 && w >= 0 && C >= 0 && C % 8 == 0, "bilinear_up2x_bwd: bad size (C %% 8 must be 0)");
+    const long total = (long)N * h * w * (C / 8);
+    if (total == 0) return IMX_OK;
+    bilinear_up2x_bwd_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const uint4*>(grad_out), reinterpret_cast<uint4*>(grad_src), N, h, w, C / 8);
+    return imx::check_launch("bilinear_up2x_bwd");
+}
+
 extern "C" int imx_nchw_f32_to_nhwc_bf16(const float* src, imx_bf16* dst, int N, int C, int H, int W,
                                          int Cp, imx_stream_t stream) {
     IMX_REQUIRE(src && dst, "nchw_to_nhwc: null pointer");

@@ -51,9 +51,11 @@ class FPSEDiscriminator(nn.Module):
         feat14 = self.enc4(feat13)
         feat15 = self.enc5(feat14)
         feat25 = self.lat5(feat15)
-        feat24 = self.upsample2x(feat25) + self.lat4(feat14)
-        feat23 = self.upsample2x(feat24) + self.lat3(feat13)
-        feat22 = self.upsample2x(feat23) + self.lat2(feat12)
+        # upsample2x (bilinear, align_corners=False) + lateral in one kernel; self.upsample2x stays as
+        # the reference's attribute
+        feat24 = NF.bilinear_up2x_add(feat25, self.lat4(feat14))
+        feat23 = NF.bilinear_up2x_add(feat24, self.lat3(feat13))
+        feat22 = NF.bilinear_up2x_add(feat23, self.lat2(feat12))
         feats = (self.final2(feat22), self.final3(feat23), self.final4(feat24))
         # The reference embeds the full-resolution label map (1x1 conv to 2F channels) and then
         # average-pools the embedding 4 times.  A 1x1 convolution commutes with average pooling,

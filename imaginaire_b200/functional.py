@@ -79,6 +79,24 @@ class _Upsample2x(torch.autograd.Function):
         return ops.upsample2x_bwd(_as_nhwc(g))
 
 
+class _BilinearUp2xAdd(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, src, lateral):
+        ctx.has_lat = lateral is not None
+        return ops.bilinear_up2x_add(src, lateral)
+
+    @staticmethod
+    def backward(ctx, g):
+        g = _as_nhwc(g)
+        return (ops.bilinear_up2x_bwd(g) if ctx.needs_input_grad[0] else None,
+                g if ctx.has_lat and ctx.needs_input_grad[1] else None)
+
+
+def bilinear_up2x_add(src, lateral=None):
+    """up2x_bilinear(src) + lateral on NHWC bf16 tensors (the FPSE discriminator's top-down step)."""
+    return _BilinearUp2xAdd.apply(to_nhwc(src), None if lateral is None else to_nhwc(lateral))
+
+
 def upsample2x(x):
     y = _Upsample2x.apply(x)
     st = getattr(x, '_imx_stats', None)

@@ -138,6 +138,27 @@ def upsample2x_bwd(g):
     return out
 
 
+def bilinear_up2x_add(src, lateral=None):
+    """bilinear x2 upsampling (align_corners=False) of NHWC bf16 `src`, plus `lateral` if given."""
+    _req_cuda(src); _req_nhwc(src, 'src')
+    n, c, h, w = src.shape
+    if lateral is not None:
+        _req_nhwc(lateral, 'lateral')
+        if tuple(lateral.shape) != (n, c, 2 * h, 2 * w):
+            raise RuntimeError('lateral shape %s does not match the upsampled source %s' % (tuple(lateral.shape), (n, c, 2 * h, 2 * w)))
+    out = empty_nhwc(n, c, 2 * h, 2 * w, src.device)
+    _C.lib().call('imx_bilinear_up2x_add_nhwc_bf16', _ptr(src), _ptr(lateral), _ptr(out), n, h, w, c, _stream())
+    return out
+
+
+def bilinear_up2x_bwd(grad_out):
+    _req_cuda(grad_out); _req_nhwc(grad_out, 'grad_out')
+    n, c, hh, ww = grad_out.shape
+    g = empty_nhwc(n, c, hh // 2, ww // 2, grad_out.device)
+    _C.lib().call('imx_bilinear_up2x_bwd_nhwc_bf16', _ptr(grad_out), _ptr(g), n, hh // 2, ww // 2, c, _stream())
+    return g
+
+
 def nchw_f32_to_nhwc_bf16(x, cp=None):
     _req_cuda(x)
     x = x.float().contiguous()

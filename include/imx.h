@@ -98,6 +98,17 @@ IMX_API int imx_upsample2x_nhwc_bf16(const imx_bf16* src, imx_bf16* dst,
 IMX_API int imx_upsample2x_bwd_nhwc_bf16(const imx_bf16* src, imx_bf16* dst,
                                  int N, int H, int W, int C, imx_stream_t stream);
 
+/* out = bilinear_upsample_x2(src) (+ lateral), align_corners = False, NHWC bf16: src N x h x w x C,
+ * lateral (may be NULL) and out N x 2h x 2w x C.  The top-down step of a feature pyramid in one
+ * pass (fp32 interpolation and addition, one rounding).  imx_bilinear_up2x_bwd_nhwc_bf16 is the
+ * gradient with respect to src (the gradient with respect to lateral is grad_out itself).
+ * ref: FPSE discriminator, imaginaire/discriminators/fpse.py:119-122
+ *      (nn.Upsample(scale_factor=2, mode='bilinear') followed by the lateral addition) */
+IMX_API int imx_bilinear_up2x_add_nhwc_bf16(const imx_bf16* src, const imx_bf16* lateral, imx_bf16* out,
+                                    int N, int h, int w, int C, imx_stream_t stream);
+IMX_API int imx_bilinear_up2x_bwd_nhwc_bf16(const imx_bf16* grad_out, imx_bf16* grad_src,
+                                    int N, int h, int w, int C, imx_stream_t stream);
+
 /* NCHW fp32 -> NHWC bf16 (channels zero-padded to Cp) and back (first C of Cp). */
 IMX_API int imx_nchw_f32_to_nhwc_bf16(const float* src, imx_bf16* dst, int N, int C, int H, int W,
                               int Cp, imx_stream_t stream);

@@ -442,6 +442,29 @@ def test_fused_adam_matches_torch_adam(betas, wd):
         FusedAdam([cpu_p]).step()       # no CPU fallback
 
 
+@pytest.mark.parametrize('shape', [(2, 16, 8, 12), (1, 8, 1, 3), (3, 64, 5, 1), (2, 256, 16, 32)])
+def test_bilinear_up2x_add_vs_torch(shape):
+    """FPSE top-down step: bilinear x2 (align_corners=False) + lateral, forward and both gradients,
+    against F.interpolate in fp32 on the same bf16-rounded inputs."""
+    from imaginaire_b200 import functional as NF
+    n, c, h, w = shape
+    g = torch.Generator().manual_seed(81)
+    src = torch.randn(n, c, h, w, generator=g).bfloat16().float()
+    lat = torch.randn(n, c, 2 * h, 2 * w, generator=g).bfloat16().float()
+    go = torch.randn(n, c, 2 * h, 2 * w, generator=g).bfloat16().float()
+    sd, ld = nhwc(src).requires_grad_(True), nhwc(lat).requires_grad_(True)
+    out = NF.bilinear_up2x_add(sd, ld)
+    sr, lr = src.clone().requires_grad_(True), lat.clone().requires_grad_(True)
+    ref = F.interpolate(sr, scale_factor=2, mode='bilinear', align_corners=False) + lr
+    assert H.rel_err(out.float().cpu(), ref.detach()) < 4e-3
+    out.backward(nhwc(go))
+    ref.backward(go)
+    assert H.rel_err(sd.grad.float().cpu(), sr.grad) < 4e-3
+    assert torch.equal(ld.grad.float().cpu(), go)
+    only_up = NF.bilinear_up2x_add(nhwc(src))
+    assert H.rel_err(only_up.float().cpu(), F.interpolate(src, scale_factor=2, mode='bilinear', align_corners=False)) < 4e-3
+
+
 # ------------------------------------------------- FlowNet2 operators
 
 @pytest.mark.parametrize('shape', [(2, 3, 17, 23), (1, 2, 64, 96), (3, 64, 5, 7), (1, 1, 1, 1)])
