@@ -40,11 +40,12 @@ class Discriminator(nn.Module):
         input_x = torch.cat((input_label, input_image), 1)
         outputs = list(self.fpse_discriminator(input_image, input_label))
         features = []
-        for net in self.discriminators:
+        for i, net in enumerate(self.discriminators):
             out, feats = net(input_x)
             outputs.append(out)
             features.append(feats)
-            input_x = nn.functional.interpolate(input_x, scale_factor=0.5, mode='bilinear', align_corners=True)
+            if i + 1 < len(self.discriminators):   # the reference also resizes after the last one; nothing reads it
+                input_x = nn.functional.interpolate(input_x, scale_factor=0.5, mode='bilinear', align_corners=True)
         return outputs, features
 
     def forward(self, data, net_G_output):
