@@ -79,16 +79,15 @@ struct ConvArgs {
     const float* rstd;
     const float* nw;
     const float* nb;
-    int C, per_instance, act, up2x;
+    int C, per_instance, up2x;
+    float act_slope;             // activation as its negative-side slope: LeakyReLU 0.2, ReLU 0, none 1
 };
 
 // named barrier of the four epilogue warps
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
-__device__ __forceinline__ float act_apply(float v, int act) {
-    if (act == 1) return v > 0.0f ? v : 0.2f * v;
-    if (act == 2) return fmaxf(v, 0.0f);
-    return v;
+__device__ __forceinline__ float act_apply(float v, float slope) {
+    return fmaxf(v, 0.0f) + slope * fminf(v, 0.0f);   // branch-free for all three activations
 }
 
 // kMode 0: plain conv epilogue.   kMode 1: SPADE gamma/beta projection + modulation.
@@ -484,7 +483,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                             const float xh = fmaf(xv - k4.x, k4.y, k4.z);
                             const float gam1 = __uint_as_float(vg[c]) + k4.w;
                             const float bet = __uint_as_float(vb[c]) + cbb[g * 64 + h * 32 + c];
-                            y2[e] = act_apply(fmaf(xh, gam1, bet), p.act);
+                            y2[e] = act_apply(fmaf(xh, gam1, bet), p.act_slope);
                         }
                         o[j >> 1] = imx::pack_bf16(y2[0], y2[1]);
                     }
@@ -778,7 +777,8 @@ extern "C" int imx_spade_gb_conv_modulate_bf16(const imx_bf16* hidden, const imx
     if (rc) return rc;
     a.out = y; a.bias = bias_gamma; a.bias_beta = bias_beta;
     a.x = x; a.mean = mean; a.rstd = rstd; a.nw = w; a.nb = b;
-    a.C = C; a.per_instance = stats_per_instance; a.act = act; a.up2x = up2x;
+    a.C = C; a.per_instance = stats_per_instance; a.up2x = up2x;
+    a.act_slope = act == 1 ? 0.2f : (act == 2 ? 0.0f : 1.0f);
     cudaStream_t s = (cudaStream_t)stream;
     return BN == 256 ? launch<256, 1>(ta, tb, a, s) : launch<128, 1>(ta, tb, a, s);
 }

@@ -37,14 +37,21 @@ inline RowMap make_rowmap(int C) {
 }
 
 // Split `np` pixels of one group over blocks.  `per_sm` CTAs per SM in total: the reducing
-// kernels end with 2C atomics per CTA onto the same few L2 slices, so they want few, long-lived
-// CTAs (2 per SM, 8 loads in flight per thread); the pure streaming kernels take more.
+// kernels end with 2C atomics per CTA onto the same addresses, and atomics on one address
+// serialise in L2 (measured ~20 ns each: a 592-CTA grid spends ~12 us in that chain), so they
+// want few, long-lived CTAs with many loads in flight per thread; the pure streaming kernels
+// take more.  (Adding the CTAs' sums through distributed shared memory in clusters of 8 before
+// the atomics was tried and is slower: 37 clusters of 2-CTA/SM kernels do not fit one wave.)
 inline int pick_blocks(long np, int rows, int groups, int per_sm = 2) {
     long iters = (np + rows - 1) / rows;
     long want = ((long)per_sm * imx::kNumSMs + groups - 1) / groups;
     long b = iters < want ? iters : want;
     return (int)(b < 1 ? 1 : b);
 }
+
+// Statistics kernel: 3 CTAs per SM when the tensor is large (the atomic tail is then small beside
+// the streaming time), 2 otherwise.
+inline int stats_ctas_per_sm(long elems) { return elems * 2 >= (64L << 20) ? 3 : 2; }
 
 __device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
     f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
@@ -62,29 +69,35 @@ __device__ __forceinline__ void load8f(const float* p, float (&f)[8]) {
 // ------------------------------------------------------------------ statistics
 
 // grid = (blocks, groups); group g covers pixels [g*HWg, (g+1)*HWg).
+// __launch_bounds__(kThreads, 4): with no minimum-CTA hint ptxas minimises registers (44) by
+// recycling the destination registers of the eight loads, which leaves ~3 of them in flight; with
+// the hint it keeps all eight in distinct registers (64) and the kernel goes from 0.57 to 0.82 of
+// the HBM peak.
 template <bool kWithSq>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 4)
 stats_kernel(const uint4* __restrict__ x, float* __restrict__ sum, float* __restrict__ sumsq,
              long HWg, int C, int cg, int tpr, int rows, int row_stride_c8) {
-    __shared__ float red[kThreads][9];
+    constexpr int NV = kWithSq ? 16 : 8;
+    __shared__ float red[kThreads][NV + 1];
     const int tid = threadIdx.x;
     const int ci = tid % tpr, r = tid / tpr;
     const bool active = r < rows;
     const int g = blockIdx.y;
-    // this block's pixel range inside the group
-    const long per = (HWg + gridDim.x - 1) / gridDim.x;
-    const long p0 = (long)blockIdx.x * per;
-    const long p1 = p0 + per < HWg ? p0 + per : HWg;
+    // block-interleaved pixel rows inside the group (see modulate_kernel)
+    const long p0 = (long)blockIdx.x * rows;
+    const long p1 = HWg;
+    const long pstep = (long)rows * gridDim.x;
     const uint4* base = x + (size_t)g * HWg * row_stride_c8;
-    for (int c8 = ci; c8 < cg; c8 += tpr) {
+    for (int c8b = 0; c8b < cg; c8b += tpr) {   // block-uniform trip count (barriers inside)
+        const int c8 = c8b + ci;
         float s[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        if (active) {
+        if (active && c8 < cg) {
             long p = p0 + r;
             // 8 independent 128-bit loads in flight per thread
-            for (; p + 7L * rows < p1; p += 8L * rows) {
+            for (; p + 7L * pstep < p1; p += 8L * pstep) {
                 uint4 v[8];
 #pragma unroll
-                for (int u = 0; u < 8; ++u) v[u] = imx::ldg_stream(base + (size_t)(p + (long)u * rows) * row_stride_c8 + c8);
+                for (int u = 0; u < 8; ++u) v[u] = imx::ldg_stream(base + (size_t)(p + (long)u * pstep) * row_stride_c8 + c8);
 #pragma unroll
                 for (int u = 0; u < 8; ++u) {
                     float f[8];
@@ -93,30 +106,37 @@ stats_kernel(const uint4* __restrict__ x, float* __restrict__ sum, float* __rest
                     for (int k = 0; k < 8; ++k) { s[k] += f[k]; if (kWithSq) q[k] = fmaf(f[k], f[k], q[k]); }
                 }
             }
-            for (; p < p1; p += rows) {
+            for (; p < p1; p += pstep) {
                 float f[8];
                 unpack8(imx::ldg_stream(base + (size_t)p * row_stride_c8 + c8), f);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) { s[k] += f[k]; if (kWithSq) q[k] = fmaf(f[k], f[k], q[k]); }
             }
         }
-        // reduce the `rows` partial sums that share this channel group
+        // reduce the `rows` partial sums that share this channel group, then one vector atomic per CTA and channel group
+        __syncthreads();
 #pragma unroll
-        for (int pass = 0; pass < (kWithSq ? 2 : 1); ++pass) {
-            __syncthreads();
+        for (int k = 0; k < 8; ++k) {
+            red[tid][k] = s[k];
+            if (kWithSq) red[tid][8 + k] = q[k];
+        }
+        __syncthreads();
+        float acc[NV] = {};
+        if (r == 0) {
 #pragma unroll
-            for (int k = 0; k < 8; ++k) red[tid][k] = pass == 0 ? s[k] : q[k];
-            __syncthreads();
-            if (r == 0) {
-                float acc[8];
+            for (int k = 0; k < NV; ++k) acc[k] = red[tid][k];
+            for (int rr = 1; rr < rows; ++rr)
 #pragma unroll
-                for (int k = 0; k < 8; ++k) acc[k] = red[tid][k];
-                for (int rr = 1; rr < rows; ++rr)
-#pragma unroll
-                    for (int k = 0; k < 8; ++k) acc[k] += red[tid + rr * tpr][k];
-                float* dst = (pass == 0 ? sum : sumsq) + (size_t)g * C + c8 * 8;
-                imx::red_add_v4(dst, acc[0], acc[1], acc[2], acc[3]);
-                imx::red_add_v4(dst + 4, acc[4], acc[5], acc[6], acc[7]);
+                for (int k = 0; k < NV; ++k) acc[k] += red[tid + rr * tpr][k];
+        }
+        if (r == 0 && c8 < cg) {
+            float* dst = sum + (size_t)g * C + c8 * 8;
+            imx::red_add_v4(dst, acc[0], acc[1], acc[2], acc[3]);
+            imx::red_add_v4(dst + 4, acc[4], acc[5], acc[6], acc[7]);
+            if (kWithSq) {
+                float* dq = sumsq + (size_t)g * C + c8 * 8;
+                imx::red_add_v4(dq, acc[NV - 8], acc[NV - 7], acc[NV - 6], acc[NV - 5]);
+                imx::red_add_v4(dq + 4, acc[NV - 4], acc[NV - 3], acc[NV - 2], acc[NV - 1]);
             }
         }
     }
@@ -124,19 +144,20 @@ stats_kernel(const uint4* __restrict__ x, float* __restrict__ sum, float* __rest
 
 // dx = dy * act'(y) for an activation that was fused into a conv epilogue (y = act(pre)), plus
 // the per-channel sum of dx (the conv's bias gradient) in the same pass.
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 4)
 act_bwd_sum_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y, uint4* __restrict__ dx,
                    float* __restrict__ sum, long NP, int cg, int tpr, int rows, float slope) {
     __shared__ float red[kThreads][9];
     const int tid = threadIdx.x;
     const int ci = tid % tpr, r = tid / tpr;
     const bool active = r < rows;
-    const long per = (NP + gridDim.x - 1) / gridDim.x;
-    const long p0 = (long)blockIdx.x * per;
-    const long p1 = p0 + per < NP ? p0 + per : NP;
-    for (int c8 = ci; c8 < cg; c8 += tpr) {
+    const long p0 = (long)blockIdx.x * rows;   // block-interleaved pixel rows (see modulate_kernel)
+    const long p1 = NP;
+    const long pstep = (long)rows * gridDim.x;
+    for (int c8b = 0; c8b < cg; c8b += tpr) {   // block-uniform trip count (barriers inside)
+        const int c8 = c8b + ci;
         float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        if (active) {
+        if (active && c8 < cg) {
             auto one = [&](const uint4 gv, const uint4 yv, long p) {
                 float g[8], yy[8];
                 unpack8(gv, g);
@@ -153,17 +174,17 @@ act_bwd_sum_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y, ui
                 for (int k = 0; k < 8; ++k) s[k] += g[k];
             };
             long p = p0 + r;
-            for (; p + 3L * rows < p1; p += 4L * rows) {
+            for (; p + 3L * pstep < p1; p += 4L * pstep) {
                 uint4 gv[4], yv[4];
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
-                    gv[u] = imx::ldg_stream(dy + (size_t)(p + (long)u * rows) * cg + c8);
-                    yv[u] = imx::ldg_stream(y + (size_t)(p + (long)u * rows) * cg + c8);
+                    gv[u] = imx::ldg_stream(dy + (size_t)(p + (long)u * pstep) * cg + c8);
+                    yv[u] = imx::ldg_stream(y + (size_t)(p + (long)u * pstep) * cg + c8);
                 }
 #pragma unroll
-                for (int u = 0; u < 4; ++u) one(gv[u], yv[u], p + (long)u * rows);
+                for (int u = 0; u < 4; ++u) one(gv[u], yv[u], p + (long)u * pstep);
             }
-            for (; p < p1; p += rows)
+            for (; p < p1; p += pstep)
                 one(imx::ldg_stream(dy + (size_t)p * cg + c8), imx::ldg_stream(y + (size_t)p * cg + c8), p);
         }
         if (sum) {
@@ -171,13 +192,15 @@ act_bwd_sum_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y, ui
 #pragma unroll
             for (int k = 0; k < 8; ++k) red[tid][k] = s[k];
             __syncthreads();
+            float acc[8] = {};
             if (r == 0) {
-                float acc[8];
 #pragma unroll
                 for (int k = 0; k < 8; ++k) acc[k] = red[tid][k];
                 for (int rr = 1; rr < rows; ++rr)
 #pragma unroll
                     for (int k = 0; k < 8; ++k) acc[k] += red[tid + rr * tpr][k];
+            }
+            if (r == 0 && c8 < cg) {
                 float* dst = sum + c8 * 8;
                 imx::red_add_v4(dst, acc[0], acc[1], acc[2], acc[3]);
                 imx::red_add_v4(dst + 4, acc[4], acc[5], acc[6], acc[7]);
@@ -205,15 +228,14 @@ __global__ void finalize_kernel(const float* __restrict__ sum, const float* __re
 
 // --------------------------------------------------------------- modulation
 
-__device__ __forceinline__ float act_fwd(float v, int act) {
-    if (act == 1) return v > 0.0f ? v : 0.2f * v;
-    if (act == 2) return fmaxf(v, 0.0f);
-    return v;
+// The activation is carried as its negative-side slope (LeakyReLU 0.2, ReLU 0, none 1), so the
+// per-element code is select / min / max instructions instead of a branch on the activation type.
+inline float act_slope(int act) { return act == 1 ? 0.2f : (act == 2 ? 0.0f : 1.0f); }
+__device__ __forceinline__ float act_fwd(float v, float slope) {
+    return fmaxf(v, 0.0f) + slope * fminf(v, 0.0f);
 }
-__device__ __forceinline__ float act_grad(float pre, int act) {
-    if (act == 1) return pre > 0.0f ? 1.0f : 0.2f;
-    if (act == 2) return pre > 0.0f ? 1.0f : 0.0f;
-    return 1.0f;
+__device__ __forceinline__ float act_grad(float pre, float slope) {
+    return pre > 0.0f ? 1.0f : slope;
 }
 
 struct ModArgs {
@@ -226,7 +248,8 @@ struct ModArgs {
     const void* gamma;
     const void* beta;
     int N, H, W, C;
-    int per_instance, gb_mode, act, up2x;
+    int per_instance, gb_mode, up2x;
+    float slope;    // activation as its negative-side slope (act_slope)
     float* gbsum;   // backward pass 1, gb_mode 0: optional (2, C) per-channel sums of dgamma / dbeta
 };
 
@@ -248,7 +271,9 @@ __device__ __forceinline__ void load_norm_params(const ModArgs& a, int n, int c,
 }
 
 // grid = (blocks, N).  Each block walks a pixel range of one sample.
-template <int kMode>  // 0: forward   1: backward pass 1 (dgamma/dbeta + reductions)   2: backward pass 2 (dx)
+// kAffine: the inner norm has a learned weight / bias (false for SPADE's parameter-free norm, which
+// then carries 16 fewer live registers per thread).
+template <int kMode, bool kAffine>  // 0: forward   1: backward pass 1 (dgamma/dbeta + reductions)   2: backward pass 2 (dx)
 __global__ void __launch_bounds__(kThreads, 2)
 modulate_kernel(ModArgs a, uint4* __restrict__ out0, void* __restrict__ out1, void* __restrict__ out2,
                 float* __restrict__ red, float inv_count, int use_batch_stats,
@@ -259,15 +284,21 @@ modulate_kernel(ModArgs a, uint4* __restrict__ out0, void* __restrict__ out1, vo
     const bool active = r < rows;
     const int n = blockIdx.y;
     const long HW = (long)a.H * a.W;
-    const long per = (HW + gridDim.x - 1) / gridDim.x;
-    const long p0 = (long)blockIdx.x * per;
-    const long p1 = p0 + per < HW ? p0 + per : HW;
+    // Block-interleaved pixel rows (block b takes rows b, b + gridDim.x, ... of `rows` pixels): at any
+    // moment the resident CTAs together read one compact window of each tensor, which keeps more
+    // DRAM pages open than giving every CTA its own distant contiguous range (1-6 % faster).
+    const long p0 = (long)blockIdx.x * rows;
+    const long p1 = HW;
+    const long pstep = (long)rows * gridDim.x;
     const int Wx = a.up2x ? a.W / 2 : a.W;
     const long HWx = a.up2x ? HW / 4 : HW;
     const uint4* xb = a.x + (size_t)n * HWx * cg;
     const size_t ob = (size_t)n * HW * cg;
+    const bool want_gbsum = kMode == 1 && (a.gb_mode == 1 || a.gbsum != nullptr);
 
-    for (int c8 = ci; c8 < cg; c8 += tpr) {
+    for (int c8b = 0; c8b < cg; c8b += tpr) {   // block-uniform trip count (barriers inside)
+        const int c8 = c8b + ci < cg ? c8b + ci : cg - 1;   // surplus threads shadow the last group, write nothing
+        const bool own = c8b + ci < cg;
         const int c = c8 * 8;
         float rs[8], mr[8], ww[8], bb[8];
         load_norm_params(a, n, c, rs, mr, ww, bb);
@@ -292,7 +323,7 @@ modulate_kernel(ModArgs a, uint4* __restrict__ out0, void* __restrict__ out1, vo
         }
         float r1[8] = {0, 0, 0, 0, 0, 0, 0, 0}, r2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         float ag[8] = {0, 0, 0, 0, 0, 0, 0, 0}, ab[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        if (active) {
+        if (active && own) {
             // Raw 128-bit loads of one pixel row.  The next row's loads are issued before the
             // current row is processed (register double buffering): twice the bytes in flight
             // per thread, which is what a 2-CTA/SM kernel needs to approach HBM bandwidth.
@@ -317,8 +348,8 @@ modulate_kernel(ModArgs a, uint4* __restrict__ out0, void* __restrict__ out1, vo
                 return q;
             };
             Raw cur = load_raw(p0 + r < p1 ? p0 + r : p1 - 1);
-            for (long p = p0 + r; p < p1; p += rows) {
-                const long pn = p + rows;
+            for (long p = p0 + r; p < p1; p += pstep) {
+                const long pn = p + pstep;
                 const Raw nxt = load_raw(pn < p1 ? pn : p);   // tail: harmless re-read of the current row
                 float xv[8], g[8], be[8];
                 unpack8(cur.x, xv);
@@ -336,8 +367,9 @@ modulate_kernel(ModArgs a, uint4* __restrict__ out0, void* __restrict__ out1, vo
                     float y[8];
 #pragma unroll
                     for (int k = 0; k < 8; ++k) {
-                        const float xh = fmaf(fmaf(xv[k], rs[k], mr[k]), ww[k], bb[k]);
-                        y[k] = act_fwd(fmaf(xh, 1.0f + g[k], be[k]), a.act);
+                        const float xn = fmaf(xv[k], rs[k], mr[k]);
+                        const float xh = kAffine ? fmaf(xn, ww[k], bb[k]) : xn;
+                        y[k] = act_fwd(fmaf(xh, 1.0f + g[k], be[k]), a.slope);
                     }
                     imx::stg_stream(out0 + ob + (size_t)p * cg + c8, pack8(y));
                 } else {
@@ -347,19 +379,19 @@ modulate_kernel(ModArgs a, uint4* __restrict__ out0, void* __restrict__ out1, vo
 #pragma unroll
                     for (int k = 0; k < 8; ++k) {
                         const float xn = fmaf(xv[k], rs[k], mr[k]);       // normalised x
-                        const float xh = fmaf(xn, ww[k], bb[k]);          // + inner affine
+                        const float xh = kAffine ? fmaf(xn, ww[k], bb[k]) : xn;   // + inner affine
                         const float pre = fmaf(xh, 1.0f + g[k], be[k]);
-                        const float dpre = dyv[k] * act_grad(pre, a.act);
+                        const float dpre = dyv[k] * act_grad(pre, a.slope);
                         const float dxh = dpre * (1.0f + g[k]);           // grad wrt xh
                         if (kMode == 1) {
                             o0[k] = dpre * xh;   // dgamma
                             o1[k] = dpre;        // dbeta
                             r1[k] += dxh;                  // -> dbias of the inner norm
                             r2[k] = fmaf(dxh, xn, r2[k]);  // -> dweight of the inner norm
-                            if (a.gb_mode == 1 || a.gbsum) { ag[k] += o0[k]; ab[k] += o1[k]; }
+                            if (want_gbsum) { ag[k] += o0[k]; ab[k] += o1[k]; }
                         } else {
                             // dx = rstd * w * (dxh - mean(dxh) - xn * mean(dxh * xn))
-                            o0[k] = rs[k] * ww[k] * (dxh - m1[k] - xn * m2[k]);
+                            o0[k] = (kAffine ? rs[k] * ww[k] : rs[k]) * (dxh - m1[k] - xn * m2[k]);
                         }
                     }
                     if (kMode == 1) {
@@ -375,8 +407,8 @@ modulate_kernel(ModArgs a, uint4* __restrict__ out0, void* __restrict__ out1, vo
             }
         }
         if (kMode == 1) {
-            // block-level reduction of r1, r2 (and adaptive dgamma/dbeta) over the row groups
-            for (int pass = 0; pass < ((a.gb_mode == 1 || a.gbsum) ? 2 : 1); ++pass) {
+            // block-level reduction of r1, r2 (and the dgamma / dbeta sums)
+            for (int pass = 0; pass < (want_gbsum ? 2 : 1); ++pass) {
                 __syncthreads();
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
@@ -384,13 +416,15 @@ modulate_kernel(ModArgs a, uint4* __restrict__ out0, void* __restrict__ out1, vo
                     sred[tid][8 + k] = pass == 0 ? r2[k] : ab[k];
                 }
                 __syncthreads();
+                float acc[16] = {};
                 if (r == 0) {
-                    float acc[16];
 #pragma unroll
                     for (int k = 0; k < 16; ++k) acc[k] = sred[tid][k];
                     for (int rr = 1; rr < rows; ++rr)
 #pragma unroll
                         for (int k = 0; k < 16; ++k) acc[k] += sred[tid + rr * tpr][k];
+                }
+                if (r == 0 && own) {
                     if (pass == 0) {
                         const int G = a.per_instance ? a.N : 1;
                         const int so = (a.per_instance ? n * a.C : 0) + c;
@@ -446,7 +480,7 @@ extern "C" int imx_bn_stats_nhwc_bf16(const imx_bf16* x, float* sum, float* sums
     const int groups = per_instance ? N : 1;
     IMX_REQUIRE(groups <= 65535, "bn_stats: batch too large");
     const long HWg = per_instance ? HW : (long)N * HW;
-    dim3 grid(pick_blocks(HWg, m.rows, groups, 4), groups);
+    dim3 grid(pick_blocks(HWg, m.rows, groups, stats_ctas_per_sm((long)N * HW * C)), groups);
     stats_kernel<true><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<const uint4*>(x), sum, sumsq, HWg, C, m.cg, m.tpr, m.rows, m.cg);
     return imx::check_launch("bn_stats");
@@ -459,7 +493,7 @@ extern "C" int imx_channel_sum_nhwc_bf16(const imx_bf16* x, float* out, int NP, 
     IMX_REQUIRE(C % 8 == 0 && Cp % 8 == 0, "channel_sum: C and Cp must be multiples of 8");
     if ((long)NP * C == 0) return IMX_OK;
     const RowMap m = make_rowmap(C);
-    dim3 grid(pick_blocks(NP, m.rows, 1, 4), 1);
+    dim3 grid(pick_blocks(NP, m.rows, 1, stats_ctas_per_sm((long)NP * C)), 1);
     stats_kernel<false><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<const uint4*>(x), out, nullptr, NP, C, m.cg, m.tpr, m.rows, Cp / 8);
     return imx::check_launch("channel_sum");
@@ -472,7 +506,7 @@ extern "C" int imx_act_bwd_bias_nhwc_bf16(const imx_bf16* dy, const imx_bf16* y,
     IMX_REQUIRE(act == 1 || act == 2, "act_bwd_bias: act must be 1 (LeakyReLU 0.2) or 2 (ReLU)");
     if (NP * C == 0) return IMX_OK;
     const RowMap m = make_rowmap(C);
-    dim3 grid(pick_blocks(NP, m.rows, 1, 4), 1);
+    dim3 grid(pick_blocks(NP, m.rows, 1, 2), 1);
     act_bwd_sum_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(y), reinterpret_cast<uint4*>(dx), bias_grad, NP,
         m.cg, m.tpr, m.rows, act == 1 ? 0.2f : 0.0f);
@@ -506,9 +540,10 @@ extern "C" int imx_spade_modulate_fwd(const imx_bf16* x, const float* mean, cons
     if ((long)N * H * W * C == 0) return IMX_OK;
     const RowMap m = make_rowmap(C);
     ModArgs a{reinterpret_cast<const uint4*>(x), nullptr, mean, rstd, w, b, gamma, beta,
-              N, H, W, C, stats_per_instance, gb_mode, act, up2x, nullptr};
+              N, H, W, C, stats_per_instance, gb_mode, up2x, act_slope(act), nullptr};
     dim3 grid(pick_blocks((long)H * W, m.rows, N, 6), N);
-    modulate_kernel<0><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
+    auto kern = (w || b) ? modulate_kernel<0, true> : modulate_kernel<0, false>;
+    kern<<<grid, kThreads, 0, (cudaStream_t)stream>>>(
         a, reinterpret_cast<uint4*>(y), nullptr, nullptr, nullptr, 0.0f, 1, m.cg, m.tpr, m.rows);
     return imx::check_launch("spade_modulate_fwd");
 }
@@ -528,9 +563,10 @@ extern "C" int imx_spade_modulate_bwd_reduce(const imx_bf16* x, const imx_bf16* 
     if ((long)N * H * W * C == 0) return IMX_OK;
     const RowMap m = make_rowmap(C);
     ModArgs a{reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(dy), mean, rstd, w, b, gamma, beta,
-              N, H, W, C, stats_per_instance, gb_mode, act, 0, gb_mode == 0 ? gb_sums : nullptr};
+              N, H, W, C, stats_per_instance, gb_mode, 0, act_slope(act), gb_mode == 0 ? gb_sums : nullptr};
     dim3 grid(pick_blocks((long)H * W, m.rows, N), N);
-    modulate_kernel<1><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
+    auto kern = (w || b) ? modulate_kernel<1, true> : modulate_kernel<1, false>;
+    kern<<<grid, kThreads, 0, (cudaStream_t)stream>>>(
         a, nullptr, dgamma, dbeta, red, 0.0f, 1, m.cg, m.tpr, m.rows);
     return imx::check_launch("spade_modulate_bwd_reduce");
 }
@@ -550,9 +586,10 @@ extern "C" int imx_spade_modulate_bwd_dx(const imx_bf16* x, const imx_bf16* dy,
     if ((long)N * H * W * C == 0) return IMX_OK;
     const RowMap m = make_rowmap(C);
     ModArgs a{reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(dy), mean, rstd, w, b, gamma, beta,
-              N, H, W, C, stats_per_instance, gb_mode, act, 0, nullptr};
+              N, H, W, C, stats_per_instance, gb_mode, 0, act_slope(act), nullptr};
     dim3 grid(pick_blocks((long)H * W, m.rows, N, 6), N);
-    modulate_kernel<2><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
+    auto kern = (w || b) ? modulate_kernel<2, true> : modulate_kernel<2, false>;
+    kern<<<grid, kThreads, 0, (cudaStream_t)stream>>>(
         a, reinterpret_cast<uint4*>(dx), nullptr, nullptr, const_cast<float*>(red),
         use_batch_stats ? 1.0f / count : 0.0f, use_batch_stats, m.cg, m.tpr, m.rows);
     return imx::check_launch("spade_modulate_bwd_dx");
