@@ -15,6 +15,7 @@
 // per pixel, not once per channel as in the reference); consecutive lanes own
 // consecutive x so flow loads / output stores are 128-byte coalesced, and the
 // 2-D block (32 x 8 pixels) keeps the taps shared by neighbouring rows in L1.
+#include <type_traits>
 #include "imx_common.cuh"
 #include "../../include/imx.h"
 
@@ -53,7 +54,45 @@ __device__ __forceinline__ Taps r2d_taps(float dx, float dy, int x, int y, int c
     return t;
 }
 
-__global__ void __launch_bounds__(TX* TY)
+// Channel groups: the 4 * U gathers of U channels are issued before any of them is used.  A thread
+// that walks the channels one at a time has four 4-byte gathers in flight, three of which usually
+// hit L1 / L2, so only a quarter of its outstanding requests move new DRAM bytes and the kernel
+// sits at ~0.4 of the HBM peak whatever the flow looks like (measured with a constant flow).
+// The minimum-CTA launch bound matters as in spade_norm.cu: without it ptxas recycles the
+// destination registers of the loads and serialises the channels again.
+constexpr int kMinCtas = 4;
+constexpr long kGroupMinElems = 8L << 20;   // output elements from which the grouped kernels pay off
+constexpr int kMinCtasBwd = 3;   // 20 loads in flight per group plus both sets of taps: 64 registers spill
+
+template <int U>
+__device__ __forceinline__ void r2d_fwd_group(const float* __restrict__ ip, float* __restrict__ op, size_t hwi, size_t hw,
+                                              int oTL, int oTR, int oBL, int oBR, double w00, double w01, double w10,
+                                              float w11) {
+    float tl[U], tr[U], bl[U], br[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        const float* q = ip + (size_t)u * hwi;
+        tl[u] = __ldg(q + oTL);
+        tr[u] = __ldg(q + oTR);
+        bl[u] = __ldg(q + oBL);
+        br[u] = __ldg(q + oBR);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        float v = 0.0f;
+        v += static_cast<float>(w00 * (double)tl[u]);
+        v += static_cast<float>(w01 * (double)tr[u]);
+        v += static_cast<float>(w10 * (double)bl[u]);
+        v += __fmul_rn(w11, br[u]);
+        __stcs(op + (size_t)u * hw, v);
+    }
+}
+
+// kGroup false (small launches, a few waves of CTAs at most): one channel at a time and no
+// minimum-CTA hint, which keeps more CTAs resident; there the latency of a thread's dependent
+// chain (flow -> taps -> gathers -> store) is hidden by other warps rather than by its own loads.
+template <bool kGroup>
+__global__ void __launch_bounds__(TX* TY, kGroup ? kMinCtas : 0)
 resample2d_fwd_kernel(const float* __restrict__ img, const float* __restrict__ flow,
                       float* __restrict__ out, int C, int H, int W, int Hi, int Wi,
                       int cpb, int nchunk) {
@@ -78,21 +117,30 @@ resample2d_fwd_kernel(const float* __restrict__ img, const float* __restrict__ f
     const int c1 = min(C, c0 + cpb);
     const float* ip = img + ((size_t)b * C + c0) * hwi;
     float* op = out + ((size_t)b * C + c0) * hw + (size_t)y * W + x;
+    int c = c0;
+    if (kGroup) {
+        for (; c + 4 <= c1; c += 4, ip += 4 * hwi, op += 4 * hw)
+            r2d_fwd_group<4>(ip, op, hwi, hw, oTL, oTR, oBL, oBR, w00, w01, w10, w11);
+        if (c1 - c == 3) r2d_fwd_group<3>(ip, op, hwi, hw, oTL, oTR, oBL, oBR, w00, w01, w10, w11);
+        else if (c1 - c == 2) r2d_fwd_group<2>(ip, op, hwi, hw, oTL, oTR, oBL, oBR, w00, w01, w10, w11);
+        else if (c1 - c == 1) r2d_fwd_group<1>(ip, op, hwi, hw, oTL, oTR, oBL, oBR, w00, w01, w10, w11);
+    } else {
 #pragma unroll 4
-    for (int c = c0; c < c1; ++c, ip += hwi, op += hw) {
-        float v = 0.0f;
-        v += static_cast<float>(w00 * (double)__ldg(ip + oTL));
-        v += static_cast<float>(w01 * (double)__ldg(ip + oTR));
-        v += static_cast<float>(w10 * (double)__ldg(ip + oBL));
-        v += __fmul_rn(w11, __ldg(ip + oBR));
-        __stcs(op, v);
+        for (; c < c1; ++c, ip += hwi, op += hw) {
+            float v = 0.0f;
+            v += static_cast<float>(w00 * (double)__ldg(ip + oTL));
+            v += static_cast<float>(w01 * (double)__ldg(ip + oTR));
+            v += static_cast<float>(w10 * (double)__ldg(ip + oBL));
+            v += __fmul_rn(w11, __ldg(ip + oBR));
+            __stcs(op, v);
+        }
     }
 }
 
 // One pass over the channels produces both gradients: the 4-tap scatter into
 // grad_img (atomics, like the reference) and the per-pixel flow gradient, which
 // the reference computes in a second kernel that re-reads everything.
-__global__ void __launch_bounds__(TX* TY)
+__global__ void __launch_bounds__(TX* TY, kMinCtasBwd)
 resample2d_bwd_kernel(const float* __restrict__ img, const float* __restrict__ flow,
                       const float* __restrict__ gout, float* __restrict__ gimg,
                       float* __restrict__ gflow, int C, int H, int W, int Hi, int Wi,
@@ -125,32 +173,54 @@ resample2d_bwd_kernel(const float* __restrict__ img, const float* __restrict__ f
     const float* ip = img + (size_t)b * C * hwi;
     const float* gp = gout + (size_t)b * C * hw + (size_t)y * W + x;
     float* gi = gimg ? gimg + (size_t)b * C * hwi : nullptr;
-    for (int c = 0; c < C; ++c, ip += hwi, gp += hw) {
-        const float g = __ldcs(gp);
-        if (gi) {
-            atomicAdd(gi + syT * Wi + sxL, s00 * g);
-            atomicAdd(gi + syT * Wi + sxR, s01 * g);
-            atomicAdd(gi + syB * Wi + sxL, s10 * g);
-            atomicAdd(gi + syB * Wi + sxR, s11 * g);
-            gi += hwi;
-        }
+    // Groups of up to four channels: all loads of the group first (see r2d_fwd_group), then the
+    // per-channel work in channel order, so the flow gradient keeps the reference's summation order.
+    auto group = [&](auto tag) {
+        constexpr int U = decltype(tag)::value;
+        float g[U], iTL[U], iTR[U], iBL[U], iBR[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) g[u] = __ldcs(gp + (size_t)u * hw);
         if (gflow) {
-            const float iTL = __ldg(ip + oTL), iTR = __ldg(ip + oTR);
-            const float iBL = __ldg(ip + oBL), iBR = __ldg(ip + oBR);
-            // Same operation order as the reference, no FMA contraction, so the flow
-            // gradient is bit-exact against the CPU restatement.
-            const float a0 = __fmul_rn(gx, g), a1 = __fmul_rn(1.0f - gx, g);
-            accx = __fadd_rn(accx, __fmul_rn(a0, iTR));
-            accx = __fsub_rn(accx, __fmul_rn(a0, iTL));
-            accx = __fadd_rn(accx, __fmul_rn(a1, iBR));
-            accx = __fsub_rn(accx, __fmul_rn(a1, iBL));
-            const float b0 = __fmul_rn(gy, g), b1 = __fmul_rn(1.0f - gy, g);
-            accy = __fadd_rn(accy, __fmul_rn(b0, iBL));
-            accy = __fsub_rn(accy, __fmul_rn(b0, iTL));
-            accy = __fadd_rn(accy, __fmul_rn(b1, iBR));
-            accy = __fsub_rn(accy, __fmul_rn(b1, iTR));
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const float* q = ip + (size_t)u * hwi;
+                iTL[u] = __ldg(q + oTL); iTR[u] = __ldg(q + oTR);
+                iBL[u] = __ldg(q + oBL); iBR[u] = __ldg(q + oBR);
+            }
         }
-    }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (gi) {
+                float* d = gi + (size_t)u * hwi;
+                atomicAdd(d + syT * Wi + sxL, s00 * g[u]);
+                atomicAdd(d + syT * Wi + sxR, s01 * g[u]);
+                atomicAdd(d + syB * Wi + sxL, s10 * g[u]);
+                atomicAdd(d + syB * Wi + sxR, s11 * g[u]);
+            }
+            if (gflow) {
+                // Same operation order as the reference, no FMA contraction, so the flow
+                // gradient is bit-exact against the CPU restatement.
+                const float a0 = __fmul_rn(gx, g[u]), a1 = __fmul_rn(1.0f - gx, g[u]);
+                accx = __fadd_rn(accx, __fmul_rn(a0, iTR[u]));
+                accx = __fsub_rn(accx, __fmul_rn(a0, iTL[u]));
+                accx = __fadd_rn(accx, __fmul_rn(a1, iBR[u]));
+                accx = __fsub_rn(accx, __fmul_rn(a1, iBL[u]));
+                const float b0 = __fmul_rn(gy, g[u]), b1 = __fmul_rn(1.0f - gy, g[u]);
+                accy = __fadd_rn(accy, __fmul_rn(b0, iBL[u]));
+                accy = __fsub_rn(accy, __fmul_rn(b0, iTL[u]));
+                accy = __fadd_rn(accy, __fmul_rn(b1, iBR[u]));
+                accy = __fsub_rn(accy, __fmul_rn(b1, iTR[u]));
+            }
+        }
+        ip += (size_t)U * hwi;
+        gp += (size_t)U * hw;
+        if (gi) gi += (size_t)U * hwi;
+    };
+    int c = 0;
+    for (; c + 4 <= C; c += 4) group(std::integral_constant<int, 4>{});
+    if (C - c == 3) group(std::integral_constant<int, 3>{});
+    else if (C - c == 2) group(std::integral_constant<int, 2>{});
+    else if (C - c == 1) group(std::integral_constant<int, 1>{});
     if (gflow) {
         float* gf = gflow + (size_t)b * 2 * hw + (size_t)y * W + x;
         __stcs(gf, accx);
@@ -202,7 +272,34 @@ __device__ __forceinline__ GsTaps gs_taps(float fx, float fy, int x, int y, int 
     return t;
 }
 
-__global__ void __launch_bounds__(TX* TY)
+template <int U>
+__device__ __forceinline__ void gs_fwd_group(const float* __restrict__ ip, float* __restrict__ op, size_t hw, const GsTaps& t) {
+    // The tap offsets are always in range (gs_taps folds a missing east / south neighbour onto the
+    // pixel itself), so every load is unconditional and the validity test is a select afterwards.
+    float vnw[U], vne[U], vsw[U], vse[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        const float* q = ip + (size_t)u * hw;
+        vnw[u] = __ldg(q + t.o_nw);
+        vne[u] = __ldg(q + t.o_ne);
+        vsw[u] = __ldg(q + t.o_sw);
+        vse[u] = __ldg(q + t.o_se);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        float o = __fmul_rn(vnw[u], t.nw);
+        o = fmaf(t.e_ok ? vne[u] : 0.0f, t.ne, o);
+        o = fmaf(t.s_ok ? vsw[u] : 0.0f, t.sw, o);
+        o = fmaf((t.e_ok && t.s_ok) ? vse[u] : 0.0f, t.se, o);
+        __stcs(op + (size_t)u * hw, o);
+    }
+}
+
+// kGroup false: one channel at a time and no minimum-CTA hint (32 registers, 8 CTAs per SM).  With only 3-4 channels a
+// thread lives too briefly for its own loads to overlap much, and occupancy wins (measured at
+// B=8, C=3: 58 us one-by-one, 66 us grouped; at C=64 grouped is 0.47 vs 0.37 of the HBM peak).
+template <bool kGroup>
+__global__ void __launch_bounds__(TX* TY, kGroup ? kMinCtas : 0)
 gridsample_warp_fwd_kernel(const float* __restrict__ img, const float* __restrict__ flow,
                            float* __restrict__ out, int C, int H, int W, int cpb, int nchunk) {
     const int x = blockIdx.x * TX + threadIdx.x;
@@ -216,21 +313,30 @@ gridsample_warp_fwd_kernel(const float* __restrict__ img, const float* __restric
     const int c1 = min(C, c0 + cpb);
     const float* ip = img + ((size_t)b * C + c0) * hw;
     float* op = out + ((size_t)b * C + c0) * hw + (size_t)y * W + x;
+    int c = c0;
+    if (kGroup) {
+        for (; c + 4 <= c1; c += 4, ip += 4 * hw, op += 4 * hw) gs_fwd_group<4>(ip, op, hw, t);
+        if (c1 - c == 3) gs_fwd_group<3>(ip, op, hw, t);
+        else if (c1 - c == 2) gs_fwd_group<2>(ip, op, hw, t);
+        else if (c1 - c == 1) gs_fwd_group<1>(ip, op, hw, t);
+    } else {
 #pragma unroll 4
-    for (int c = c0; c < c1; ++c, ip += hw, op += hw) {
-        const float vnw = __ldg(ip + t.o_nw);
-        const float vne = t.e_ok ? __ldg(ip + t.o_ne) : 0.0f;
-        const float vsw = t.s_ok ? __ldg(ip + t.o_sw) : 0.0f;
-        const float vse = (t.e_ok && t.s_ok) ? __ldg(ip + t.o_se) : 0.0f;
-        float o = __fmul_rn(vnw, t.nw);
-        o = fmaf(vne, t.ne, o);
-        o = fmaf(vsw, t.sw, o);
-        o = fmaf(vse, t.se, o);
-        __stcs(op, o);
+        for (; c < c1; ++c, ip += hw, op += hw) {
+            const float vnw = __ldg(ip + t.o_nw);
+            const float vne = t.e_ok ? __ldg(ip + t.o_ne) : 0.0f;
+            const float vsw = t.s_ok ? __ldg(ip + t.o_sw) : 0.0f;
+            const float vse = (t.e_ok && t.s_ok) ? __ldg(ip + t.o_se) : 0.0f;
+            float o = __fmul_rn(vnw, t.nw);
+            o = fmaf(vne, t.ne, o);
+            o = fmaf(vsw, t.sw, o);
+            o = fmaf(vse, t.se, o);
+            __stcs(op, o);
+        }
     }
 }
 
-__global__ void __launch_bounds__(TX* TY)
+template <bool kGroup>
+__global__ void __launch_bounds__(TX* TY, kGroup ? kMinCtasBwd : 0)
 gridsample_warp_bwd_kernel(const float* __restrict__ img, const float* __restrict__ flow,
                            const float* __restrict__ gout, float* __restrict__ gimg,
                            float* __restrict__ gflow, int C, int H, int W) {
@@ -246,23 +352,47 @@ gridsample_warp_bwd_kernel(const float* __restrict__ img, const float* __restric
     const float* ip = img + (size_t)b * C * hw;
     const float* gp = gout + (size_t)b * C * hw + (size_t)y * W + x;
     float* gi = gimg ? gimg + (size_t)b * C * hw : nullptr;
-    for (int c = 0; c < C; ++c, ip += hw, gp += hw) {
-        const float g = __ldcs(gp);
-        if (gi) {
-            atomicAdd(gi + t.o_nw, t.nw * g);
-            if (t.e_ok) atomicAdd(gi + t.o_ne, t.ne * g);
-            if (t.s_ok) atomicAdd(gi + t.o_sw, t.sw * g);
-            if (t.e_ok && t.s_ok) atomicAdd(gi + t.o_se, t.se * g);
-            gi += hw;
-        }
+    const bool se_ok = t.e_ok && t.s_ok;
+    auto group = [&](auto tag) {   // all loads of up to four channels first, see r2d_fwd_group
+        constexpr int U = decltype(tag)::value;
+        float g[U], vnw[U], vne[U], vsw[U], vse[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) g[u] = __ldcs(gp + (size_t)u * hw);
         if (gflow) {
-            const float vnw = __ldg(ip + t.o_nw);
-            const float vne = t.e_ok ? __ldg(ip + t.o_ne) : 0.0f;
-            const float vsw = t.s_ok ? __ldg(ip + t.o_sw) : 0.0f;
-            const float vse = (t.e_ok && t.s_ok) ? __ldg(ip + t.o_se) : 0.0f;
-            gix += g * ((vne - vnw) * s + (vse - vsw) * t.wy);
-            giy += g * ((vsw - vnw) * e + (vse - vne) * t.wx);
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const float* q = ip + (size_t)u * hw;
+                vnw[u] = __ldg(q + t.o_nw); vne[u] = __ldg(q + t.o_ne);
+                vsw[u] = __ldg(q + t.o_sw); vse[u] = __ldg(q + t.o_se);
+            }
         }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (gi) {
+                float* d = gi + (size_t)u * hw;
+                atomicAdd(d + t.o_nw, t.nw * g[u]);
+                if (t.e_ok) atomicAdd(d + t.o_ne, t.ne * g[u]);
+                if (t.s_ok) atomicAdd(d + t.o_sw, t.sw * g[u]);
+                if (se_ok) atomicAdd(d + t.o_se, t.se * g[u]);
+            }
+            if (gflow) {
+                const float ne = t.e_ok ? vne[u] : 0.0f, sw = t.s_ok ? vsw[u] : 0.0f, se = se_ok ? vse[u] : 0.0f;
+                gix += g[u] * ((ne - vnw[u]) * s + (se - sw) * t.wy);
+                giy += g[u] * ((sw - vnw[u]) * e + (se - ne) * t.wx);
+            }
+        }
+        ip += (size_t)U * hw;
+        gp += (size_t)U * hw;
+        if (gi) gi += (size_t)U * hw;
+    };
+    int c = 0;
+    if (kGroup) {
+        for (; c + 4 <= C; c += 4) group(std::integral_constant<int, 4>{});
+        if (C - c == 3) group(std::integral_constant<int, 3>{});
+        else if (C - c == 2) group(std::integral_constant<int, 2>{});
+        else if (C - c == 1) group(std::integral_constant<int, 1>{});
+    } else {
+        for (; c < C; ++c) group(std::integral_constant<int, 1>{});
     }
     if (gflow) {
         // d(ix)/d(flow_x) = ((W-1)/2) / ((W-1)/2) = 1 inside the border, 0 where clipped.
@@ -287,7 +417,10 @@ extern "C" int imx_resample2d_fwd_f32(const float* img, const float* flow, float
     const int nchunk = (C + cpb - 1) / cpb;
     IMX_REQUIRE((long)B * nchunk <= 65535, "resample2d_fwd: batch*channel-chunks too large");
     dim3 grid((W + TX - 1) / TX, (H + TY - 1) / TY, B * nchunk), block(TX, TY);
-    resample2d_fwd_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(img, flow, out, C, H, W, Hi, Wi, cpb, nchunk);
+    if ((long)B * C * H * W >= kGroupMinElems)
+        resample2d_fwd_kernel<true><<<grid, block, 0, (cudaStream_t)stream>>>(img, flow, out, C, H, W, Hi, Wi, cpb, nchunk);
+    else
+        resample2d_fwd_kernel<false><<<grid, block, 0, (cudaStream_t)stream>>>(img, flow, out, C, H, W, Hi, Wi, cpb, nchunk);
     return imx::check_launch("resample2d_fwd");
 }
 
@@ -319,7 +452,8 @@ extern "C" int imx_gridsample_warp_fwd_f32(const float* img, const float* flow, 
     const int nchunk = (C + cpb - 1) / cpb;
     IMX_REQUIRE((long)B * nchunk <= 65535, "gridsample_warp_fwd: batch*channel-chunks too large");
     dim3 grid((W + TX - 1) / TX, (H + TY - 1) / TY, B * nchunk), block(TX, TY);
-    gridsample_warp_fwd_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(img, flow, out, C, H, W, cpb, nchunk);
+    if (cpb >= 8) gridsample_warp_fwd_kernel<true><<<grid, block, 0, (cudaStream_t)stream>>>(img, flow, out, C, H, W, cpb, nchunk);
+    else gridsample_warp_fwd_kernel<false><<<grid, block, 0, (cudaStream_t)stream>>>(img, flow, out, C, H, W, cpb, nchunk);
     return imx::check_launch("gridsample_warp_fwd");
 }
 
@@ -333,6 +467,7 @@ extern "C" int imx_gridsample_warp_bwd_f32(const float* img, const float* flow, 
     if ((long)B * H * W == 0) return IMX_OK;
     IMX_REQUIRE(H >= 2 && W >= 2, "gridsample_warp_bwd: H and W must be >= 2");
     dim3 grid((W + TX - 1) / TX, (H + TY - 1) / TY, B), block(TX, TY);
-    gridsample_warp_bwd_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(img, flow, grad_out, grad_img, grad_flow, C, H, W);
+    if (C >= 8) gridsample_warp_bwd_kernel<true><<<grid, block, 0, (cudaStream_t)stream>>>(img, flow, grad_out, grad_img, grad_flow, C, H, W);
+    else gridsample_warp_bwd_kernel<false><<<grid, block, 0, (cudaStream_t)stream>>>(img, flow, grad_out, grad_img, grad_flow, C, H, W);
     return imx::check_launch("gridsample_warp_bwd");
 }

@@ -55,10 +55,45 @@ def config1():
                       'gflop_per_img': 420.0, 'gpu_tflops': 0.420 / t, 'mode': 'train-mode norms, no_grad'}))
 
 
-def synthetic_flow(b, h, w, gen):
-    """bilinear upsample of N(0, 8 px) drawn at 32x64."""
-    low = torch.randn(b, 2, 32, 64, generator=gen) * 8.0
+def synthetic_flow(b, h, w, gen, grid=(32, 64)):
+    """bilinear upsample of N(0, 8 px) drawn at 32x64 (``grid``: coarser grids
+    give smoother fields of the same amplitude)."""
+    low = torch.randn(b, 2, grid[0], grid[1], generator=gen) * 8.0
     return torch.nn.functional.interpolate(low, size=(h, w), mode='bilinear', align_corners=False).contiguous()
+
+
+def config4_smoothness():
+    """The same warps as config4 (B=8, C in {3, 64}) under smoother flow fields: N(0, 8 px) drawn on
+    coarser grids, and a constant translation.  Shows how much of the distance to the HBM peak is
+    the gather pattern of the SURVEY flow (|grad flow| ~0.7 px/px) rather than the kernel."""
+    from imaginaire_b200 import ops
+    h, w, b = 512, 1024, 8
+    g = torch.Generator().manual_seed(4)
+    for c in (3, 64):
+        img = torch.randn(b, c, h, w, generator=g).to(DEV)
+        go = torch.randn(b, c, h, w, generator=g).to(DEV)
+        fwd_bytes = (2 * c + 2) * b * h * w * 4
+        bwd_bytes = (3 * c + 4) * b * h * w * 4
+        for label, grid in (('N(0,8px) at 32x64 (SURVEY)', (32, 64)), ('N(0,8px) at 8x16', (8, 16)), ('N(0,8px) at 2x4', (2, 4)),
+                            ('constant (3.3, -2.6) px', None)):
+            if grid is None:
+                flow = torch.empty(b, 2, h, w)
+                flow[:, 0] = 3.3
+                flow[:, 1] = -2.6
+            else:
+                flow = synthetic_flow(b, h, w, g, grid)
+            gx = (flow[:, :, :, 1:] - flow[:, :, :, :-1]).abs().mean().item()
+            flow = flow.to(DEV)
+            reps = 20 if c == 3 else 5
+            tf = gpu_time(lambda: ops.resample2d_fwd(img, flow), reps)
+            tb = gpu_time(lambda: ops.resample2d_bwd(img, flow, go), reps)
+            tg = gpu_time(lambda: ops.gridsample_warp_fwd(img, flow), reps)
+            print(json.dumps({'config': 'config4 warp smoothness B=%d C=%d 512x1024, flow %s' % (b, c, label),
+                              'mean_abs_dflow_dx': gx,
+                              'resample2d_fwd_us': tf * 1e6, 'resample2d_fwd_frac_hbm': fwd_bytes / tf / 1e9 / HBM_PEAK,
+                              'resample_fwd_us': tg * 1e6, 'resample_fwd_frac_hbm': fwd_bytes / tg / 1e9 / HBM_PEAK,
+                              'resample2d_bwd_us': tb * 1e6, 'resample2d_bwd_frac_hbm': bwd_bytes / tb / 1e9 / HBM_PEAK}))
+        del img, go
 
 
 def config4():
@@ -199,6 +234,7 @@ def config5():
 
 if __name__ == '__main__':
     which = sys.argv[1] if len(sys.argv) > 1 else 'all'
-    for name, fn in (('config1', config1), ('config4', config4), ('config4', config4_flow_branch), ('config4', config4_generator), ('config5', config5)):
-        if which in (name, 'all'):
+    for name, fn in (('config1', config1), ('config4', config4), ('config4', config4_flow_branch), ('config4', config4_generator), ('config5', config5),
+                     ('config4_smoothness', config4_smoothness)):
+        if which == name or (which == 'all' and name != 'config4_smoothness'):
             fn()

@@ -45,6 +45,7 @@ def hbm():
         mean, rstd = ops.bn_finalize(sums, n * h * w, 1e-5)
         y = ops.spade_modulate_fwd(x, mean, rstd, None, None, g, b, False, 1)
         ops.spade_modulate_bwd(x, y, mean, rstd, None, None, g, b, False, 1, n * h * w)
+        ops.act_bwd_bias(g, y, 1, True)
     img = torch.randn(8, 64, 512, 1024, device='cuda')
     # SURVEY 8(d) config 4 flow: bilinear upsample of N(0, 8 px) drawn at 32 x 64
     flow = torch.nn.functional.interpolate(torch.randn(8, 2, 32, 64, device='cuda') * 8.0, size=(512, 1024),
