@@ -25,6 +25,25 @@ from .conv import Conv2dBlock, LinearBlock
 
 # ------------------------------------------------------------- inner norms
 
+def _frozen_identity_affine(weight, bias):
+    """True for a frozen weight / bias pair that is exactly (1, 0).
+
+    The reference builds SyncBatchNorm with affine=True whatever the config says and only switches
+    ``requires_grad`` off for ``affine: false`` (imaginaire/layers/activation_norm.py:403-410), so
+    SPADE's "parameter-free" inner norm carries a weight of ones and a bias of zeros that never
+    change.  Values are checked, not assumed (a loaded checkpoint may hold anything); the check
+    reads the device once per tensor version."""
+    if weight is None or bias is None or weight.requires_grad or bias.requires_grad or not weight.is_cuda:
+        return False
+    hit = getattr(weight, '_imx_identity_affine', None)     # cached on the tensor: dies with it
+    if hit is None or hit[0] != weight._version or hit[1] != bias._version or hit[2] is not bias:
+        with torch.no_grad():
+            ident = bool(((weight == 1).all() & (bias == 0).all()).item())
+        hit = (weight._version, bias._version, bias, ident)
+        weight._imx_identity_affine = hit
+    return hit[3]
+
+
 def norm_state(norm):
     """NormState view of a torch.nn normalisation module (None -> identity)."""
     if norm is None:
@@ -39,8 +58,11 @@ def norm_state(norm):
             raise NotImplementedError('InstanceNorm2d(track_running_stats=True) is not supported')
     else:
         raise NotImplementedError('inner norm %s is outside the SPADE hot path' % type(norm).__name__)
+    weight, bias = getattr(norm, 'weight', None), getattr(norm, 'bias', None)
+    if _frozen_identity_affine(weight, bias):
+        weight = bias = None      # the kernels' affine-free instantiation (fewer live registers)
     return NF.NormState(
-        kind, getattr(norm, 'weight', None), getattr(norm, 'bias', None),
+        kind, weight, bias,
         getattr(norm, 'running_mean', None), getattr(norm, 'running_var', None),
         norm.momentum, norm.eps, norm.training, norm.track_running_stats,
         getattr(norm, 'num_batches_tracked', None), getattr(norm, 'process_group', None))

@@ -54,6 +54,33 @@ def test_spade_norm_lrelu_vs_reference_golden(tag, grad):
             assert H.rel_err(sd[k].cpu(), after[k]) < 2e-3, k
 
 
+def test_frozen_identity_affine_takes_the_affine_free_kernels():
+    """SPADE's 'parameter-free' sync-batch norm carries a frozen weight of ones / bias of zeros (the
+    reference builds it with affine=True): detected by value, re-checked when the tensors change."""
+    from imaginaire_b200 import ops, functional as NF
+    from imaginaire_b200.layers import SpatiallyAdaptiveNorm
+    from imaginaire_b200.layers.activation_norm import norm_state
+    torch.manual_seed(3)
+    m = SpatiallyAdaptiveNorm(num_features=32, cond_dims=5, num_filters=16, kernel_size=3, separate_projection=True,
+                              activation_norm_type='sync_batch',
+                              activation_norm_params=types.SimpleNamespace(affine=False)).to(_dev()).train()
+    x = torch.randn(2, 32, 12, 20, device=_dev())
+    label = torch.randn(2, 5, 12, 20, device=_dev())
+    assert not m.norm.weight.requires_grad and norm_state(m.norm).weight is None
+    y1 = NF.to_nchw(m.forward_fused(x.clone().requires_grad_(True), label, act=ops.ACT_LRELU))
+    m.norm.weight.requires_grad_(True)            # same values through the affine instantiation
+    assert norm_state(m.norm).weight is not None
+    y2 = NF.to_nchw(m.forward_fused(x.clone().requires_grad_(True), label, act=ops.ACT_LRELU))
+    assert torch.equal(y1, y2)
+    m.norm.weight.requires_grad_(False)
+    with torch.no_grad():
+        m.norm.weight.fill_(2.0)
+        m.norm.bias.fill_(0.5)
+    assert norm_state(m.norm).weight is not None   # frozen but no longer the identity
+    y3 = NF.to_nchw(m.forward_fused(x.clone().requires_grad_(True), label, act=ops.ACT_LRELU))
+    assert not torch.allclose(y1, y3)
+
+
 def _make_res_block(d, cin, cout):
     from imaginaire_b200.layers import Res2dBlock
     an = types.SimpleNamespace(num_filters=16, kernel_size=5, separate_projection=True, cond_dims=6,
