@@ -9,6 +9,7 @@ import torch
 import torch.nn.functional as F
 from torch import nn
 
+from .. import functional as NF
 from ..layers import Conv2dBlock
 
 _VGG19 = [('relu_1_1', 3, 64), ('relu_1_2', 64, 64), 'pool',
@@ -97,6 +98,10 @@ class PerceptualLoss(nn.Module):
             with torch.no_grad():
                 feat_tg = self.model(target)
             for layer, weight in zip(self.layers, self.weights):
+                if isinstance(self.criterion, nn.L1Loss) and not self.instance_normalized:
+                    # bf16 feature maps: one fused kernel each way instead of ten ATen passes
+                    loss = loss + weight * NF.l1_loss_mean(feat_in[layer], feat_tg[layer].detach())
+                    continue
                 a, b = feat_in[layer].float(), feat_tg[layer].detach().float()
                 if self.instance_normalized:
                     a, b = F.instance_norm(a), F.instance_norm(b)

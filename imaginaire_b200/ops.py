@@ -298,6 +298,31 @@ def act_bwd_bias(dy, y, act, want_bias_grad):
     return dx, bg
 
 
+def _same_dense_layout(a, b):
+    return (a.shape == b.shape and a.stride() == b.stride()
+            and (a.is_contiguous() or (a.dim() == 4 and a.is_contiguous(memory_format=torch.channels_last))))
+
+
+def l1_abs_sum(a, b):
+    """1-element fp32 tensor: sum |a - b| over two bf16 tensors of one dense layout."""
+    _req_cuda(a, b)
+    if a.dtype != torch.bfloat16 or b.dtype != torch.bfloat16 or not _same_dense_layout(a, b):
+        raise ValueError('l1_abs_sum: bf16 tensors of one dense memory layout expected')
+    out = torch.zeros(1, dtype=torch.float32, device=a.device)
+    _C.lib().call('imx_l1_abs_sum_bf16', _ptr(a), _ptr(b), a.numel(), _ptr(out), _stream())
+    return out
+
+
+def l1_abs_grad(a, b, upstream, denom):
+    """bf16 tensor shaped and laid out like a: sign(a - b) * (upstream / denom) (upstream: fp32 device scalar)."""
+    _req_cuda(a, b, upstream)
+    if upstream.dtype != torch.float32 or upstream.numel() != 1:
+        raise ValueError('l1_abs_grad: upstream must be one fp32 value on the device')
+    grad = torch.empty_like(a)        # preserves the (dense) strides of a
+    _C.lib().call('imx_l1_abs_grad_bf16', _ptr(a), _ptr(b), _ptr(grad), a.numel(), _ptr(upstream), float(denom), _stream())
+    return grad
+
+
 def _gb_mode(gamma):
     if gamma is None:
         return 2

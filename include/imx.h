@@ -109,6 +109,19 @@ IMX_API int imx_bilinear_up2x_add_nhwc_bf16(const imx_bf16* src, const imx_bf16*
 IMX_API int imx_bilinear_up2x_bwd_nhwc_bf16(const imx_bf16* grad_out, imx_bf16* grad_src,
                                     int N, int h, int w, int C, imx_stream_t stream);
 
+/* Mean-absolute-difference loss on bf16 feature maps (flat arrays of n elements; a, b and grad
+ * dense, one shared memory layout, 16-byte aligned).
+ *   imx_l1_abs_sum_bf16 :  *sum += sum_i |float(a[i]) - float(b[i])|   (fp32; the caller zeroes *sum
+ *                          and divides by n for the mean)
+ *   imx_l1_abs_grad_bf16:  grad[i] = bf16(sign(a[i] - b[i]) * ((*upstream) / denom)), sign(0) = 0;
+ *                          upstream is a DEVICE scalar (the gradient of the loss value), denom a
+ *                          host value (n for the mean).  The gradient w.r.t. b is -grad.
+ * ref: nn.L1Loss on feature maps in imaginaire/losses/perceptual.py:66-67, :130-131 and
+ *      imaginaire/losses/feature_matching.py:12, :36-38. */
+IMX_API int imx_l1_abs_sum_bf16(const imx_bf16* a, const imx_bf16* b, int64_t n, float* sum, imx_stream_t stream);
+IMX_API int imx_l1_abs_grad_bf16(const imx_bf16* a, const imx_bf16* b, imx_bf16* grad, int64_t n,
+                         const float* upstream, float denom, imx_stream_t stream);
+
 /* NCHW fp32 -> NHWC bf16 (channels zero-padded to Cp) and back (first C of Cp). */
 IMX_API int imx_nchw_f32_to_nhwc_bf16(const float* src, imx_bf16* dst, int N, int C, int H, int W,
                               int Cp, imx_stream_t stream);

@@ -561,3 +561,46 @@ def test_wgrad_peer_reduce_and_gather_equal_the_averaged_gradient(case):
         assert bool(torch.isfinite(got).all())
         assert H.rel_err(got.cpu(), ref.cpu()) < 2e-6, r
         assert torch.equal(arenas[r][slot:], arenas[0][slot:])          # every rank holds the same bits
+
+
+@pytest.mark.parametrize('shape,nhwc', [((2, 16, 8, 12), True), ((1, 8, 1, 3), True), ((3, 7, 5, 3), False),
+                                        ((8, 64, 64, 96), True), ((1, 1, 1, 1), False)])
+def test_l1_loss_mean_vs_torch(shape, nhwc):
+    """Fused feature-map L1 (value and gradient) against the torch expression it replaces, in fp32."""
+    from imaginaire_b200 import functional as NF
+    torch.manual_seed(11)
+    dev = torch.device('cuda:0')
+    a = torch.randn(*shape, device=dev).bfloat16()
+    b = torch.randn(*shape, device=dev).bfloat16()
+    b.view(-1)[::3] = a.view(-1)[::3]                     # exact ties: sign(0) = 0
+    if nhwc:
+        a = a.contiguous(memory_format=torch.channels_last)
+        b = b.contiguous(memory_format=torch.channels_last)
+    a1 = a.clone().requires_grad_(True)
+    loss = NF.l1_loss_mean(a1, b) * 3.0
+    loss.backward()
+    a2 = a.clone().requires_grad_(True)
+    ref = torch.nn.functional.l1_loss(a2.float(), b.float()) * 3.0
+    ref.backward()
+    assert loss.dtype == torch.float32 and loss.dim() == 0
+    assert abs(float(loss) - float(ref)) <= 2e-6 * max(1.0, abs(float(ref)))
+    assert a1.grad.dtype == torch.bfloat16 and a1.grad.stride() == a.stride()
+    assert torch.equal(a1.grad, a2.grad)                  # both are sign * (3 / n) rounded to bf16 once
+    # gradient with respect to the second argument
+    b3 = b.clone().requires_grad_(True)
+    NF.l1_loss_mean(a, b3).backward()
+    b4 = b.clone().requires_grad_(True)
+    torch.nn.functional.l1_loss(a.float(), b4.float()).backward()
+    assert torch.equal(b3.grad, b4.grad)
+
+
+def test_l1_loss_mean_other_inputs_take_the_torch_expression():
+    from imaginaire_b200 import functional as NF
+    dev = torch.device('cuda:0')
+    a = torch.randn(2, 3, 4, 5, device=dev)
+    b = torch.randn(2, 3, 4, 5, device=dev)
+    assert torch.equal(NF.l1_loss_mean(a, b), torch.nn.functional.l1_loss(a, b))
+    ab = a.bfloat16()
+    bb = b.bfloat16().contiguous(memory_format=torch.channels_last)      # layouts differ
+    assert torch.equal(NF.l1_loss_mean(ab, bb), torch.nn.functional.l1_loss(ab.float(), bb.float()))
+

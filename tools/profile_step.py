@@ -21,11 +21,23 @@ data = {k: v.to(dev) for k, v in bench.synthetic_batch(cfg, int(sys.argv[1]) if 
 for _ in range(2):
     trainer.step(dict(data))
 torch.cuda.synchronize()
-with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+ATEN = bool(os.environ.get('ATEN'))     # ATEN=1: also list the ATen ops by their own kernel time, with shapes and call sites
+with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], record_shapes=ATEN, with_stack=ATEN) as prof:
     trainer.step(dict(data))
     torch.cuda.synchronize()
 if rank != 0:
     sys.exit(0)
+if ATEN:
+    ops_rows = []
+    for e in prof.key_averages(group_by_input_shape=True, group_by_stack_n=6):
+        t = getattr(e, 'self_device_time_total', 0)
+        if e.key.startswith('aten::') and t > 0:
+            where = [f for f in e.stack if 'imaginaire_b200' in f or 'bench.py' in f]
+            ops_rows.append((t, e.count, e.key, str(e.input_shapes)[:90], (where[0] if where else (e.stack[0] if e.stack else ''))[-90:]))
+    ops_rows.sort(reverse=True)
+    print('ATen ops by own kernel time: %.1f ms total' % (sum(r[0] for r in ops_rows) / 1e3))
+    for t, c, k, shp, where in ops_rows[:int(os.environ.get('TOP', 45))]:
+        print('%7.3f ms x%-4d %-28s %-90s %s' % (t / 1e3, c, k, shp, where))
 rows = []
 for e in prof.key_averages():
     t = getattr(e, 'device_time_total', None)
