@@ -220,6 +220,83 @@ inline int grid_for(long total, int threads) {
     return (int)(b < 1 ? 1 : (b > cap ? cap : b));
 }
 
+// ------------------------------------------------------------------ 2x2 / stride-2 max pooling
+// ref: the perceptual loss' VGG-19 (torchvision layout: nn.MaxPool2d(2, 2) between the conv
+// stages, imaginaire/losses/perceptual.py:175-192 (torchvision vgg19 .features: MaxPool2d(2, 2) at indices 4, 9, 18, 27)).  NHWC bf16, one thread per output pixel and
+// 8-channel group.  ATen's kernel also writes int64 argmax indices (8 B per output element); here
+// the backward recomputes the argmax from the saved input: the first of (0,0), (0,1), (1,0), (1,1)
+// that equals the window maximum takes the gradient, as in ATen.  Floor mode: an odd last row /
+// column is not pooled and gets a zero gradient.
+__device__ __forceinline__ uint32_t bf16x2_max_nan(uint32_t a, uint32_t b) {
+    const __nv_bfloat162 r = __hmax2_nan(*reinterpret_cast<const __nv_bfloat162*>(&a), *reinterpret_cast<const __nv_bfloat162*>(&b));
+    return *reinterpret_cast<const uint32_t*>(&r);
+}
+__device__ __forceinline__ uint4 max4_u4(const uint4& a, const uint4& b, const uint4& c, const uint4& d) {
+    uint4 r;
+    r.x = bf16x2_max_nan(bf16x2_max_nan(a.x, b.x), bf16x2_max_nan(c.x, d.x));
+    r.y = bf16x2_max_nan(bf16x2_max_nan(a.y, b.y), bf16x2_max_nan(c.y, d.y));
+    r.z = bf16x2_max_nan(bf16x2_max_nan(a.z, b.z), bf16x2_max_nan(c.z, d.z));
+    r.w = bf16x2_max_nan(bf16x2_max_nan(a.w, b.w), bf16x2_max_nan(c.w, d.w));
+    return r;
+}
+
+__global__ void __launch_bounds__(256, 4)
+maxpool2x2_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, int N, int H, int W, int cg) {
+    const int Ho = H / 2, Wo = W / 2;
+    const long total = (long)N * Ho * Wo * cg;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int c8 = (int)(i % cg);
+        long p = i / cg;
+        const int x = (int)(p % Wo); p /= Wo;
+        const int y = (int)(p % Ho);
+        const int n = (int)(p / Ho);
+        const uint4* q = src + (((size_t)n * H + 2 * y) * W + 2 * x) * cg + c8;
+        const uint4 a = imx::ldg_stream(q), b = imx::ldg_stream(q + cg);
+        const uint4 c = imx::ldg_stream(q + (size_t)W * cg), d = imx::ldg_stream(q + (size_t)W * cg + cg);
+        imx::stg_stream(dst + i, max4_u4(a, b, c, d));
+    }
+}
+
+// 16-bit lanes of `v` equal to the lanes of `m` and not yet taken -> gradient lanes of g, else 0;
+// `taken` accumulates the lanes already routed (0xffff per lane).
+__device__ __forceinline__ uint32_t route2(uint32_t v, uint32_t m, uint32_t g, uint32_t& taken) {
+    // compare as floats so that -0 == +0, like ATen's value comparison
+    const bool lo = imx::bf16_lo(v) == imx::bf16_lo(m), hi = imx::bf16_hi(v) == imx::bf16_hi(m);
+    uint32_t mask = (lo ? 0x0000ffffu : 0u) | (hi ? 0xffff0000u : 0u);
+    mask &= ~taken;
+    taken |= mask;
+    return g & mask;
+}
+__device__ __forceinline__ uint4 route8(const uint4& v, const uint4& m, const uint4& g, uint4& taken) {
+    return make_uint4(route2(v.x, m.x, g.x, taken.x), route2(v.y, m.y, g.y, taken.y),
+                      route2(v.z, m.z, g.z, taken.z), route2(v.w, m.w, g.w, taken.w));
+}
+
+__global__ void __launch_bounds__(256, 4)
+maxpool2x2_bwd_kernel(const uint4* __restrict__ src, const uint4* __restrict__ gout, uint4* __restrict__ gsrc,
+                      int N, int H, int W, int cg) {
+    const int Ho = H / 2, Wo = W / 2;
+    const long total = (long)N * Ho * Wo * cg;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int c8 = (int)(i % cg);
+        long p = i / cg;
+        const int x = (int)(p % Wo); p /= Wo;
+        const int y = (int)(p % Ho);
+        const int n = (int)(p / Ho);
+        const size_t o = (((size_t)n * H + 2 * y) * W + 2 * x) * cg + c8;
+        const size_t row = (size_t)W * cg;
+        const uint4 a = imx::ldg_stream(src + o), b = imx::ldg_stream(src + o + cg);
+        const uint4 c = imx::ldg_stream(src + o + row), d = imx::ldg_stream(src + o + row + cg);
+        const uint4 g = imx::ldg_stream(gout + i);
+        const uint4 m = max4_u4(a, b, c, d);
+        uint4 taken = make_uint4(0, 0, 0, 0);
+        imx::stg_stream(gsrc + o, route8(a, m, g, taken));
+        imx::stg_stream(gsrc + o + cg, route8(b, m, g, taken));
+        imx::stg_stream(gsrc + o + row, route8(c, m, g, taken));
+        imx::stg_stream(gsrc + o + row + cg, route8(d, m, g, taken));
+    }
+}
+
 }  // namespace
 
 extern "C" int imx_nearest_resize_nchw_f32_to_nhwc_bf16(const float* src, imx_bf16* dst,
@@ -379,6 +456,28 @@ extern "C" int imx_bilinear_up2x_bwd_nhwc_bf16(const imx_bf16* grad_out, imx_bf1
     bilinear_up2x_bwd_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<const uint4*>(grad_out), reinterpret_cast<uint4*>(grad_src), N, h, w, C / 8);
     return imx::check_launch("bilinear_up2x_bwd");
+}
+
+extern "C" int imx_maxpool2x2_nhwc_bf16(const imx_bf16* src, imx_bf16* dst, int N, int H, int W, int C, imx_stream_t stream) {
+    IMX_REQUIRE(src && dst, "maxpool2x2: null pointer");
+    IMX_REQUIRE(N >= 0 && H >= 0 && W >= 0 && C >= 0 && C % 8 == 0, "maxpool2x2: bad size (C %% 8 must be 0)");
+    const long total = (long)N * (H / 2) * (W / 2) * (C / 8);
+    if (total == 0) return IMX_OK;
+    maxpool2x2_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const uint4*>(src), reinterpret_cast<uint4*>(dst), N, H, W, C / 8);
+    return imx::check_launch("maxpool2x2");
+}
+
+extern "C" int imx_maxpool2x2_bwd_nhwc_bf16(const imx_bf16* src, const imx_bf16* grad_out, imx_bf16* grad_src,
+                                            int N, int H, int W, int C, imx_stream_t stream) {
+    IMX_REQUIRE(src && grad_out && grad_src, "maxpool2x2_bwd: null pointer");
+    IMX_REQUIRE(N >= 0 && H >= 0 && W >= 0 && C >= 0 && C % 8 == 0, "maxpool2x2_bwd: bad size (C %% 8 must be 0)");
+    const long total = (long)N * (H / 2) * (W / 2) * (C / 8);
+    if (total == 0) return IMX_OK;
+    maxpool2x2_bwd_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const uint4*>(src), reinterpret_cast<const uint4*>(grad_out), reinterpret_cast<uint4*>(grad_src),
+        N, H, W, C / 8);
+    return imx::check_launch("maxpool2x2_bwd");
 }
 
 extern "C" int imx_nchw_f32_to_nhwc_bf16(const float* src, imx_bf16* dst, int N, int C, int H, int W,

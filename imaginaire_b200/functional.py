@@ -481,3 +481,28 @@ def l1_loss_mean(a, b):
         return _L1Mean.apply(a, b)
     return torch.nn.functional.l1_loss(a.float(), b.float())
 
+
+# ------------------------------------------------------------------ 2x2 max pooling (VGG)
+
+class _MaxPool2x2(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        ctx.save_for_backward(x)
+        return ops.maxpool2x2(x)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, = ctx.saved_tensors
+        return ops.maxpool2x2_bwd(x, dy.contiguous(memory_format=torch.channels_last))
+
+
+def max_pool2x2(x):
+    """``F.max_pool2d(x, kernel_size=2, stride=2)``.  ref: the MaxPool2d(2, 2) stages of the perceptual
+    loss' VGG-19 (imaginaire/losses/perceptual.py:175-192).  NHWC bf16 CUDA tensors with C % 8 == 0
+    take the native kernels (no int64 index tensor; the backward recomputes the argmax); anything
+    else goes through torch."""
+    if (x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 4 and x.shape[1] % 8 == 0
+            and x.is_contiguous(memory_format=torch.channels_last) and x.numel() > 0):
+        return _MaxPool2x2.apply(x)
+    return torch.nn.functional.max_pool2d(x, kernel_size=2, stride=2)
+

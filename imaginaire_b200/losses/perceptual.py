@@ -42,7 +42,7 @@ class _VGG19Features(nn.Module):
         out = {}
         for name, block in zip(self.names, self.blocks):
             if name == 'pool':
-                x = F.max_pool2d(x, kernel_size=2, stride=2)
+                x = NF.max_pool2x2(x)
             else:
                 x = block.forward_native(x)
                 if name in self.wanted:

@@ -298,6 +298,24 @@ def act_bwd_bias(dy, y, act, want_bias_grad):
     return dx, bg
 
 
+def maxpool2x2(x):
+    """2x2 / stride-2 max pooling of an NHWC bf16 tensor (floor mode)."""
+    _req_cuda(x); _req_nhwc(x, 'x')
+    n, c, h, w = x.shape
+    y = empty_nhwc(n, c, h // 2, w // 2, x.device)
+    _C.lib().call('imx_maxpool2x2_nhwc_bf16', _ptr(x), _ptr(y), n, h, w, c, _stream())
+    return y
+
+
+def maxpool2x2_bwd(x, dy):
+    """Gradient of maxpool2x2 with respect to x (argmax recomputed from x)."""
+    _req_cuda(x, dy); _req_nhwc(x, 'x'); _req_nhwc(dy, 'dy')
+    n, c, h, w = x.shape
+    dx = (torch.zeros if (h % 2 or w % 2) else torch.empty)((n, h, w, c), dtype=torch.bfloat16, device=x.device).permute(0, 3, 1, 2)
+    _C.lib().call('imx_maxpool2x2_bwd_nhwc_bf16', _ptr(x), _ptr(dy), _ptr(dx), n, h, w, c, _stream())
+    return dx
+
+
 def _same_dense_layout(a, b):
     return (a.shape == b.shape and a.stride() == b.stride()
             and (a.is_contiguous() or (a.dim() == 4 and a.is_contiguous(memory_format=torch.channels_last))))

@@ -109,6 +109,16 @@ IMX_API int imx_bilinear_up2x_add_nhwc_bf16(const imx_bf16* src, const imx_bf16*
 IMX_API int imx_bilinear_up2x_bwd_nhwc_bf16(const imx_bf16* grad_out, imx_bf16* grad_src,
                                     int N, int h, int w, int C, imx_stream_t stream);
 
+/* 2x2 / stride-2 max pooling, NHWC bf16 (C % 8 == 0), floor mode: src N x H x W x C ->
+ * dst N x H/2 x W/2 x C; NaN propagates.  The backward recomputes the argmax from src (no index
+ * tensor): the first of (0,0), (0,1), (1,0), (1,1) equal to the window maximum takes grad_out;
+ * only the pooled 2*(H/2) x 2*(W/2) region of grad_src is written (an odd last row / column must
+ * be zeroed by the caller).
+ * ref: nn.MaxPool2d(2, 2) of the perceptual loss' VGG-19, imaginaire/losses/perceptual.py:175-192 (torchvision vgg19 .features: MaxPool2d(2, 2) at indices 4, 9, 18, 27) */
+IMX_API int imx_maxpool2x2_nhwc_bf16(const imx_bf16* src, imx_bf16* dst, int N, int H, int W, int C, imx_stream_t stream);
+IMX_API int imx_maxpool2x2_bwd_nhwc_bf16(const imx_bf16* src, const imx_bf16* grad_out, imx_bf16* grad_src,
+                                 int N, int H, int W, int C, imx_stream_t stream);
+
 /* Mean-absolute-difference loss on bf16 feature maps (flat arrays of n elements; a, b and grad
  * dense, one shared memory layout, 16-byte aligned).
  *   imx_l1_abs_sum_bf16 :  *sum += sum_i |float(a[i]) - float(b[i])|   (fp32; the caller zeroes *sum

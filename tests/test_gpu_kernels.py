@@ -583,7 +583,8 @@ def test_l1_loss_mean_vs_torch(shape, nhwc):
     ref = torch.nn.functional.l1_loss(a2.float(), b.float()) * 3.0
     ref.backward()
     assert loss.dtype == torch.float32 and loss.dim() == 0
-    assert abs(float(loss) - float(ref)) <= 2e-6 * max(1.0, abs(float(ref)))
+    # fp32 sums in two different orders (atomics across CTAs here, ATen's tree there)
+    assert abs(float(loss) - float(ref)) <= 2e-5 * max(1.0, abs(float(ref)))
     assert a1.grad.dtype == torch.bfloat16 and a1.grad.stride() == a.stride()
     assert torch.equal(a1.grad, a2.grad)                  # both are sign * (3 / n) rounded to bf16 once
     # gradient with respect to the second argument
@@ -603,4 +604,23 @@ def test_l1_loss_mean_other_inputs_take_the_torch_expression():
     ab = a.bfloat16()
     bb = b.bfloat16().contiguous(memory_format=torch.channels_last)      # layouts differ
     assert torch.equal(NF.l1_loss_mean(ab, bb), torch.nn.functional.l1_loss(ab.float(), bb.float()))
+
+
+@pytest.mark.parametrize('shape', [(2, 16, 8, 12), (1, 8, 2, 2), (3, 64, 7, 9), (2, 128, 32, 48), (1, 8, 3, 5)])
+def test_max_pool2x2_vs_torch(shape):
+    """Native NHWC bf16 2x2 max pooling: values and gradient routing (ties -> first maximum) as ATen."""
+    from imaginaire_b200 import functional as NF
+    torch.manual_seed(5)
+    dev = torch.device('cuda:0')
+    x = torch.randn(*shape, device=dev).relu_().bfloat16().contiguous(memory_format=torch.channels_last)   # ReLU: many tied zeros
+    x1 = x.clone().requires_grad_(True)
+    y = NF.max_pool2x2(x1)
+    x2 = x.clone().requires_grad_(True)
+    ref = torch.nn.functional.max_pool2d(x2, kernel_size=2, stride=2)
+    assert y.shape == ref.shape and torch.equal(y, ref)
+    if y.numel():
+        g = torch.randn_like(ref)
+        y.backward(g)
+        ref.backward(g)
+        assert torch.equal(x1.grad, x2.grad)
 

@@ -22,14 +22,16 @@ for _ in range(2):
     trainer.step(dict(data))
 torch.cuda.synchronize()
 ATEN = bool(os.environ.get('ATEN'))     # ATEN=1: also list the ATen ops by their own kernel time, with shapes and call sites
-with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], record_shapes=ATEN, with_stack=ATEN) as prof:
+_xc = torch._C._profiler._ExperimentalConfig(verbose=True) if ATEN else None     # needed for Python stacks in key_averages
+with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], record_shapes=ATEN, with_stack=ATEN,
+             experimental_config=_xc) as prof:
     trainer.step(dict(data))
     torch.cuda.synchronize()
 if rank != 0:
     sys.exit(0)
 if ATEN:
     ops_rows = []
-    for e in prof.key_averages(group_by_input_shape=True, group_by_stack_n=6):
+    for e in prof.key_averages(group_by_input_shape=True, group_by_stack_n=12):
         t = getattr(e, 'self_device_time_total', 0)
         if e.key.startswith('aten::') and t > 0:
             where = [f for f in e.stack if 'imaginaire_b200' in f or 'bench.py' in f]
