@@ -291,7 +291,9 @@ def run_ours(args):
     h2d_bytes = sum(v.numel() * v.element_size() for v in host.values())
 
     def one_step(data):
-        return trainer.step(dict(data))
+        # Fresh tensor objects every step (no copy): per-batch caches that the layers keep on the input
+        # tensors (resized / pooled label maps) are rebuilt each step, as with a new batch in training.
+        return trainer.step({k: v.detach() for k, v in data.items()})
 
     def barrier():
         torch.cuda.synchronize()

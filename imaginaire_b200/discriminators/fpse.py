@@ -16,6 +16,23 @@ from .. import functional as NF
 from ..layers import Conv2dBlock
 
 
+def _pooled_label_maps(segmaps, levels):
+    """NHWC bf16 label maps average-pooled by 4, 8, ... (one per pyramid level).  The discriminator
+    sees the same label tensor for the real and the fake pass, in the D and in the G update: the
+    pyramid is kept on the tensor object (it dies with the batch) and rebuilt if the tensor changes."""
+    cache = segmaps.__dict__.get('_imx_fpse_pooled') if not segmaps.requires_grad else None
+    if cache is not None and cache[0] == segmaps._version and len(cache[1]) == levels:
+        return cache[1]
+    pooled = F.avg_pool2d(segmaps.float(), kernel_size=2, stride=2)
+    maps = []
+    for _ in range(levels):
+        pooled = F.avg_pool2d(pooled, kernel_size=2, stride=2)
+        maps.append(NF.to_nhwc(pooled))
+    if not segmaps.requires_grad:
+        segmaps.__dict__['_imx_fpse_pooled'] = (segmaps._version, maps)
+    return maps
+
+
 class FPSEDiscriminator(nn.Module):
     def __init__(self, num_input_channels, num_labels, num_filters, kernel_size, weight_norm_type,
                  activation_norm_type):
@@ -64,11 +81,9 @@ class FPSEDiscriminator(nn.Module):
         # power iteration) is evaluated once per forward, as in the reference.
         conv = self.embedding.layers['conv']
         weight = conv.effective_weight()
-        pooled = F.avg_pool2d(segmaps.float(), kernel_size=2, stride=2)
         preds = []
-        for feat in feats:
-            pooled = F.avg_pool2d(pooled, kernel_size=2, stride=2)
-            segemb = NF.conv2d(NF.to_nhwc(pooled), weight, conv.bias, None, 1, 0)
+        for feat, pooled in zip(feats, _pooled_label_maps(segmaps, len(feats))):
+            segemb = NF.conv2d(pooled, weight, conv.bias, None, 1, 0)
             pred = self.output(feat) + torch.mul(segemb, self.seg(feat)).sum(dim=1, keepdim=True)
             preds.append(pred)
         return tuple(preds)
