@@ -71,14 +71,16 @@ def test_frozen_identity_affine_takes_the_affine_free_kernels():
     m.norm.weight.requires_grad_(True)            # same values through the affine instantiation
     assert norm_state(m.norm).weight is not None
     y2 = NF.to_nchw(m.forward_fused(x.clone().requires_grad_(True), label, act=ops.ACT_LRELU))
-    assert torch.equal(y1, y2)
+    # same arithmetic (fmaf(xn, 1, 0) == xn), but the batch statistics are summed with atomics whose order
+    # differs from run to run: a last-bit difference in mean / rstd may move a bf16 output by one ulp
+    assert torch.allclose(y1, y2, rtol=2e-2, atol=2e-2)
     m.norm.weight.requires_grad_(False)
     with torch.no_grad():
         m.norm.weight.fill_(2.0)
         m.norm.bias.fill_(0.5)
     assert norm_state(m.norm).weight is not None   # frozen but no longer the identity
     y3 = NF.to_nchw(m.forward_fused(x.clone().requires_grad_(True), label, act=ops.ACT_LRELU))
-    assert not torch.allclose(y1, y3)
+    assert float((y1 - y3).abs().mean()) > 0.1
 
 
 def _make_res_block(d, cin, cout):
