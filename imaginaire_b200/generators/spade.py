@@ -211,9 +211,12 @@ class SPADEGenerator(nn.Module):
     def _mid(self, name):
         return getattr(self, self._mid_prefix + name)
 
-    def _run(self, blocks, x, seg, z):
+    def _run(self, blocks, x, seg, z, final_act=None):
         """Runs a chain of blocks; every block is told which statistics its consumer needs so
-        its last convolution can emit them from the epilogue."""
+        its last convolution can emit them from the epilogue.  final_act: activation of the chain's
+        consumer, applied in the epilogue of the last residual block's final convolution."""
+        if final_act is not None:
+            blocks[-1][0].post_act = final_act
         for k, (blk, kind) in enumerate(blocks):
             nxt = blocks[k + 1][0] if k + 1 < len(blocks) else None
             mode = None
@@ -251,11 +254,20 @@ class SPADEGenerator(nn.Module):
         x = up(x)
         x = self._run([(self.up_1a, 'res'), (self._mid('up_1a'), mid_kind), (self.up_1b, 'res')], x, seg, z)
         x = up(x)
-        x = self._run([(self.up_2a, 'res'), (self._mid('up_2a'), mid_kind), (self.up_2b, 'res')], x, seg, z)
-        x = up(x)
         c = self.image_channels
+        # 256-pixel output: the to-RGB block (LeakyReLU -> conv) is the only consumer of up_2b's
+        # output, and LeakyReLU commutes with the nearest x2 upsampling in between, so it is applied
+        # in the epilogue of up_2b's last convolution (at a quarter of the pixels) instead of as a
+        # pass of its own over the 256-channel full-resolution tensor.
+        rgb_act = self.conv_img256.leading_act_code() if self.out_image_small_side_size == 256 else None
+        if rgb_act is not None and not (isinstance(self.up_2b, Res2dBlock) and self.up_2b._native
+                                        and self.up_2b.conv_block_1.ends_with_plain_conv()):
+            rgb_act = None
+        x = self._run([(self.up_2a, 'res'), (self._mid('up_2a'), mid_kind), (self.up_2b, 'res')], x, seg, z,
+                      final_act=rgb_act)
+        x = up(x)
         if self.out_image_small_side_size == 256:
-            out = NF.to_nchw(self.conv_img256.forward_native(x), c, apply_tanh=True)
+            out = NF.to_nchw(self.conv_img256.forward_native(x, skip_first_act=rgb_act is not None), c, apply_tanh=True)
         else:
             x256 = up(self.conv_img256.forward_native(x))
             x = self._run([(self.up_3a, 'res'), (self.up_3b, 'res')], x, seg, z)

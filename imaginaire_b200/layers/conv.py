@@ -198,9 +198,15 @@ class _BaseConvBlock(nn.Module):
                 x = layer(x)
         return x
 
-    def forward_native(self, x, cond_inputs=(), kw_cond_inputs=None, residual=None, stats_mode=None):
+    def forward_native(self, x, cond_inputs=(), kw_cond_inputs=None, residual=None, stats_mode=None,
+                       post_act=ops.ACT_NONE, skip_first_act=False):
         """2-D forward on the native kernels.
 
+        post_act: activation of the CONSUMER block applied in the epilogue of this block's last
+            convolution (after bias and residual); the consumer is then run with skip_first_act=True.
+            Only honoured when the convolution is the block's last operation and has no activation
+            of its own (callers check with ``ends_with_plain_conv``).
+        skip_first_act: the block's leading activation was already applied by the producer.
         residual: NHWC bf16 tensor added in the epilogue of the block's convolution.
         stats_mode: 'batch' / 'instance' -> the convolution's epilogue also produces the
             statistics that the next normalisation layer needs (only honoured when the
@@ -219,6 +225,10 @@ class _BaseConvBlock(nn.Module):
                 fused_act = _act_code(nxt[1])
             if name == 'conv':
                 last = (i + (2 if fused_act else 1)) >= len(items)
+                if last and fused_act == ops.ACT_NONE and post_act != ops.ACT_NONE and stats_mode is None:
+                    fused_act = post_act
+                    post_act = ops.ACT_NONE
+                    i -= 1          # nothing of this block's own is consumed by the borrowed activation
                 x = layer.native_forward(x, act=fused_act, residual=residual if last else None,
                                          stats_mode=stats_mode if last else None)
                 if last:
@@ -227,13 +237,28 @@ class _BaseConvBlock(nn.Module):
                 from .activation_norm import apply_norm_layer
                 x = apply_norm_layer(layer, x, cond_inputs, kw_cond_inputs, fused_act)
             elif name == 'nonlinearity':
-                x = self._standalone_act(layer, x)
+                if not (skip_first_act and i == 0):
+                    x = self._standalone_act(layer, x)
             else:   # noise
                 x = layer(x)
             i += 2 if fused_act else 1
         if residual is not None:
             x = x + residual
+        if post_act != ops.ACT_NONE:     # could not ride in an epilogue: apply it here
+            x = F.leaky_relu(x, 0.2) if post_act == ops.ACT_LRELU else F.relu(x)
         return x
+
+    def ends_with_plain_conv(self):
+        """True when the block's last operation is its convolution (so a consumer's activation can
+        ride in that convolution's epilogue)."""
+        return len(self.layers) > 0 and list(self.layers.keys())[-1] == 'conv'
+
+    def leading_act_code(self):
+        """Kernel code of the block's leading activation, or None if it does not start with a fusable one."""
+        if len(self.layers) == 0:
+            return None
+        name, layer = next(iter(self.layers.items()))
+        return _act_code(layer) if name == 'nonlinearity' else None
 
     @staticmethod
     def _standalone_act(layer, x):

@@ -106,8 +106,9 @@ class _BaseResBlock(nn.Module):
             if self.learn_shortcut else x
         mid_stats = _inner_stats_mode(self.conv_block_1)
         dx = self.conv_block_0.forward_native(x, cond_inputs, kw_cond_inputs, stats_mode=mid_stats)
+        post_act, self.post_act = getattr(self, 'post_act', ops.ACT_NONE), ops.ACT_NONE   # one-shot, set by the caller
         return self.conv_block_1.forward_native(dx, cond_inputs, kw_cond_inputs, residual=shortcut,
-                                                stats_mode=self.emit_stats)
+                                                stats_mode=self.emit_stats, post_act=post_act)
 
     def forward(self, x, *cond_inputs, do_checkpoint=False, **kw_cond_inputs):
         if self._native and not do_checkpoint:
