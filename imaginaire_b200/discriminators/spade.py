@@ -8,6 +8,7 @@ Conv2dBlock.
 import torch
 from torch import nn
 
+from .. import functional as NF
 from ..layers.conv import prefetch_spectral_norms
 from ..utils.data import get_paired_input_image_channel_number, get_paired_input_label_channel_number
 from .fpse import FPSEDiscriminator
@@ -45,7 +46,7 @@ class Discriminator(nn.Module):
             outputs.append(out)
             features.append(feats)
             if i + 1 < len(self.discriminators):   # the reference also resizes after the last one; nothing reads it
-                input_x = nn.functional.interpolate(input_x, scale_factor=0.5, mode='bilinear', align_corners=True)
+                input_x = NF.bilinear_half_align_corners(input_x)   # interpolate(scale_factor=0.5, bilinear, align_corners=True)
         return outputs, features
 
     def forward(self, data, net_G_output):

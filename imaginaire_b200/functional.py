@@ -5,6 +5,8 @@ hand-written kernels of libimx_kernels.so; PyTorch only keeps the graph.
 Activations are bf16 NHWC (channels_last) tensors with the channel count padded
 to a multiple of 8 (padding channels are zero).
 """
+import math
+
 import torch
 import torch.distributed as dist
 
@@ -505,4 +507,31 @@ def max_pool2x2(x):
             and x.is_contiguous(memory_format=torch.channels_last) and x.numel() > 0):
         return _MaxPool2x2.apply(x)
     return torch.nn.functional.max_pool2d(x, kernel_size=2, stride=2)
+
+
+# ------------------------------------------------------------------ 0.5x bilinear (discriminator input pyramid)
+
+class _BilinearHalfAC(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, ho, wo):
+        ctx.in_size = tuple(x.shape)
+        ctx.out_size = (ho, wo)
+        return ops.bilinear_resize_ac(x, ho, wo)
+
+    @staticmethod
+    def backward(ctx, g):
+        # the (small) gradient goes through ATen's own backward kernel
+        return torch.ops.aten.upsample_bilinear2d_backward(g.contiguous(), list(ctx.out_size), list(ctx.in_size), True,
+                                                           None, None), None, None
+
+
+def bilinear_half_align_corners(x):
+    """``F.interpolate(x, scale_factor=0.5, mode='bilinear', align_corners=True)``.
+    ref: imaginaire/discriminators/spade.py:86-88.  Contiguous NCHW fp32 CUDA tensors take the native
+    forward kernel (ATen's arithmetic, one thread per output element); others go through torch."""
+    if x.is_cuda and x.dtype == torch.float32 and x.dim() == 4 and x.is_contiguous() and x.numel() > 0:
+        ho, wo = int(math.floor(x.shape[2] * 0.5)), int(math.floor(x.shape[3] * 0.5))
+        if ho > 0 and wo > 0:
+            return _BilinearHalfAC.apply(x, ho, wo)
+    return torch.nn.functional.interpolate(x, scale_factor=0.5, mode='bilinear', align_corners=True)
 

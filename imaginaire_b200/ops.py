@@ -298,6 +298,17 @@ def act_bwd_bias(dy, y, act, want_bias_grad):
     return dx, bg
 
 
+def bilinear_resize_ac(x, ho, wo):
+    """F.interpolate(x, size=(ho, wo), mode='bilinear', align_corners=True) for a contiguous NCHW fp32 tensor."""
+    _req_cuda(x)
+    if x.dtype != torch.float32 or x.dim() != 4 or not x.is_contiguous():
+        raise ValueError('bilinear_resize_ac: contiguous NCHW fp32 tensor expected')
+    n, c, h, w = x.shape
+    y = torch.empty((n, c, ho, wo), dtype=torch.float32, device=x.device)
+    _C.lib().call('imx_bilinear_resize_ac_nchw_f32', _ptr(x), _ptr(y), n * c, h, w, ho, wo, _stream())
+    return y
+
+
 def maxpool2x2(x):
     """2x2 / stride-2 max pooling of an NHWC bf16 tensor (floor mode)."""
     _req_cuda(x); _req_nhwc(x, 'x')

@@ -109,6 +109,13 @@ IMX_API int imx_bilinear_up2x_add_nhwc_bf16(const imx_bf16* src, const imx_bf16*
 IMX_API int imx_bilinear_up2x_bwd_nhwc_bf16(const imx_bf16* grad_out, imx_bf16* grad_src,
                                     int N, int h, int w, int C, imx_stream_t stream);
 
+/* Bilinear resize with align_corners = True of `planes` (= N * C) contiguous H x W fp32 planes to
+ * Ho x Wo (ATen's upsample_bilinear2d arithmetic: source index = dst * (in - 1) / (out - 1)).
+ * ref: the 0.5x input pyramid of the multi-resolution patch discriminator,
+ *      imaginaire/discriminators/spade.py:86-88 (multires_patch.py:169-171). */
+IMX_API int imx_bilinear_resize_ac_nchw_f32(const float* src, float* dst, int64_t planes, int H, int W, int Ho, int Wo,
+                                    imx_stream_t stream);
+
 /* 2x2 / stride-2 max pooling, NHWC bf16 (C % 8 == 0), floor mode: src N x H x W x C ->
  * dst N x H/2 x W/2 x C; NaN propagates.  The backward recomputes the argmax from src (no index
  * tensor): the first of (0,0), (0,1), (1,0), (1,1) equal to the window maximum takes grad_out;

@@ -624,3 +624,22 @@ def test_max_pool2x2_vs_torch(shape):
         ref.backward(g)
         assert torch.equal(x1.grad, x2.grad)
 
+
+@pytest.mark.parametrize('shape', [(2, 5, 16, 24), (1, 38, 64, 96), (3, 1, 7, 9), (2, 3, 2, 2), (1, 2, 3, 2)])
+def test_bilinear_half_align_corners_vs_torch(shape):
+    """The discriminator pyramid's 0.5x bilinear resize (align_corners=True) against F.interpolate."""
+    from imaginaire_b200 import functional as NF
+    torch.manual_seed(9)
+    dev = torch.device('cuda:0')
+    x = torch.randn(*shape, device=dev)
+    x1 = x.clone().requires_grad_(True)
+    y = NF.bilinear_half_align_corners(x1)
+    x2 = x.clone().requires_grad_(True)
+    ref = torch.nn.functional.interpolate(x2, scale_factor=0.5, mode='bilinear', align_corners=True)
+    assert y.shape == ref.shape
+    assert torch.allclose(y, ref, rtol=1e-6, atol=1e-6)          # same formula; only FMA contraction may differ
+    g = torch.randn_like(ref)
+    y.backward(g)
+    ref.backward(g)
+    assert torch.allclose(x1.grad, x2.grad, rtol=1e-6, atol=1e-6)
+
