@@ -119,6 +119,55 @@ inline int l1_blocks(long n8) {
     return (int)(b < 1 ? 1 : b);
 }
 
+// ------------------------------------------------------------------ per-pixel channel dot product
+// out[p] = sum_c a[p][c] * b[p][c] for NHWC bf16 tensors (the projection term of the FPSE
+// discriminator: (segmap embedding * feature).sum(dim=1), imaginaire/discriminators/fpse.py:125-127).
+// Through ATen this is a materialised product tensor plus a reduction forward and two broadcast
+// products backward.  One warp per pixel; fp32 accumulation, one rounding.
+__device__ __forceinline__ float dot8(const uint4& a, const uint4& b) {
+    float s = imx::bf16_lo(a.x) * imx::bf16_lo(b.x);
+    s = fmaf(imx::bf16_hi(a.x), imx::bf16_hi(b.x), s);
+    s = fmaf(imx::bf16_lo(a.y), imx::bf16_lo(b.y), s); s = fmaf(imx::bf16_hi(a.y), imx::bf16_hi(b.y), s);
+    s = fmaf(imx::bf16_lo(a.z), imx::bf16_lo(b.z), s); s = fmaf(imx::bf16_hi(a.z), imx::bf16_hi(b.z), s);
+    s = fmaf(imx::bf16_lo(a.w), imx::bf16_lo(b.w), s); s = fmaf(imx::bf16_hi(a.w), imx::bf16_hi(b.w), s);
+    return s;
+}
+
+__global__ void __launch_bounds__(kThreadsL)
+channel_dot_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, uint16_t* __restrict__ out, long pixels, int cg) {
+    const int lane = threadIdx.x & 31;
+    const long warps = (long)gridDim.x * (kThreadsL / 32);
+    for (long p = (long)blockIdx.x * (kThreadsL / 32) + (threadIdx.x >> 5); p < pixels; p += warps) {
+        float s = 0.0f;
+        for (int c8 = lane; c8 < cg; c8 += 32) s += dot8(imx::ldg_stream(a + p * cg + c8), imx::ldg_stream(b + p * cg + c8));
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+        if (lane == 0) out[p] = (uint16_t)(imx::pack_bf16(s, 0.0f) & 0xffffu);
+    }
+}
+
+__device__ __forceinline__ uint32_t scale2(uint32_t v, float g) {
+    return imx::pack_bf16(imx::bf16_lo(v) * g, imx::bf16_hi(v) * g);
+}
+
+// da[p][c] = g[p] * b[p][c],  db[p][c] = g[p] * a[p][c]   (either output may be NULL)
+__global__ void __launch_bounds__(kThreadsL)
+channel_dot_bwd_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, const uint16_t* __restrict__ g,
+                       uint4* __restrict__ da, uint4* __restrict__ db, long pixels, int cg) {
+    const long total = pixels * cg;
+    for (long i = (long)blockIdx.x * kThreadsL + threadIdx.x; i < total; i += (long)gridDim.x * kThreadsL) {
+        const float gv = __uint_as_float((uint32_t)g[i / cg] << 16);
+        if (da) {
+            const uint4 v = imx::ldg_stream(b + i);
+            imx::stg_stream(da + i, make_uint4(scale2(v.x, gv), scale2(v.y, gv), scale2(v.z, gv), scale2(v.w, gv)));
+        }
+        if (db) {
+            const uint4 v = imx::ldg_stream(a + i);
+            imx::stg_stream(db + i, make_uint4(scale2(v.x, gv), scale2(v.y, gv), scale2(v.z, gv), scale2(v.w, gv)));
+        }
+    }
+}
+
 }  // namespace
 
 extern "C" int imx_l1_abs_sum_bf16(const imx_bf16* a, const imx_bf16* b, int64_t n, float* sum, imx_stream_t stream) {
@@ -151,3 +200,30 @@ extern "C" int imx_l1_abs_grad_bf16(const imx_bf16* a, const imx_bf16* b, imx_bf
         upstream, denom);
     return imx::check_launch("l1_abs_grad");
 }
+
+extern "C" int imx_channel_dot_nhwc_bf16(const imx_bf16* a, const imx_bf16* b, imx_bf16* out, int64_t pixels, int C,
+                                         imx_stream_t stream) {
+    IMX_REQUIRE(pixels >= 0 && C >= 0 && C % 8 == 0, "channel_dot: bad size (C %% 8 must be 0)");
+    if (pixels == 0) return IMX_OK;
+    IMX_REQUIRE(a && b && out, "channel_dot: null pointer");
+    long blocks = (pixels + kThreadsL / 32 - 1) / (kThreadsL / 32);
+    if (blocks > 16L * imx::kNumSMs) blocks = 16L * imx::kNumSMs;
+    channel_dot_kernel<<<(int)blocks, kThreadsL, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const uint4*>(a), reinterpret_cast<const uint4*>(b), reinterpret_cast<uint16_t*>(out), (long)pixels, C / 8);
+    return imx::check_launch("channel_dot");
+}
+
+extern "C" int imx_channel_dot_bwd_nhwc_bf16(const imx_bf16* a, const imx_bf16* b, const imx_bf16* grad_out,
+                                             imx_bf16* grad_a, imx_bf16* grad_b, int64_t pixels, int C, imx_stream_t stream) {
+    IMX_REQUIRE(pixels >= 0 && C >= 0 && C % 8 == 0, "channel_dot_bwd: bad size (C %% 8 must be 0)");
+    if (pixels * C == 0 || (!grad_a && !grad_b)) return IMX_OK;
+    IMX_REQUIRE(a && b && grad_out, "channel_dot_bwd: null pointer");
+    const long total = (long)pixels * (C / 8);
+    long blocks = (total + kThreadsL - 1) / kThreadsL;
+    if (blocks > 16L * imx::kNumSMs) blocks = 16L * imx::kNumSMs;
+    channel_dot_bwd_kernel<<<(int)blocks, kThreadsL, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const uint4*>(a), reinterpret_cast<const uint4*>(b), reinterpret_cast<const uint16_t*>(grad_out),
+        reinterpret_cast<uint4*>(grad_a), reinterpret_cast<uint4*>(grad_b), (long)pixels, C / 8);
+    return imx::check_launch("channel_dot_bwd");
+}
+

@@ -84,6 +84,6 @@ class FPSEDiscriminator(nn.Module):
         preds = []
         for feat, pooled in zip(feats, _pooled_label_maps(segmaps, len(feats))):
             segemb = NF.conv2d(pooled, weight, conv.bias, None, 1, 0)
-            pred = self.output(feat) + torch.mul(segemb, self.seg(feat)).sum(dim=1, keepdim=True)
+            pred = self.output(feat) + NF.channel_dot(segemb, self.seg(feat))
             preds.append(pred)
         return tuple(preds)

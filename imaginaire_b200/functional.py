@@ -535,3 +535,29 @@ def bilinear_half_align_corners(x):
             return _BilinearHalfAC.apply(x, ho, wo)
     return torch.nn.functional.interpolate(x, scale_factor=0.5, mode='bilinear', align_corners=True)
 
+
+# ------------------------------------------------------------------ per-pixel channel dot (FPSE projection term)
+
+class _ChannelDot(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, a, b):
+        ctx.save_for_backward(a, b)
+        return ops.channel_dot(a, b)
+
+    @staticmethod
+    def backward(ctx, g):
+        a, b = ctx.saved_tensors
+        return ops.channel_dot_bwd(a, b, g.to(torch.bfloat16).contiguous(), ctx.needs_input_grad[0], ctx.needs_input_grad[1])
+
+
+def channel_dot(a, b):
+    """``torch.mul(a, b).sum(dim=1, keepdim=True)``.  ref: imaginaire/discriminators/fpse.py:125-127.
+    NHWC bf16 CUDA tensors of the same shape with C % 8 == 0 take one kernel each way (fp32
+    accumulation, no product tensor); anything else goes through torch."""
+    def ok(t):
+        return (t.is_cuda and t.dtype == torch.bfloat16 and t.dim() == 4 and t.shape[1] % 8 == 0
+                and t.is_contiguous(memory_format=torch.channels_last))
+    if a.shape == b.shape and ok(a) and ok(b) and a.numel() > 0:
+        return _ChannelDot.apply(a, b)
+    return torch.mul(a, b).sum(dim=1, keepdim=True)
+

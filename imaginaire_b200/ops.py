@@ -309,6 +309,25 @@ def bilinear_resize_ac(x, ho, wo):
     return y
 
 
+def channel_dot(a, b):
+    """(N, 1, H, W) bf16: sum over the channels of a * b for two NHWC bf16 tensors."""
+    _req_cuda(a, b); _req_nhwc(a, 'a'); _req_nhwc(b, 'b')
+    n, c, h, w = a.shape
+    out = torch.empty((n, 1, h, w), dtype=torch.bfloat16, device=a.device)
+    _C.lib().call('imx_channel_dot_nhwc_bf16', _ptr(a), _ptr(b), _ptr(out), n * h * w, c, _stream())
+    return out
+
+
+def channel_dot_bwd(a, b, g, want_a=True, want_b=True):
+    """Gradients of channel_dot: (g * b, g * a) as NHWC bf16 (None where not wanted); g: (N, 1, H, W) bf16 contiguous."""
+    _req_cuda(a, b, g)
+    n, c, h, w = a.shape
+    da = empty_nhwc(n, c, h, w, a.device) if want_a else None
+    db = empty_nhwc(n, c, h, w, a.device) if want_b else None
+    _C.lib().call('imx_channel_dot_bwd_nhwc_bf16', _ptr(a), _ptr(b), _ptr(g), _ptr(da), _ptr(db), n * h * w, c, _stream())
+    return da, db
+
+
 def maxpool2x2(x):
     """2x2 / stride-2 max pooling of an NHWC bf16 tensor (floor mode)."""
     _req_cuda(x); _req_nhwc(x, 'x')

@@ -139,6 +139,16 @@ IMX_API int imx_l1_abs_sum_bf16(const imx_bf16* a, const imx_bf16* b, int64_t n,
 IMX_API int imx_l1_abs_grad_bf16(const imx_bf16* a, const imx_bf16* b, imx_bf16* grad, int64_t n,
                          const float* upstream, float denom, imx_stream_t stream);
 
+/* Per-pixel dot product over the channels of two NHWC bf16 tensors (pixels x C, C % 8 == 0):
+ * out[p] = bf16(sum_c a[p][c] * b[p][c]) with fp32 accumulation, and its gradients
+ * grad_a[p][c] = grad_out[p] * b[p][c], grad_b[p][c] = grad_out[p] * a[p][c] (either may be NULL).
+ * ref: the projection term of the FPSE discriminator, torch.mul(segemb, seg).sum(dim=1, keepdim=True),
+ *      imaginaire/discriminators/fpse.py:125-127. */
+IMX_API int imx_channel_dot_nhwc_bf16(const imx_bf16* a, const imx_bf16* b, imx_bf16* out, int64_t pixels, int C,
+                              imx_stream_t stream);
+IMX_API int imx_channel_dot_bwd_nhwc_bf16(const imx_bf16* a, const imx_bf16* b, const imx_bf16* grad_out,
+                                  imx_bf16* grad_a, imx_bf16* grad_b, int64_t pixels, int C, imx_stream_t stream);
+
 /* NCHW fp32 -> NHWC bf16 (channels zero-padded to Cp) and back (first C of Cp). */
 IMX_API int imx_nchw_f32_to_nhwc_bf16(const float* src, imx_bf16* dst, int N, int C, int H, int W,
                               int Cp, imx_stream_t stream);

@@ -643,3 +643,23 @@ def test_bilinear_half_align_corners_vs_torch(shape):
     ref.backward(g)
     assert torch.allclose(x1.grad, x2.grad, rtol=1e-6, atol=1e-6)
 
+
+@pytest.mark.parametrize('shape', [(2, 16, 8, 12), (1, 8, 1, 3), (3, 256, 5, 7), (2, 264, 4, 4)])
+def test_channel_dot_vs_torch(shape):
+    """FPSE projection term: per-pixel dot over channels and its gradients against torch in fp32."""
+    from imaginaire_b200 import functional as NF
+    torch.manual_seed(13)
+    dev = torch.device('cuda:0')
+    a = torch.randn(*shape, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+    b = torch.randn(*shape, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+    a1, b1 = a.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    y = NF.channel_dot(a1, b1)
+    a2, b2 = a.float().requires_grad_(True), b.float().requires_grad_(True)
+    ref = torch.mul(a2, b2).sum(dim=1, keepdim=True)
+    assert y.shape == ref.shape and y.dtype == torch.bfloat16
+    assert H.rel_err(y.float(), ref) < 1e-2                      # one bf16 rounding of the fp32 sum
+    g = torch.randn_like(ref).bfloat16()
+    y.backward(g)
+    ref.backward(g.float())
+    assert H.rel_err(a1.grad.float(), a2.grad) < 1e-2 and H.rel_err(b1.grad.float(), b2.grad) < 1e-2
+
