@@ -455,6 +455,14 @@ def spade_gb_fused(hidden, w_gamma, w_beta, b_gamma, b_beta, x, ns, act, pad, in
                                       ns.per_instance, act)
 
 
+def _require_cuda(name, *ts):
+    """The helpers below keep a torch expression for CUDA tensors whose dtype / layout the native
+    kernels do not cover; there is no CPU path."""
+    for t in ts:
+        if not t.is_cuda:
+            raise RuntimeError('%s: CUDA tensors required (this build has no CPU path)' % name)
+
+
 # ------------------------------------------------------------------ feature-map L1 loss
 
 class _L1Mean(torch.autograd.Function):
@@ -478,6 +486,7 @@ def l1_loss_mean(a, b):
     imx_l1_abs_grad_bf16: 4 + 6 bytes per element instead of ~60 through ATen); the arithmetic is the
     same, |float(a) - float(b)| in fp32.  Anything else (fp32 inputs, mismatched layouts) goes
     through the torch expression."""
+    _require_cuda('l1_loss_mean', a, b)
     if (a.is_cuda and b.is_cuda and a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
             and ops._same_dense_layout(a, b) and a.numel() > 0):
         return _L1Mean.apply(a, b)
@@ -503,6 +512,7 @@ def max_pool2x2(x):
     loss' VGG-19 (imaginaire/losses/perceptual.py:175-192).  NHWC bf16 CUDA tensors with C % 8 == 0
     take the native kernels (no int64 index tensor; the backward recomputes the argmax); anything
     else goes through torch."""
+    _require_cuda('max_pool2x2', x)
     if (x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 4 and x.shape[1] % 8 == 0
             and x.is_contiguous(memory_format=torch.channels_last) and x.numel() > 0):
         return _MaxPool2x2.apply(x)
@@ -529,6 +539,7 @@ def bilinear_half_align_corners(x):
     """``F.interpolate(x, scale_factor=0.5, mode='bilinear', align_corners=True)``.
     ref: imaginaire/discriminators/spade.py:86-88.  Contiguous NCHW fp32 CUDA tensors take the native
     forward kernel (ATen's arithmetic, one thread per output element); others go through torch."""
+    _require_cuda('bilinear_half_align_corners', x)
     if x.is_cuda and x.dtype == torch.float32 and x.dim() == 4 and x.is_contiguous() and x.numel() > 0:
         ho, wo = int(math.floor(x.shape[2] * 0.5)), int(math.floor(x.shape[3] * 0.5))
         if ho > 0 and wo > 0:
@@ -554,6 +565,8 @@ def channel_dot(a, b):
     """``torch.mul(a, b).sum(dim=1, keepdim=True)``.  ref: imaginaire/discriminators/fpse.py:125-127.
     NHWC bf16 CUDA tensors of the same shape with C % 8 == 0 take one kernel each way (fp32
     accumulation, no product tensor); anything else goes through torch."""
+    _require_cuda('channel_dot', a, b)
+
     def ok(t):
         return (t.is_cuda and t.dtype == torch.bfloat16 and t.dim() == 4 and t.shape[1] % 8 == 0
                 and t.is_contiguous(memory_format=torch.channels_last))

@@ -172,3 +172,18 @@ def test_host_side_planners_and_validation_of_the_later_entry_points():
     # peer-memory gradient path
     assert lib.raw('imx_wgrad_reduce_peers_f32')(one, 9, 8, 0, 1, 1, 1, 1, 1, 128, 64, 1.0, 0, None) != 0
     assert lib.raw('imx_gather_rows_peers_f32')(one, 1, 0, None, 0, 1, None) == 0
+
+
+def test_loss_and_pooling_helpers_have_no_cpu_path():
+    """The fused loss / pooling / resize helpers keep torch expressions only for CUDA tensors the
+    kernels do not cover; CPU tensors are refused like everywhere else in the product path."""
+    import torch
+    from imaginaire_b200 import functional as NF
+    calls = ((NF.l1_loss_mean, (torch.zeros(2), torch.zeros(2))),
+             (NF.max_pool2x2, (torch.zeros(1, 8, 2, 2),)),
+             (NF.bilinear_half_align_corners, (torch.zeros(1, 1, 4, 4),)),
+             (NF.channel_dot, (torch.zeros(1, 8, 2, 2), torch.zeros(1, 8, 2, 2))))
+    for fn, args in calls:
+        with pytest.raises(RuntimeError, match='no CPU path'):
+            fn(*args)
+
