@@ -225,11 +225,10 @@ class _BaseConvBlock(nn.Module):
                 fused_act = _act_code(nxt[1])
             if name == 'conv':
                 last = (i + (2 if fused_act else 1)) >= len(items)
+                conv_act = fused_act
                 if last and fused_act == ops.ACT_NONE and post_act != ops.ACT_NONE and stats_mode is None:
-                    fused_act = post_act
-                    post_act = ops.ACT_NONE
-                    i -= 1          # nothing of this block's own is consumed by the borrowed activation
-                x = layer.native_forward(x, act=fused_act, residual=residual if last else None,
+                    conv_act, post_act = post_act, ops.ACT_NONE      # the consumer's activation rides in this epilogue
+                x = layer.native_forward(x, act=conv_act, residual=residual if last else None,
                                          stats_mode=stats_mode if last else None)
                 if last:
                     residual = None
