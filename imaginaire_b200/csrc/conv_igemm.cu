@@ -526,12 +526,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 template <int BN, int kMode, int MT = 1>
 int launch(const CUtensorMap& ta, const CUtensorMap& tb, const ConvArgs& a, cudaStream_t stream) {
     using C = Cfg<BN, MT>;
-    static bool attr_set = false;   // per (BN, mode, MT) instantiation
+    static bool attr_set[imx::kMaxDevices] = {};   // per (BN, mode, MT) instantiation and device
     auto kern = conv_igemm_kernel<BN, kMode, MT>;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
+    {
+        cudaError_t e = imx::ensure_dyn_smem(kern, C::SMEM_BYTES, attr_set);
         if (e != cudaSuccess) return imx::set_error((int)e, "conv_igemm: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-        attr_set = true;
     }
     const long items = (long)a.total_tiles * a.splits;
     const int grid = items < num_sms() ? (int)items : num_sms();

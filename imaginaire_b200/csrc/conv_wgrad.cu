@@ -380,11 +380,10 @@ template <int BN>
 int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const WgradArgs& a, cudaStream_t stream) {
     using C = WCfg<BN>;
     auto kern = conv_wgrad_kernel<BN>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES);
+    static bool attr_set[imx::kMaxDevices] = {};
+    {
+        cudaError_t e = imx::ensure_dyn_smem(kern, C::SMEM_BYTES, attr_set);
         if (e != cudaSuccess) return imx::set_error((int)e, "conv2d_wgrad: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-        attr_set = true;
     }
     const int grid = a.total_units < num_sms() ? a.total_units : num_sms();
     kern<<<grid, kThreads, C::SMEM_BYTES, stream>>>(tdy, tx, a);

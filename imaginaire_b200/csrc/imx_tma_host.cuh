@@ -37,14 +37,35 @@ inline int encode_tmap(CUtensorMap* m, const void* base, int rank, const uint64_
     return IMX_OK;
 }
 
+constexpr int kMaxDevices = 64;
+
+inline int current_device() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return (dev >= 0 && dev < kMaxDevices) ? dev : 0;
+}
+
+// SM count of the CURRENT device (cached per device: one process may drive several GPUs).
 inline int num_sms() {
-    static int n = 0;
-    if (n == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = imx::kNumSMs;
+    static int n[kMaxDevices] = {};
+    const int dev = current_device();
+    if (n[dev] == 0) {
+        int v = 0;
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = imx::kNumSMs;
+        n[dev] = v;
     }
-    return n;
+    return n[dev];
+}
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a per-device setting: `done` is one flag array per kernel
+// instantiation, indexed by the current device.
+template <typename K>
+inline cudaError_t ensure_dyn_smem(K kern, int bytes, bool (&done)[kMaxDevices]) {
+    const int dev = current_device();
+    if (done[dev]) return cudaSuccess;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess) done[dev] = true;
+    return e;
 }
 
 

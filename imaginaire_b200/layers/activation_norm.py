@@ -208,11 +208,16 @@ class SpatiallyAdaptiveNorm(nn.Module):
         if cond.requires_grad:
             # learned conditioning maps (vid2vid label embeddings): keep it differentiable
             return NF.to_nhwc(F.interpolate(cond.float(), size=(h, w), mode='nearest'))
-        cache = cond.__dict__.setdefault('_imx_resized', {})
+        # kept on the label tensor (dies with the batch); a caller that refills the same tensor in place
+        # (static input buffer, prefetcher copy_) advances its version counter and the maps are rebuilt
+        cache = cond.__dict__.get('_imx_resized')
+        if cache is None or cache[0] != cond._version:
+            cache = (cond._version, {})
+            cond.__dict__['_imx_resized'] = cache
         key = (h, w)
-        if key not in cache:
-            cache[key] = ops.nearest_resize_to_nhwc(cond, h, w)
-        return cache[key]
+        if key not in cache[1]:
+            cache[1][key] = ops.nearest_resize_to_nhwc(cond, h, w)
+        return cache[1][key]
 
     def _projection(self, i):
         """(hidden block or None, gamma conv, beta conv or None) of conditioning input i."""

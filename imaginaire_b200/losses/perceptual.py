@@ -1,10 +1,17 @@
 """VGG-19 perceptual loss.  ref: imaginaire/losses/perceptual.py:15-191
 
 The feature extractor is VGG-19 up to relu_5_1 built from the native Conv2dBlock (3x3
-tcgen05 convolutions with the ReLU in the epilogue; 2x2 max-pools are torch calls).  The
-reference loads ImageNet weights from the network; there is no network here, so the
-weights are randomly initialised (throughput is unaffected).
+tcgen05 convolutions with the ReLU in the epilogue, native 2x2 max-pools).  The reference
+downloads torchvision's ImageNet weights (perceptual.py:177); here they come from a local
+file: ``cfg.trainer.perceptual_loss.weights_path`` or the environment variable
+``IMX_VGG19_WEIGHTS`` names a torchvision ``vgg19`` state dict (``features.N.weight/bias`` or
+the bare ``N.weight/bias`` of ``vgg19().features``), remapped onto the blocks by
+``load_torchvision_state_dict``.  Without one the filters stay randomly initialised and a
+warning says so once (fine for throughput runs, not the reference's loss).
 """
+import os
+import warnings
+
 import torch
 import torch.nn.functional as F
 from torch import nn
@@ -37,6 +44,30 @@ class _VGG19Features(nn.Module):
         self.names, self.blocks = self.names[:last + 1], self.blocks[:last + 1]
         for p in self.parameters():
             p.requires_grad = False
+        self.pretrained = False
+
+    # torchvision's vgg19().features: index of the Conv2d that precedes each named ReLU (perceptual.py:178-190
+    # names the ReLU outputs 1, 3, 6, ...; the convolution sits one index earlier)
+    _TV_CONV_INDEX = {'relu_1_1': 0, 'relu_1_2': 2, 'relu_2_1': 5, 'relu_2_2': 7, 'relu_3_1': 10, 'relu_3_2': 12,
+                      'relu_3_3': 14, 'relu_3_4': 16, 'relu_4_1': 19, 'relu_4_2': 21, 'relu_4_3': 23,
+                      'relu_4_4': 25, 'relu_5_1': 28}
+
+    def load_torchvision_state_dict(self, sd):
+        """Copies ``features.N.{weight,bias}`` (or ``N.{weight,bias}``) of a torchvision VGG-19 onto the blocks."""
+        prefix = 'features.' if any(k.startswith('features.') for k in sd) else ''
+        with torch.no_grad():
+            for name, block in zip(self.names, self.blocks):
+                if name == 'pool':
+                    continue
+                conv = block.layers['conv']
+                idx = self._TV_CONV_INDEX[name]
+                w, b = sd['%s%d.weight' % (prefix, idx)], sd['%s%d.bias' % (prefix, idx)]
+                if tuple(w.shape) != tuple(conv.weight.shape):
+                    raise ValueError('VGG-19 checkpoint: %s%d.weight has shape %s, expected %s'
+                                     % (prefix, idx, tuple(w.shape), tuple(conv.weight.shape)))
+                conv.weight.copy_(w)     # in place: advances the version counter the packed-filter cache keys on
+                conv.bias.copy_(b)
+        self.pretrained = True
 
     def forward(self, x):
         out = {}
@@ -80,6 +111,13 @@ class PerceptualLoss(nn.Module):
         if network != 'vgg19':
             raise NotImplementedError('only the vgg19 perceptual network is provided')
         self.model = _VGG19Features(layers)
+        path = None
+        if cfg is not None and hasattr(cfg, 'trainer') and hasattr(cfg.trainer, 'perceptual_loss'):
+            path = getattr(cfg.trainer.perceptual_loss, 'weights_path', None)
+        path = path or os.environ.get('IMX_VGG19_WEIGHTS')
+        if path:
+            self.model.load_torchvision_state_dict(torch.load(path, map_location='cpu', weights_only=True))
+        self._warned = False
         self.layers, self.weights = list(layers), list(weights)
         self.criterion = nn.L1Loss() if criterion == 'l1' else nn.MSELoss()
         self.resize, self.resize_mode = resize, resize_mode
@@ -88,6 +126,10 @@ class PerceptualLoss(nn.Module):
 
     def forward(self, inp, target):
         self.model.eval()
+        if not self.model.pretrained and not self._warned:
+            self._warned = True
+            warnings.warn('PerceptualLoss: VGG-19 runs with randomly initialised filters (no weights_path / '
+                          'IMX_VGG19_WEIGHTS); this is not the reference\'s ImageNet perceptual loss')
         inp, target = apply_imagenet_normalization(inp), apply_imagenet_normalization(target)
         if self.resize:
             inp = F.interpolate(inp, mode=self.resize_mode, size=(224, 224), align_corners=False)

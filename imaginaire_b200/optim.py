@@ -65,3 +65,8 @@ def _adam_launch(items, lr, beta1, beta2, eps, weight_decay, step):
     # launches issued: one per 96 tensors / 1184 chunks of 32768 elements
     chunks = sum((t[0].numel() + 32767) // 32768 for t in items)
     lib.launches += max((n + 95) // 96, (chunks + 1183) // 1184) - 1
+    # The kernel writes through raw pointers, which autograd's version counters do not see.  Everything that
+    # caches a value derived from a parameter (packed bf16 filters in functional._packed_weight, the
+    # identity-affine check in layers/activation_norm.py) keys on Tensor._version, so the counters are
+    # advanced here exactly as an in-place torch update would advance them.
+    torch._C._increment_version([t[0] for t in items])

@@ -26,7 +26,10 @@ class ModelAverage(nn.Module):
         self.remove_sn = remove_sn
         self.start_iteration = start_iteration
         self.register_buffer('num_updates_tracked', torch.tensor(0, dtype=torch.long))
-        self._steps = 0
+        # host mirror of num_updates_tracked (the checkpointed counter, model_average.py:87-91); None = not read
+        # yet / a state dict was loaded: the next update reads the buffer once (.item()), later ones stay
+        # sync-free
+        self._steps = None
         requires_grad(self.averaged_model, False)
         if remove_sn:
             def strip(m):
@@ -39,6 +42,10 @@ class ModelAverage(nn.Module):
 
     def forward(self, *inputs, **kwargs):
         return self.module(*inputs, **kwargs)
+
+    def _load_from_state_dict(self, *args, **kwargs):
+        super()._load_from_state_dict(*args, **kwargs)
+        self._steps = None      # resume: the warm-up counter continues from the checkpointed buffer
 
     @staticmethod
     def sn_compute_weight(weight, u, v):
@@ -63,6 +70,8 @@ class ModelAverage(nn.Module):
 
     @torch.no_grad()
     def update_average(self):
+        if self._steps is None:
+            self._steps = int(self.num_updates_tracked.item())
         self.num_updates_tracked += 1
         self._steps += 1
         beta = 0.0 if self._steps <= self.start_iteration else self.beta

@@ -10,8 +10,11 @@
  *           :46-69 (padded channels-last copy), :72-149 (forward), :152-241 (d/d input1),
  *           :243-336 (d/d input2); output size from correlation_cuda.cc:25-35.
  *
- * The reference's CUDA extensions cannot be built here (old ATen API, GPU needed) and the
- * reference holds no tests or golden vectors for them: "parity unpinned" by the reference.
+ * Pinned: the reference's own kernel bodies are compiled for host cores (oracle/ref_cuda/,
+ * output in oracle/_ref/, 32-lane blocks run as fibers with emulated shuffles and barriers) and
+ * this restatement equals their multiply-add-fused build bit for bit on
+ * tests/golden/ref_{channelnorm,correlation}_*.npz and on fresh inputs where oracle/_ref is
+ * present (tests/test_native_ops_reference_pin.py); the -ffp-contract=off build is within 1e-6.
  * The restatement keeps the reference's ORDER of floating-point operations, including the
  * per-lane partial sums of the 32-thread blocks and their reduction trees, so that the CUDA
  * kernels (which keep the same order) can be compared bit for bit.  `acc += a * b` in the

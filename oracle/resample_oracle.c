@@ -7,11 +7,13 @@
  *
  *   r2d_*  follows imaginaire/third_party/resample2d/src/resample2d_kernel.cu
  *          :15-75  (forward), :78-129 (d/d image), :131-203 (d/d flow), kernel_size == 1.
- *          The reference's CUDA extension cannot be built here (pre-1.5 ATen API, needs a
- *          GPU), and the reference has no tests or golden vectors for it: this half of the
- *          oracle is pinned only by known-answer cases (integer flows are exact shifts,
- *          zero flow is the identity) and by closeness to the grid_sample oracle below
- *          -- "parity unpinned" by the reference itself.
+ *          Pinned: the reference's own kernel bodies are compiled for host cores
+ *          (oracle/ref_cuda/, output in oracle/_ref/) and this restatement equals them bit for
+ *          bit -- forward and both gradients -- on tests/golden/ref_resample2d_*.npz
+ *          (oracle/make_golden_native_ops.py) and on fresh inputs where oracle/_ref is present
+ *          (tests/test_native_ops_reference_pin.py).  That is the -ffp-contract=off build; the
+ *          build that fuses multiply-adds the way nvcc -fmad=true does differs from it by a
+ *          rounding in the fourth tap and in the flow gradient's terms (held to 1e-5).
  *   gsw_*  follows imaginaire/model_utils/fs_vid2vid.py:14-39 resample() =
  *          F.grid_sample(bilinear, border, align_corners=True) over
  *          linspace(-1,1)+flow/((size-1)/2).  Pinned bit-exactly against the reference's
