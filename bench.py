@@ -282,8 +282,8 @@ def run_ours(args):
 
     cfg = Config(os.path.join(ROOT, 'configs', args.config))
     batch = args.batch or cfg.data.train.batch_size
-    net_G, net_D, opt_G, opt_D = get_model_optimizer_and_scheduler(cfg, seed=0, device=dev)
-    trainer = Trainer(cfg, net_G, net_D, opt_G, opt_D)
+    net_G, net_D, opt_G, opt_D, sch_G, sch_D = get_model_optimizer_and_scheduler(cfg, seed=0, device=dev)
+    trainer = Trainer(cfg, net_G, net_D, opt_G, opt_D, sch_G, sch_D, (), None)
     net_G.train(); net_D.train()
 
     host = synthetic_batch(cfg, batch, seed=100 + rank, pinned=True)

@@ -1,50 +1,72 @@
-"""SPADE training step (generator + discriminator update).
-ref: imaginaire/trainers/base.py:594-666 (gen_update / dis_update),
-     imaginaire/trainers/spade.py:60-187 (losses, gen_forward, dis_forward)
+"""SPADE trainer (generator + discriminator update).
+ref: imaginaire/trainers/spade.py:23-187 (constructor, losses, _start_of_iteration, gen_forward, dis_forward),
+     imaginaire/trainers/base.py:594-666 (gen_update / dis_update, in trainers/base.py here)
 
-Only what one optimisation step needs (no logging, checkpointing, FID).  The generator
-runs three times per iteration exactly as in the reference: once under no_grad for the
-discriminator update (the fused no-HBM gamma/beta path), once with autograd for its own
-update, and once backward.
+Same constructor as the reference (``Trainer(cfg, net_G, net_D, opt_G, opt_D, sch_G, sch_D, train_data_loader,
+val_data_loader)``), same loss names, weights and composition.  The generator runs three times per iteration
+exactly as in the reference: once under no_grad for the discriminator update (the fused no-HBM gamma/beta path),
+once with autograd for its own update, and once backward.  A network that is frozen in a phase is called through
+``.module`` instead of its data-parallel wrapper (same computation, no gradient exchange to set up).
 """
+import math
+
 import torch
+import torch.nn.functional as F
 
-from .. import grad_sync
 from ..losses import FeatureMatchingLoss, GANLoss, GaussianKLLoss, PerceptualLoss
-from ..utils.model_average import requires_grad
+from .base import BaseTrainer
 
 
-class Trainer:
-    def __init__(self, cfg, net_G, net_D, opt_G, opt_D):
-        self.cfg = cfg
-        self.net_G, self.net_D, self.opt_G, self.opt_D = net_G, net_D, opt_G, opt_D
-        self.net_G_module = net_G.module
-        if hasattr(self.net_G_module, 'module') and hasattr(self.net_G_module, 'averaged_model'):
-            self.net_G_module = self.net_G_module.module      # inside ModelAverage
+class Trainer(BaseTrainer):
+    def __init__(self, cfg, net_G, net_D, opt_G, opt_D, sch_G=None, sch_D=None, train_data_loader=(),
+                 val_data_loader=None):
+        super().__init__(cfg, net_G, net_D, opt_G, opt_D, sch_G, sch_D, train_data_loader, val_data_loader)
+        self.video_mode = getattr(cfg.data, 'type', '') == 'imaginaire.datasets.paired_videos'
+
+    def _init_loss(self, cfg):
         t = cfg.trainer
-        self.criteria, self.weights = {}, {}
         self.criteria['GAN'] = GANLoss(t.gan_mode)
         self.weights['GAN'] = t.loss_weight.gan
         if hasattr(t, 'perceptual_loss'):
-            dev = next(net_G.parameters()).device
             self.criteria['Perceptual'] = PerceptualLoss(cfg=cfg, network=t.perceptual_loss.mode,
                                                          layers=t.perceptual_loss.layers,
-                                                         weights=t.perceptual_loss.weights).to(dev)
+                                                         weights=t.perceptual_loss.weights)
             self.weights['Perceptual'] = t.loss_weight.perceptual
         self.criteria['FeatureMatching'] = FeatureMatchingLoss()
         self.weights['FeatureMatching'] = t.loss_weight.feature_matching
         self.criteria['GaussianKL'] = GaussianKLLoss()
         self.weights['GaussianKL'] = t.loss_weight.kl
-        self.gen_losses, self.dis_losses = {}, {}
+
+    def _start_of_iteration(self, data, current_iteration):
+        """Video batches are folded into the channel axis, then labels / images are resized to a multiple of the
+        generator's base (spade.py:99-130, 297-313)."""
+        if data['label'].dim() == 5:
+            label_image_raw = data['images'][:, 0:-1]
+            label_image = label_image_raw.reshape(label_image_raw.size(0), -1, label_image_raw.size(3),
+                                                  label_image_raw.size(4))
+            images = data['images'][:, -1]
+            label_label = data['label'].reshape(data['label'].size(0), -1, data['label'].size(3),
+                                                data['label'].size(4))
+            data['label'] = torch.cat([label_label, label_image], 1)
+            data['images'] = images
+        return self._resize_data(data)
+
+    def _resize_data(self, data):
+        base = getattr(self.net_G, 'base', 32)
+        sy = math.floor(data['label'].size(2) * 1.0 // base) * base
+        sx = math.floor(data['label'].size(3) * 1.0 // base) * base
+        if (sy, sx) != tuple(data['label'].shape[2:]):
+            data['label'] = F.interpolate(data['label'], size=[sy, sx], mode='nearest')
+            if 'images' in data:
+                data['images'] = F.interpolate(data['images'], size=[sy, sx], mode='bicubic')
+        return data
 
     # ----------------------------------------------------------- generator
     def gen_forward(self, data):
         net_G_output = self.net_G(data)
-        # the discriminator is frozen here: no gradient exchange to set up, so the data-parallel
-        # wrapper is bypassed (same computation)
-        net_D_output = self.net_D.module(data, net_G_output)
+        net_D_output = self.net_D.module(data, net_G_output)      # frozen here: the wrapper has nothing to do
         losses = self.gen_losses
-        losses['GAN'] = self.criteria['GAN'](net_D_output['fake_outputs'], True, dis_update=False)
+        losses['GAN'] = self.criteria['GAN'](self._get_outputs(net_D_output, real=False), True, dis_update=False)
         losses['FeatureMatching'] = self.criteria['FeatureMatching'](net_D_output['fake_features'],
                                                                      net_D_output['real_features'])
         if self.net_G_module.use_style_encoder:
@@ -57,43 +79,22 @@ class Trainer:
         losses['total'] = total
         return total
 
-    def gen_update(self, data):
-        self.opt_G.zero_grad(set_to_none=True)
-        requires_grad(self.net_G_module, True)
-        requires_grad(self.net_D, False)
-        total = self.gen_forward(data)
-        total.backward()
-        grad_sync.finish_all()      # no-op unless the peer-memory gradient path is active
-        self.opt_G.step()
-        if self.cfg.trainer.model_average:
-            self.net_G.module.update_average()
-        return total.detach()
-
     # -------------------------------------------------------- discriminator
     def dis_forward(self, data):
         with torch.no_grad():
-            net_G_output = self.net_G.module(data)      # no_grad: nothing for the DDP wrapper to do
+            net_G_output = self.net_G.module(data)      # no_grad: nothing for the data-parallel wrapper to do
             net_G_output['fake_images'] = net_G_output['fake_images'].detach()
         net_D_output = self.net_D(data, net_G_output)
-        fake = self.criteria['GAN'](net_D_output['fake_outputs'], False, dis_update=True)
-        true = self.criteria['GAN'](net_D_output['real_outputs'], True, dis_update=True)
+        fake = self.criteria['GAN'](self._get_outputs(net_D_output, real=False), False, dis_update=True)
+        true = self.criteria['GAN'](self._get_outputs(net_D_output, real=True), True, dis_update=True)
         self.dis_losses.update({'GAN/fake': fake, 'GAN/true': true, 'GAN': fake + true})
         total = self.dis_losses['GAN'] * self.weights['GAN']
         self.dis_losses['total'] = total
         return total
 
-    def dis_update(self, data):
-        self.opt_D.zero_grad(set_to_none=True)
-        requires_grad(self.net_G_module, False)
-        requires_grad(self.net_D, True)
-        total = self.dis_forward(data)
-        total.backward()
-        grad_sync.finish_all()
-        self.opt_D.step()
-        return total.detach()
-
     def step(self, data):
-        """One training iteration in the reference's order (train.py:76-79)."""
-        d = self.dis_update(data)
-        g = self.gen_update(data)
-        return g, d
+        """One training iteration in the reference's order (train.py:76-79): dis_update, then gen_update.
+        Returns the two total losses (detached)."""
+        self.dis_update(data)
+        self.gen_update(data)
+        return self.gen_losses['total'], self.dis_losses['total']

@@ -1,20 +1,20 @@
 """Builds networks, optimisers and the data-parallel wrapping.
 ref: imaginaire/utils/trainer.py:24-37 (seeds), :69-125 (get_model_optimizer_and_scheduler),
-     :128-216 (wrap / DDP), :242-306 (optimisers)
+     :128-216 (wrap / DDP), :219-306 (schedulers, optimisers), :40-66 (get_trainer)
 
 apex is replaced as SURVEY.md Appendix C prescribes: mixed precision is the kernels' own
 bf16-storage / fp32-accumulate arithmetic (no loss scaling), apex FusedAdam becomes
 imaginaire_b200.optim.FusedAdam (csrc/optim.cu), apex DDP becomes torch DDP over NCCL.
 """
+import importlib
 import os
 import random
 
 import numpy as np
 import torch
 from torch.nn.parallel import DistributedDataParallel
+from torch.optim import lr_scheduler
 
-from ..discriminators.spade import Discriminator
-from ..generators.spade import Generator
 from .distributed import get_rank, get_world_size
 from .init_weight import weights_init
 from .model_average import ModelAverage
@@ -30,20 +30,62 @@ def set_random_seed(seed, by_rank=False):
     torch.cuda.manual_seed_all(seed)
 
 
-def get_optimizer(opt_cfg, params):
-    if opt_cfg.type != 'adam':
-        raise NotImplementedError('only adam is wired up for the SPADE step')
-    # the library's multi-tensor kernel; like every other product path it refuses CPU parameters at step()
-    return FusedAdam(list(params), lr=opt_cfg.lr, eps=getattr(opt_cfg, 'eps', 1e-8),
-                     betas=(opt_cfg.adam_beta1, opt_cfg.adam_beta2))
+def get_optimizer(cfg_opt, net):
+    """ref: utils/trainer.py:261-276.  Every parameter of the network goes to the optimizer (also the ones that
+    are frozen at construction: the trainer flips requires_grad per phase, trainers/base.py:602-603)."""
+    if hasattr(net, 'get_param_groups'):
+        params = net.get_param_groups(cfg_opt)
+    elif isinstance(net, torch.nn.Module):
+        params = net.parameters()
+    else:
+        params = net        # an iterable of parameters / parameter groups
+    return get_optimizer_for_params(cfg_opt, params)
+
+
+def get_optimizer_for_params(cfg_opt, params):
+    """ref: utils/trainer.py:279-306.  'adam' is the library's multi-tensor kernel (the reference's apex FusedAdam /
+    torch Adam: same update rule and state layout); like every other product path it refuses CPU parameters at
+    step().  The other optimizers of the reference (madam, fromage, rmsprop, sgd) are outside the SPADE path."""
+    if cfg_opt.type != 'adam':
+        raise NotImplementedError('Optimizer {} is not wired up for the SPADE step.'.format(cfg_opt.type))
+    return FusedAdam(list(params), lr=cfg_opt.lr, eps=getattr(cfg_opt, 'eps', 1e-8),
+                     betas=(cfg_opt.adam_beta1, cfg_opt.adam_beta2))
+
+
+def get_scheduler(cfg_opt, opt):
+    """ref: utils/trainer.py:219-240: 'step' -> StepLR(step_size, gamma), 'constant' -> LambdaLR(1)."""
+    policy = cfg_opt.lr_policy
+    if policy.type == 'step':
+        return lr_scheduler.StepLR(opt, step_size=policy.step_size, gamma=policy.gamma)
+    if policy.type == 'constant':
+        return lr_scheduler.LambdaLR(opt, lambda x: 1)
+    raise NotImplementedError('Learning rate policy {} not implemented.'.format(policy.type))
+
+
+def get_trainer(cfg, net_G, net_D=None, opt_G=None, opt_D=None, sch_G=None, sch_D=None, train_data_loader=None,
+                val_data_loader=None):
+    """ref: utils/trainer.py:40-66: the Trainer class of the module that ``cfg.trainer.type`` names (resolved through
+    the ``imaginaire`` alias package, so the reference's config files work unchanged)."""
+    trainer_lib = importlib.import_module(_resolve(cfg.trainer.type))
+    return trainer_lib.Trainer(cfg, net_G, net_D, opt_G, opt_D, sch_G, sch_D, train_data_loader, val_data_loader)
+
+
+def _resolve(module_name):
+    """'imaginaire.x.y' -> 'imaginaire_b200.x.y' (the same module object the alias package would return)."""
+    if module_name == 'imaginaire' or module_name.startswith('imaginaire.'):
+        return 'imaginaire_b200' + module_name[len('imaginaire'):]
+    return module_name
 
 
 def get_model_optimizer_and_scheduler(cfg, seed=0, device='cuda'):
-    """Returns (net_G, net_D, opt_G, opt_D).  Networks are built and initialised with the same
-    seed on every rank, then the seed is offset by rank like the reference."""
+    """ref: utils/trainer.py:69-125.  Returns (net_G, net_D, opt_G, opt_D, sch_G, sch_D).  Networks are built by the
+    modules ``cfg.gen.type`` / ``cfg.dis.type`` name and initialised with the same seed on every rank, then the seed
+    is offset by rank like the reference."""
     set_random_seed(seed, by_rank=False)
-    net_G = Generator(cfg.gen, cfg.data)
-    net_D = Discriminator(cfg.dis, cfg.data)
+    lib_G = importlib.import_module(_resolve(cfg.gen.type))
+    lib_D = importlib.import_module(_resolve(cfg.dis.type))
+    net_G = lib_G.Generator(cfg.gen, cfg.data)
+    net_D = lib_D.Discriminator(cfg.dis, cfg.data)
     init = getattr(cfg.trainer, 'init', None)
     if init is not None:
         fn = weights_init(init.type, init.gain, getattr(init, 'bias', None))
@@ -51,9 +93,10 @@ def get_model_optimizer_and_scheduler(cfg, seed=0, device='cuda'):
         net_D.apply(fn)
     net_G, net_D = net_G.to(device), net_D.to(device)
     set_random_seed(seed, by_rank=True)
-    opt_G = get_optimizer(cfg.gen_opt, [p for p in net_G.parameters() if p.requires_grad])
-    opt_D = get_optimizer(cfg.dis_opt, [p for p in net_D.parameters() if p.requires_grad])
-    return wrap_model_and_optimizer(cfg, net_G, net_D, opt_G, opt_D)
+    opt_G = get_optimizer(cfg.gen_opt, net_G)
+    opt_D = get_optimizer(cfg.dis_opt, net_D)
+    net_G, net_D, opt_G, opt_D = wrap_model_and_optimizer(cfg, net_G, net_D, opt_G, opt_D)
+    return net_G, net_D, opt_G, opt_D, get_scheduler(cfg.gen_opt, opt_G), get_scheduler(cfg.dis_opt, opt_D)
 
 
 def wrap_model_and_optimizer(cfg, net_G, net_D, opt_G, opt_D):

@@ -75,3 +75,31 @@ def build_generator(config_name, seed=0):
     net = Generator(cfg.gen, cfg.data)
     net.apply(weights_init(cfg.trainer.init.type, cfg.trainer.init.gain))
     return cfg, net
+
+
+def subsample(t, limit=20000):
+    """The rule oracle/make_golden_train.py stores large tensors by: a strided sample of the flattened tensor."""
+    flat = t.reshape(-1)
+    return flat[::-(-flat.numel() // limit)] if flat.numel() > limit else t
+
+
+def seeded_vgg19_features(seed=1234):
+    """torchvision's VGG-19 with its default initialisation under a fixed seed (oracle/make_golden_train.py builds
+    the reference's perceptual network the same way: there is no network to download ImageNet weights from)."""
+    from torchvision.models.vgg import vgg19
+    with torch.random.fork_rng():
+        torch.manual_seed(seed)
+        return vgg19(weights=None).features
+
+
+def c3mini_batch(n=2, h=256, w=256, classes=35):
+    """Inputs of tests/golden/{train_step,discriminator,generator}_c3mini.npz."""
+    label = onehot_label(5, n, classes, h, w, blocky=8)
+    g = torch.Generator().manual_seed(6)
+    images = torch.rand(n, 3, h, w, generator=g) * 2 - 1
+    return {'label': label, 'images': images}
+
+
+def style_noise(seed, n, dims):
+    g = torch.Generator().manual_seed(seed)
+    return torch.randn(n, dims, generator=g)

@@ -1,0 +1,265 @@
+"""The timed training step against the REFERENCE's own trainer, discriminator, generator and AdaptiveNorm.
+
+Fixtures: tests/golden/{train_step,discriminator,generator}_c3mini.npz and adaptive_norm_*.npz, produced by
+oracle/make_golden_train.py from the imported reference (fp32, CPU) on configs/spade_c3_mini.yaml -- BASELINE
+configs[2]'s architecture (sync batch norm, separate 5x5 SPADE projections, spectral norm everywhere, SPADE
+discriminator = FPSE + 2 patch discriminators, hinge + feature matching + KL + VGG-19 perceptual loss, Adam, EMA) at
+16 base filters and 256x256.  Networks, inputs and the (seeded random) VGG-19 are rebuilt here from the same seeds;
+sha256 digests in the fixtures prove they are the same bits.
+
+The native path computes in bf16 storage with fp32 accumulation, the reference in fp32: tolerances are bf16-sized and
+written beside each assertion.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from tests import helpers as H
+
+pytestmark = pytest.mark.gpu
+CONFIG = 'spade_c3_mini.yaml'
+
+
+def _dev():
+    assert torch.cuda.is_available(), 'GPU tests need a CUDA device'
+    return torch.device('cuda:0')
+
+
+def _cfg():
+    from imaginaire_b200.config import Config
+    return Config(os.path.join(H.ROOT, 'configs', CONFIG))
+
+
+def _rel_l2(a, b):
+    a, b = torch.as_tensor(a).double().reshape(-1), torch.as_tensor(b).double().reshape(-1)
+    return float((a - b).norm() / (b.norm() + 1e-30))
+
+
+def _cos(a, b):
+    a, b = torch.as_tensor(a).double().reshape(-1), torch.as_tensor(b).double().reshape(-1)
+    return float((a * b).sum() / (a.norm() * b.norm() + 1e-30))
+
+
+def _fix_eps(net_G_module, eps):
+    enc = net_G_module.style_encoder
+    enc.freeze_random = True
+    enc.eps = eps.to(_dev())
+
+
+def _build_trainer():
+    """get_model_optimizer_and_scheduler + get_trainer exactly as train.py:45-60 calls them."""
+    from imaginaire_b200.utils.trainer import get_model_optimizer_and_scheduler, get_trainer
+    cfg = _cfg()
+    net_G, net_D, opt_G, opt_D, sch_G, sch_D = get_model_optimizer_and_scheduler(cfg, seed=0)
+    trainer = get_trainer(cfg, net_G, net_D, opt_G, opt_D, sch_G, sch_D, (), None)
+    vgg = H.seeded_vgg19_features()
+    trainer.criteria['Perceptual'].model.load_torchvision_state_dict(vgg.state_dict())
+    return cfg, trainer, vgg
+
+
+def test_seeded_networks_are_the_references_bits():
+    """Same seed -> same construction order -> bit-identical initial weights as the reference trainer's networks
+    (and the same VGG-19), so every comparison below starts from identical parameters."""
+    d = H.load_golden('train_step_c3mini.npz')
+    cfg, trainer, vgg = _build_trainer()
+    G, D = trainer.net_G_module, trainer.net_D.module
+    assert list(G.state_dict().keys()) == [str(k) for k in d['g_keys']]
+    assert list(D.state_dict().keys()) == [str(k) for k in d['d_keys']]
+    assert H.state_dict_digest(G.state_dict()) == str(d['g_sha256'])
+    assert H.state_dict_digest(D.state_dict()) == str(d['d_sha256'])
+    assert H.state_dict_digest(vgg.state_dict()) == str(d['vgg_sha256'])
+
+
+def test_c3_style_generator_forward_vs_reference():
+    """generators/spade.py:401-493 with sync_batch + separate 5x5 projections + spectral SPADE convs (the
+    headline architecture), train mode, grad and no-grad paths."""
+    from imaginaire_b200.generators.spade import Generator
+    from imaginaire_b200.utils.init_weight import weights_init
+    d = H.load_golden('generator_c3mini.npz')
+    cfg = _cfg()
+    ref = torch.from_numpy(d['fake_images']).float()
+    data = {k: v.to(_dev()) for k, v in H.c3mini_batch().items()}
+    for grad in (False, True):
+        torch.manual_seed(0)
+        net = Generator(cfg.gen, cfg.data)
+        net.apply(weights_init(cfg.trainer.init.type, cfg.trainer.init.gain))
+        assert H.state_dict_digest(net.state_dict()) == str(d['state_dict_sha256'])
+        net = net.to(_dev()).train()
+        _fix_eps(net, torch.from_numpy(d['eps']))
+        with torch.set_grad_enabled(grad):
+            out = net(dict(data))
+        img = out['fake_images'].float().cpu()
+        diff = (img - ref).abs()
+        print('c3-style generator grad=%s: max-abs %.4f mean-abs %.5f (ref mean-abs %.4f)'
+              % (grad, float(diff.max()), float(diff.mean()), float(ref.abs().mean())))
+        assert H.rel_err(out['mu'].cpu(), d['mu']) < 3e-2 and H.rel_err(out['logvar'].cpu(), d['logvar']) < 3e-2
+        # bf16 tolerance after tanh (north_star quotes max-abs <= 2e-2, mean-abs <= 2e-3 as the example)
+        assert float(diff.max()) <= 2e-2 and float(diff.mean()) <= 2e-3
+
+
+def test_discriminator_forward_vs_reference():
+    """discriminators/spade.py:73-117, fpse.py:87-132, multires_patch.py:250-313: every output and every feature
+    map, real and fake pass, plus the spectral-norm vectors after the two power iterations."""
+    from imaginaire_b200.discriminators.spade import Discriminator
+    from imaginaire_b200.utils.init_weight import weights_init
+    d = H.load_golden('discriminator_c3mini.npz')
+    cfg = _cfg()
+    from imaginaire_b200.generators.spade import Generator
+    # the reference builds G, then D, then initialises G, then D under one seed (utils/trainer.py:93-106): D's
+    # weights depend on the draws G consumed before it
+    torch.manual_seed(0)
+    net_G = Generator(cfg.gen, cfg.data)
+    net = Discriminator(cfg.dis, cfg.data)
+    fn = weights_init(cfg.trainer.init.type, cfg.trainer.init.gain)
+    net_G.apply(fn)
+    net.apply(fn)
+    assert H.state_dict_digest(net.state_dict()) == str(d['state_dict_sha256'])
+    net = net.to(_dev()).train()
+    data = {k: v.to(_dev()) for k, v in H.c3mini_batch().items()}
+    g = torch.Generator().manual_seed(7)
+    fake = (torch.rand(2, 3, 256, 256, generator=g) * 2 - 1).to(_dev())
+    with torch.no_grad():
+        out = net(data, {'fake_images': fake})
+    worst_o, worst_f = 0.0, 0.0
+    for kind in ('real', 'fake'):
+        outs, feats = out[kind + '_outputs'], out[kind + '_features']
+        assert len(outs) == 5 and len(feats) == 2          # 3 FPSE heads + 2 patch discriminators
+        for i, o in enumerate(outs):
+            ref = torch.from_numpy(d['%s_outputs.%d' % (kind, i)]).float()
+            o = o.float().cpu()
+            assert o.shape == ref.shape, (kind, i, o.shape, ref.shape)
+            worst_o = max(worst_o, _rel_l2(o, ref))
+        for i, fl in enumerate(feats):
+            assert len(fl) == 5
+            for j, f in enumerate(fl):
+                ref = torch.from_numpy(d['%s_features.%d.%d' % (kind, i, j)]).float()
+                f = f.float().cpu()
+                f = f[:, :, ::2, ::2] if f.shape[-1] > 32 else f
+                assert f.shape == ref.shape, (kind, i, j, f.shape, ref.shape)
+                worst_f = max(worst_f, _rel_l2(f, ref))
+    print('discriminator: worst relative L2 error outputs %.4f features %.4f' % (worst_o, worst_f))
+    assert worst_o < 2e-2 and worst_f < 2e-2               # bf16 storage through <= 6 layers
+    sd = net.state_dict()
+    for k, v in d.items():
+        if k.startswith('sd_after.'):
+            assert H.rel_err(sd[k[len('sd_after.'):]].cpu(), v) < 2e-3, k
+
+
+def test_one_training_iteration_vs_reference_trainer():
+    """dis_update then gen_update (train.py:76-79; trainers/base.py:594-666, trainers/spade.py:128-187): every loss
+    term, gradients of every parameter (norms) and of a spread of tensors (direction), the weights after the two
+    Adam steps, the EMA copy, spectral-norm vectors and running statistics."""
+    d = H.load_golden('train_step_c3mini.npz')
+    cfg, trainer, _ = _build_trainer()
+    G, D = trainer.net_G_module, trainer.net_D.module
+    data = trainer.start_of_iteration(H.c3mini_batch(), current_iteration=1)
+
+    # ---- discriminator update
+    _fix_eps(G, torch.from_numpy(d['eps_dis']))
+    d_before = {k: v.detach().clone() for k, v in D.state_dict().items()}
+    trainer.dis_update(data)
+    for k in ('GAN/fake', 'GAN/true', 'GAN', 'total'):
+        ours, ref = float(trainer.dis_losses[k]), float(d['dis_loss.' + k])
+        print('dis %-16s ours %.6f reference %.6f' % (k, ours, ref))
+        assert abs(ours - ref) <= 2e-3 * max(1.0, abs(ref)), k
+    _check_grads_and_update('d', d, dict(D.named_parameters()), d_before, D.state_dict(), lr=cfg.dis_opt.lr)
+
+    # ---- generator update
+    _fix_eps(G, torch.from_numpy(d['eps_gen']))
+    g_before = {k: v.detach().clone() for k, v in G.state_dict().items()}
+    trainer.gen_update(data)
+    for k in ('GAN', 'FeatureMatching', 'GaussianKL', 'Perceptual', 'total'):
+        ours, ref = float(trainer.gen_losses[k]), float(d['gen_loss.' + k])
+        print('gen %-16s ours %.6f reference %.6f' % (k, ours, ref))
+        # the discriminator these are measured through has just taken a sign-like Adam step (beta1 = 0, first
+        # step: |update| = lr per element), so a bf16-sized gradient difference moves them by a few per cent
+        assert abs(ours - ref) <= 5e-2 * max(abs(ref), 1e-3) + 1e-4, k
+    _check_grads_and_update('g', d, dict(G.named_parameters()), g_before, G.state_dict(), lr=cfg.gen_opt.lr)
+
+    sd = G.state_dict()
+    for k, v in d.items():
+        if k.startswith('g_buffer_after.'):
+            name = k[len('g_buffer_after.'):]
+            tol = 2e-2 if 'running' in name else 5e-3
+            assert H.rel_err(sd[name].cpu(), v) < tol, name
+    ema = trainer.net_G.module.averaged_model.state_dict()
+    for k, v in d.items():
+        if k.startswith('ema_after.'):
+            name = k[len('ema_after.'):]
+            ours = H.subsample(ema[name].float().cpu())
+            # beta = 0 during warm-up: the EMA copy is the current weight (W / sigma for spectral layers)
+            assert _rel_l2(ours, v) < 2e-2, name
+    assert int(trainer.net_G.module.num_updates_tracked) == int(d['ema_num_updates'])
+    assert float(next(iter(trainer.opt_G.state.values()))['step']) == float(d['opt_g_step'])
+
+
+def _check_grads_and_update(tag, d, params, before, after, lr):
+    names = [str(n) for n in d[tag + '_grad_names']]
+    ref_norms = d[tag + '_grad_norms']
+    missing = [n for n in names if params[n].grad is None]
+    assert not missing, 'no gradient for %s' % missing[:5]
+    ratios = []
+    for n, rn in zip(names, ref_norms):
+        if rn > 1e-12:
+            ratios.append(float(params[n].grad.float().norm()) / rn)
+    ratios = np.array(ratios)
+    print('%s: gradient-norm ratio ours/reference over %d tensors: median %.4f min %.4f max %.4f'
+          % (tag, len(ratios), np.median(ratios), ratios.min(), ratios.max()))
+    assert abs(np.median(ratios) - 1) < 2e-2 and ratios.min() > 0.8 and ratios.max() < 1.25
+    worst = 1.0
+    for n in [str(x) for x in d[tag + '_full_names']]:
+        ours = H.subsample(params[n].grad.float().cpu())
+        cos = _cos(ours, d['%s_grad.%s' % (tag, n)])
+        worst = min(worst, cos)
+        assert cos > 0.98, (n, cos)
+        # after the first Adam step (beta1 = 0): w - lr * g / (|g| + eps); elements whose gradient is far above the
+        # bf16 noise moved by -lr * sign(g) exactly as in the reference
+        ref_after, ref_before = d['%s_after.%s' % (tag, n)], d['%s_before.%s' % (tag, n)]
+        ours_delta = H.subsample((after[n] - before[n]).float().cpu()).reshape(-1).numpy()
+        ref_delta = (ref_after - ref_before).reshape(-1)
+        g_ref = d['%s_grad.%s' % (tag, n)].reshape(-1)
+        strong = np.abs(g_ref) > 0.1 * np.abs(g_ref).max()
+        agree = np.mean(np.sign(ours_delta[strong]) == np.sign(ref_delta[strong]))
+        assert agree > 0.99, (n, agree)
+        assert np.abs(ours_delta).max() <= lr * 1.001
+    print('%s: worst gradient cosine over the fully stored tensors %.5f' % (tag, worst))
+
+
+@pytest.mark.parametrize('tag', ['a', 'b', 'c'])
+def test_adaptive_norm_vs_reference(tag):
+    """layers/activation_norm.py:22-106: forward, gradients of x / y / parameters, running statistics; sync_batch and
+    instance inner norms, joint and separate projections, spectral and plain linear layers."""
+    from types import SimpleNamespace
+    from imaginaire_b200 import functional as NF
+    from imaginaire_b200.layers.activation_norm import AdaptiveNorm
+    d = H.load_golden('adaptive_norm_%s.npz' % tag)
+    x0, y0 = torch.from_numpy(d['x']), torch.from_numpy(d['y'])
+    m = AdaptiveNorm(x0.shape[1], y0.shape[1], weight_norm_type=str(d['weight_norm_type']),
+                     separate_projection=bool(d['separate_projection']), activation_norm_type=str(d['norm_kind']),
+                     activation_norm_params=SimpleNamespace(affine=bool(d['affine'])))
+    m.load_state_dict(H.split_sd(d, 'sd.'), strict=True)
+    m = m.to(_dev()).train(bool(d['training']))
+    x = x0.to(_dev()).requires_grad_(True)
+    y = y0.to(_dev()).requires_grad_(True)
+    out = NF.to_nchw(m(x, y), x0.shape[1])
+    ref = torch.from_numpy(d['out'])
+    assert H.rel_err(out.detach().cpu(), ref) < 1e-2                   # bf16 storage of x and of the output
+    out.backward(torch.from_numpy(d['gout']).to(_dev()))
+    assert _rel_l2(x.grad.cpu(), d['gx']) < 2e-2
+    assert _rel_l2(y.grad.cpu(), d['gy']) < 2e-2
+    for n, p in m.named_parameters():
+        key = 'grad.' + n
+        if key in d:
+            assert p.grad is not None, n
+            assert _rel_l2(p.grad.cpu(), d[key]) < 3e-2, n
+    after = H.split_sd(d, 'sd_after.')
+    sd = m.state_dict()
+    for k in after:
+        if k.endswith(('running_mean', 'running_var', 'weight_u', 'weight_v')):
+            assert H.rel_err(sd[k].cpu(), after[k]) < 5e-3, k
+    with torch.no_grad():                                              # the no-grad path (fused kernels)
+        out2 = NF.to_nchw(m(x0.to(_dev()), y0.to(_dev())), x0.shape[1])
+    if not bool(d['training']):
+        assert H.rel_err(out2.cpu(), ref) < 1e-2

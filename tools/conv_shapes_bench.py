@@ -43,8 +43,8 @@ def main():
     batch = int(sys.argv[1]) if len(sys.argv) > 1 else 8
     cfg = Config(os.path.join(bench.ROOT, 'configs', bench.CONFIG_NAME))
     dev = torch.device('cuda:0')
-    net_G, net_D, opt_G, opt_D = get_model_optimizer_and_scheduler(cfg, seed=0, device=dev)
-    trainer = Trainer(cfg, net_G, net_D, opt_G, opt_D)
+    net_G, net_D, opt_G, opt_D, sch_G, sch_D = get_model_optimizer_and_scheduler(cfg, seed=0, device=dev)
+    trainer = Trainer(cfg, net_G, net_D, opt_G, opt_D, sch_G, sch_D, (), None)
     data = {k: v.to(dev) for k, v in bench.synthetic_batch(cfg, batch, 100).items()}
     trainer.step(dict(data))
     seen = {}

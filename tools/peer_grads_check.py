@@ -16,8 +16,8 @@ dev = torch.device('cuda', local)
 if world > 1:
     dist.init_process_group('nccl', init_method='env://')
 cfg = Config(os.path.join(bench.ROOT, 'configs', bench.CONFIG_NAME))
-net_G, net_D, opt_G, opt_D = get_model_optimizer_and_scheduler(cfg, seed=0, device=dev)
-trainer = Trainer(cfg, net_G, net_D, opt_G, opt_D)
+net_G, net_D, opt_G, opt_D, sch_G, sch_D = get_model_optimizer_and_scheduler(cfg, seed=0, device=dev)
+trainer = Trainer(cfg, net_G, net_D, opt_G, opt_D, sch_G, sch_D, (), None)
 data = {k: v.to(dev) for k, v in bench.synthetic_batch(cfg, 8, 100 + rank).items()}
 
 

@@ -15,8 +15,8 @@ dev = torch.device('cuda', local)
 if world > 1:
     import torch.distributed as dist
     dist.init_process_group('nccl', init_method='env://')
-net_G, net_D, opt_G, opt_D = get_model_optimizer_and_scheduler(cfg, seed=0, device=dev)
-trainer = Trainer(cfg, net_G, net_D, opt_G, opt_D)
+net_G, net_D, opt_G, opt_D, sch_G, sch_D = get_model_optimizer_and_scheduler(cfg, seed=0, device=dev)
+trainer = Trainer(cfg, net_G, net_D, opt_G, opt_D, sch_G, sch_D, (), None)
 data = {k: v.to(dev) for k, v in bench.synthetic_batch(cfg, int(sys.argv[1]) if len(sys.argv) > 1 else 8, 100).items()}
 for _ in range(2):
     trainer.step(dict(data))
