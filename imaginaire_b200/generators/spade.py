@@ -125,6 +125,11 @@ class Generator(nn.Module):
         return images, data['key']['seg_maps'][0]
 
 
+# Debugging aid (tools/generator_error_trace.py): set to a list to receive (block name, NHWC output) after every
+# block of SPADEGenerator.forward.
+TRACE = None
+
+
 class SPADEGenerator(nn.Module):
     def __init__(self, num_labels, out_image_small_side_size, image_channels, num_filters,
                  kernel_size, style_dims, activation_norm_params, weight_norm_type,
@@ -230,7 +235,15 @@ class SPADEGenerator(nn.Module):
                 x = blk.forward_native(x, (z,), None, stats_mode=mode)
             else:
                 x = blk.forward_native(x, (), None, stats_mode=mode)
+            if TRACE is not None:
+                TRACE.append((self._block_name(blk), x))
         return x
+
+    def _block_name(self, blk):
+        for name, child in self.named_children():
+            if child is blk:
+                return name
+        return type(blk).__name__
 
     def forward(self, data):
         seg = data['label']

@@ -121,8 +121,14 @@ def main():
     cfg.local_rank = 0
     cfg.logdir = '/tmp/imx_golden_logdir'
 
-    net_G, net_D, opt_G, opt_D, sch_G, sch_D = get_model_optimizer_and_scheduler(cfg, seed=SEED)
-    trainer = get_trainer(cfg, net_G, net_D, opt_G, opt_D, sch_G, sch_D, object(), None)
+    def build():
+        net_G, net_D, opt_G, opt_D, sch_G, sch_D = get_model_optimizer_and_scheduler(cfg, seed=SEED)
+        trainer = get_trainer(cfg, net_G, net_D, opt_G, opt_D, sch_G, sch_D, object(), None)
+        net_G.train()
+        net_D.train()
+        return trainer, net_G, net_D, opt_G
+
+    trainer, net_G, net_D, opt_G = build()
     G = trainer.net_G_module
     D = net_D.module
     out = {'g_sha256': np.array(state_dict_digest(G.state_dict())),
@@ -176,11 +182,26 @@ def main():
     fix_style_noise(G, eps_g)
     trainer.gen_update(data)
     for k, v in trainer.gen_losses.items():
+        out['seq_gen_loss.' + k] = v.detach().reshape(())
+    out['eps_dis'], out['eps_gen'] = eps_d, eps_g
+    out['seq_ema_num_updates'] = net_G.module.num_updates_tracked.detach().clone()
+
+    # ------------------------------------------------------------------ gen_update alone, from the initial state
+    # After its first Adam step (beta1 = 0: every weight moves by +-lr, whatever the size of its gradient) the
+    # discriminator is a discontinuous function of its gradients' signs, so the generator losses measured through it
+    # in the sequence above are comparable only loosely between two arithmetics.  The generator update is therefore
+    # also recorded against the INITIAL discriminator, where it can be held tightly.
+    trainer, net_G, net_D, opt_G = build()
+    G = trainer.net_G_module
+    g_before = {k: v.detach().clone() for k, v in G.state_dict().items()}
+    g_mid = g_before
+    fix_style_noise(G, eps_g)
+    trainer.gen_update(data)
+    for k, v in trainer.gen_losses.items():
         out['gen_loss.' + k] = v.detach().reshape(())
     g_grads = grads(G)
     g_after = {k: v.detach().clone() for k, v in G.state_dict().items()}
     ema_after = {k: v.detach().clone() for k, v in net_G.module.averaged_model.state_dict().items()}
-    out['eps_dis'], out['eps_gen'] = eps_d, eps_g
 
     # every parameter: gradient norm and norm of the update; a spread of tensors in full
     for tag, gr, before, after in (('d', d_grads, d_before, d_after), ('g', g_grads, g_before, g_after)):
@@ -219,7 +240,7 @@ def main():
     save('train_step_c3mini.npz', **out)
     for k in sorted(out):
         if 'loss' in k:
-            print('%-28s %.6f' % (k, float(out[k])))
+            print('%-32s %.6f' % (k, float(out[k])))
 
     # ------------------------------------------------------------------ AdaptiveNorm (activation_norm.py:22-106)
     from imaginaire.layers.activation_norm import AdaptiveNorm

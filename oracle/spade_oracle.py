@@ -33,6 +33,29 @@ def _q(t):
     return t if QUANT is None else QUANT(t)
 
 
+# Second emulation level: STORE (same kind of function) rounds every tensor the native pipeline keeps in HBM between
+# two kernels -- convolution outputs (after bias / activation / residual sum), gamma and beta when autograd
+# materialises them (STORE_GAMMA_BETA) -- on top of QUANT's rounding of the convolution operands.  QUANT alone is "one
+# rounding per convolution input"; QUANT + STORE is the rounding schedule of a bf16-storage pipeline in which the
+# normalisation statistics are not known when a convolution's output is written, so that output is rounded once when
+# stored and once more after the modulation.
+STORE = None
+STORE_GAMMA_BETA = True
+
+# Debugging aid: set to a list to receive (block name, output) after every block of spade_generator().
+TRACE = None
+
+
+def _s(t):
+    return t if STORE is None else STORE(t)
+
+
+def _trace(name, t):
+    if TRACE is not None:
+        TRACE.append((name, t.detach().clone()))
+    return t
+
+
 # --------------------------------------------------------------- primitives
 
 def nearest_resize(x, size):
@@ -75,10 +98,11 @@ def effective_weight(sd, prefix, training):
     return w / sigma
 
 
-def conv(sd, prefix, x, stride, padding, training):
+def conv(sd, prefix, x, stride, padding, training, store=True):
     """ref: imaginaire/layers/conv.py:93-104 (nn.Conv2d, zero padding)"""
-    return F.conv2d(_q(x), _q(effective_weight(sd, prefix, training)), sd.get(prefix + 'bias'), stride=stride,
-                    padding=padding)
+    y = F.conv2d(_q(x), _q(effective_weight(sd, prefix, training)), sd.get(prefix + 'bias'), stride=stride,
+                 padding=padding)
+    return _s(y) if store else y
 
 
 def linear(sd, prefix, x, training):
@@ -137,14 +161,15 @@ def spatially_adaptive_norm(sd, prefix, x, cond_inputs, p, training):
             hidden = label
             if p['num_filters'] > 0:
                 hidden = F.relu(conv(sd, mlp + '0.layers.conv.', label, 1, pad, training))
-            gamma = conv(sd, prefix + 'gammas.%d.layers.conv.' % i, hidden, 1, pad, training)
-            beta = conv(sd, prefix + 'betas.%d.layers.conv.' % i, hidden, 1, pad, training)
+            gamma = conv(sd, prefix + 'gammas.%d.layers.conv.' % i, hidden, 1, pad, training, store=STORE_GAMMA_BETA)
+            beta = conv(sd, prefix + 'betas.%d.layers.conv.' % i, hidden, 1, pad, training, store=STORE_GAMMA_BETA)
         else:
             hidden, k = label, 0
             if p['num_filters'] > 0:
                 hidden = F.relu(conv(sd, mlp + '0.layers.conv.', label, 1, pad, training))
                 k = 1
-            gamma, beta = conv(sd, mlp + '%d.layers.conv.' % k, hidden, 1, pad, training).chunk(2, dim=1)
+            gamma, beta = conv(sd, mlp + '%d.layers.conv.' % k, hidden, 1, pad, training,
+                               store=STORE_GAMMA_BETA).chunk(2, dim=1)
         out = out * (1 + gamma) + beta
     return out
 
@@ -167,7 +192,8 @@ def spade_res_block(sd, prefix, x, seg, p, training, kernel_size=3):
     dx = spatially_adaptive_norm(sd, prefix + 'conv_block_0.layers.norm.', x, [seg], p, training)
     dx = conv(sd, prefix + 'conv_block_0.layers.conv.', leaky_relu(dx), 1, pad, training)
     dx = spatially_adaptive_norm(sd, prefix + 'conv_block_1.layers.norm.', dx, [seg], p, training)
-    dx = conv(sd, prefix + 'conv_block_1.layers.conv.', leaky_relu(dx), 1, pad, training)
+    # the residual sum is formed on the fp32 accumulators of this convolution and stored once
+    dx = conv(sd, prefix + 'conv_block_1.layers.conv.', leaky_relu(dx), 1, pad, training, store=False)
     if (prefix + 'conv_block_s.layers.conv.weight_orig' in sd) or (prefix + 'conv_block_s.layers.conv.weight' in sd):
         xs = x
         if (prefix + 'conv_block_s.layers.norm.norm.weight' in sd) or \
@@ -176,7 +202,7 @@ def spade_res_block(sd, prefix, x, seg, p, training, kernel_size=3):
         xs = conv(sd, prefix + 'conv_block_s.layers.conv.', xs, 1, 0, training)   # no activation (:98-108)
     else:
         xs = x
-    return xs + dx
+    return _s(xs + dx)
 
 
 def style_encoder(sd, prefix, images, kernel_size, training, eps_noise):
@@ -220,16 +246,16 @@ def spade_generator(sd, seg, z, g, training, prefix='spade_generator.'):
         if g['use_style']:
             h = adaptive_norm(sd, prefix + 'cbn_%s.layers.norm.' % name, x, z, g['global_norm'],
                               p['separate_projection'], training)
-            return conv(sd, prefix + 'cbn_%s.layers.conv.' % name, leaky_relu(h), 1, pad, training)
-        return conv(sd, prefix + 'conv_%s.layers.conv.' % name, leaky_relu(x), 1, pad, training)
+            return _trace('cbn_' + name, conv(sd, prefix + 'cbn_%s.layers.conv.' % name, leaky_relu(h), 1, pad, training))
+        return _trace('conv_' + name, conv(sd, prefix + 'conv_%s.layers.conv.' % name, leaky_relu(x), 1, pad, training))
 
     def res(name, x):
-        return spade_res_block(sd, prefix + name + '.', x, seg, p, training, k)
+        return _trace(name, spade_res_block(sd, prefix + name + '.', x, seg, p, training, k))
 
     def to_rgb(name, x):
         return conv(sd, prefix + name + '.layers.conv.', leaky_relu(x), 1, 2, training)
 
-    x = leaky_relu(conv(sd, prefix + 'head_0.layers.conv.', in_seg, 1, pad, training))
+    x = _trace('head_0', leaky_relu(conv(sd, prefix + 'head_0.layers.conv.', in_seg, 1, pad, training)))
     x = mid('head_0', x)
     x = res('head_2', res('head_1', x))
     x = upsample2x(x)

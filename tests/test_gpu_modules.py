@@ -167,16 +167,18 @@ def test_generator_unit_test_vs_reference_golden():
     assert H.state_dict_digest(net.state_dict()) == str(d['state_dict_sha256'])
     label, images = H.unit_test_generator_inputs()
     ref = torch.from_numpy(d['fake_images']).float()
-    # inherent bf16 noise: the CPU oracle with conv operands (activations, weights) rounded to bf16
-    so.QUANT = lambda t: t.bfloat16().float()
+    # inherent bf16 noise: the CPU oracle with every tensor the pipeline keeps in HBM between kernels (convolution
+    # operands and outputs) rounded to bf16; profiles/r02_generator_error_trace.md shows the CUDA path on top of this
+    # emulation block by block (ratio 1.00 - 1.01)
+    so.QUANT = so.STORE = lambda t: t.bfloat16().float()
     try:
         emu = so.generator(net.state_dict(), {'label': label, 'images': images},
                            so.generator_spec_from_cfg(cfg.gen, (256, 256)), True, torch.from_numpy(d['eps']))
     finally:
-        so.QUANT = None
+        so.QUANT = so.STORE = None
     emu_diff = (emu['fake_images'] - ref).abs()
     emu_max, emu_mean = float(emu_diff.max()), float(emu_diff.mean())
-    print('bf16-operand oracle vs fp32 reference: max-abs %.4f mean-abs %.5f' % (emu_max, emu_mean))
+    print('bf16-storage oracle vs fp32 reference: max-abs %.4f mean-abs %.5f' % (emu_max, emu_mean))
     net = net.to(_dev()).train()
     for grad in (False, True):
         net.load_state_dict({k: v for k, v in H.build_generator('spade_unit_test.yaml')[1].state_dict().items()})
@@ -192,12 +194,13 @@ def test_generator_unit_test_vs_reference_golden():
         diff = (img - ref).abs()
         print('generator grad=%s: max-abs %.4f mean-abs %.5f' % (grad, float(diff.max()), float(diff.mean())))
         # Stated bf16 tolerance.  BASELINE.json's example figures (max-abs 2e-2 / mean-abs 2e-3)
-        # are below what bf16 storage itself allows for this randomly initialised network: the
-        # fp32 oracle with nothing but its conv operands rounded to bf16 already deviates from
-        # the fp32 reference by max-abs 6.6e-2 / mean-abs 7.7e-3 (measured below).  The bound
-        # is therefore "within 2x the inherent bf16-operand noise", plus absolute caps.
-        assert float(diff.max()) <= 0.15 and float(diff.mean()) <= 1.5e-2
-        assert float(diff.mean()) <= 2.0 * emu_mean and float(diff.max()) <= 2.5 * emu_max
+        # are below what bf16 itself allows for this randomly initialised network: the fp32
+        # oracle with nothing but its conv operands rounded to bf16 already deviates from the
+        # fp32 reference by max-abs 6.6e-2 / mean-abs 7.7e-3, with bf16 storage between kernels
+        # by 8.1e-2 / 1.0e-2.  The bound is "mean-abs within 1.1x, max-abs (one pixel of 196 608)
+        # within 1.5x of the bf16-storage emulation", plus absolute caps.
+        assert float(diff.max()) <= 0.15 and float(diff.mean()) <= 1.2e-2
+        assert float(diff.mean()) <= 1.1 * emu_mean and float(diff.max()) <= 1.5 * emu_max
         assert H.rel_err(out['mu'].cpu(), d['mu']) < 3e-2
 
 
