@@ -17,6 +17,7 @@
 // 2-D block (32 x 8 pixels) keeps the taps shared by neighbouring rows in L1.
 #include <type_traits>
 #include "imx_common.cuh"
+#include "warp_window.cuh"
 #include "../../include/imx.h"
 
 namespace {
@@ -413,6 +414,8 @@ extern "C" int imx_resample2d_fwd_f32(const float* img, const float* flow, float
     IMX_REQUIRE(B >= 0 && C >= 0 && H >= 0 && W >= 0, "resample2d_fwd: negative size");
     IMX_REQUIRE(Hi >= H && Wi >= W, "resample2d_fwd: image (%dx%d) smaller than flow (%dx%d)", Hi, Wi, H, W);
     if ((long)B * C * H * W == 0) return IMX_OK;
+    if (imx::warpwin::applicable(img, B, C, H, W, Hi, Wi))      // large launches: taps read from a staged window
+        return imx::warpwin::resample2d_fwd(img, flow, out, B, C, H, W, Hi, Wi, (cudaStream_t)stream);
     const int cpb = pick_channels_per_block(B, C, H, W);
     const int nchunk = (C + cpb - 1) / cpb;
     IMX_REQUIRE((long)B * nchunk <= 65535, "resample2d_fwd: batch*channel-chunks too large");
@@ -448,6 +451,8 @@ extern "C" int imx_gridsample_warp_fwd_f32(const float* img, const float* flow, 
     IMX_REQUIRE(B >= 0 && C >= 0 && H >= 0 && W >= 0, "gridsample_warp_fwd: negative size");
     if ((long)B * C * H * W == 0) return IMX_OK;
     IMX_REQUIRE(H >= 2 && W >= 2, "gridsample_warp_fwd: H and W must be >= 2");
+    if (imx::warpwin::applicable(img, B, C, H, W, H, W))
+        return imx::warpwin::gridsample_fwd(img, flow, out, B, C, H, W, (cudaStream_t)stream);
     const int cpb = pick_channels_per_block(B, C, H, W);
     const int nchunk = (C + cpb - 1) / cpb;
     IMX_REQUIRE((long)B * nchunk <= 65535, "gridsample_warp_fwd: batch*channel-chunks too large");

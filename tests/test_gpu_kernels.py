@@ -53,6 +53,28 @@ def test_resample2d_forward_bit_exact_vs_oracle(shape):
     assert np.array_equal(out, ref)                                          # and in fact bit-exact
 
 
+@pytest.mark.parametrize('shape,scale', [((1, 16, 512, 1024), 8.0), ((2, 9, 500, 1028), 8.0), ((1, 16, 512, 1024), 24.0),
+                                         ((1, 16, 512, 1024), 0.0)])
+@pytest.mark.parametrize('which', ['resample2d', 'gridsample'])
+def test_warp_forward_through_the_shared_memory_window_is_bit_exact(shape, scale, which):
+    """Large launches read their taps from a TMA-staged source window (csrc/warp_window.cu): same arithmetic, so
+    still bit-exact.  The flows cover all three box sizes (scale 0 / 8 / 24 px), ragged tiles (H = 500), and tiles
+    whose taps fit no box (the out-of-range rows of the SURVEY flow set) that fall back to per-pixel gathers."""
+    from imaginaire_b200 import ops
+    from imaginaire_b200.model_utils.fs_vid2vid import resample
+    b, c, h, w = shape
+    g = torch.Generator().manual_seed(21)
+    img = torch.randn(b, c, h, w, generator=g)
+    flow = H.synthetic_flow(22, b, h, w, scale=scale)
+    if which == 'resample2d':
+        out = ops.resample2d_fwd(img.to(DEV), flow.to(DEV)).cpu().numpy()
+        ref = wo.resample2d_forward(img.numpy(), flow.numpy())
+    else:
+        out = resample(img.to(DEV), flow.to(DEV)).cpu().numpy()
+        ref = wo.gridsample_warp_forward(img.numpy(), flow.numpy())
+    assert np.array_equal(out, ref)
+
+
 def test_resample2d_empty_and_invalid():
     from imaginaire_b200 import ops, _C
     out = ops.resample2d_fwd(torch.zeros(0, 3, 8, 8, device=DEV), torch.zeros(0, 2, 8, 8, device=DEV))

@@ -267,8 +267,11 @@ def _check_grads_and_update(tag, d, params, before, after, lr):
         print('%s: gradient cosine %.5f  %s' % (tag, cos, n))
         # bf16 storage of the activation gradients costs direction on the way back through the 13 blocks: the fp32
         # oracle with its stored tensors and their gradients rounded to bf16 loses the same amount
-        # (profiles/r02_generator_grad_trace.md, CUDA vs emulation parameter by parameter)
-        bad += [] if cos > (0.98 if tag == 'd' else 0.88) else [(n, cos)]
+        # (profiles/r02_generator_grad_trace.md, CUDA vs emulation parameter by parameter: 0.97 at the head for a
+        # linear loss; through the GAN / feature-matching / VGG losses 0.93-0.94, and 0.85-0.90 run to run for
+        # 16-element bias vectors)
+        floor = 0.98 if tag == 'd' else (0.9 if ref_grad.size > 64 else 0.75)
+        bad += [] if cos > floor else [(n, cos)]
         # after the first Adam step (beta1 = 0): w - lr * g / (|g| + eps); elements whose gradient is far above the
         # bf16 noise moved by -lr * sign(g) exactly as in the reference
         ref_after, ref_before = d['%s_after.%s' % (tag, n)], d['%s_before.%s' % (tag, n)]
