@@ -15,6 +15,7 @@
 // per pixel, not once per channel as in the reference); consecutive lanes own
 // consecutive x so flow loads / output stores are 128-byte coalesced, and the
 // 2-D block (32 x 8 pixels) keeps the taps shared by neighbouring rows in L1.
+#include <cstdlib>
 #include <type_traits>
 #include "imx_common.cuh"
 #include "warp_window.cuh"
@@ -414,8 +415,13 @@ extern "C" int imx_resample2d_fwd_f32(const float* img, const float* flow, float
     IMX_REQUIRE(B >= 0 && C >= 0 && H >= 0 && W >= 0, "resample2d_fwd: negative size");
     IMX_REQUIRE(Hi >= H && Wi >= W, "resample2d_fwd: image (%dx%d) smaller than flow (%dx%d)", Hi, Wi, H, W);
     if ((long)B * C * H * W == 0) return IMX_OK;
-    if (imx::warpwin::applicable(img, B, C, H, W, Hi, Wi))      // large launches: taps read from a staged window
-        return imx::warpwin::resample2d_fwd(img, flow, out, B, C, H, W, Hi, Wi, (cudaStream_t)stream);
+    {
+        // the shared-memory window does not pay for this arithmetic (three double-precision products per element,
+        // see warp_window.cu); kept behind a switch for measurements
+        const char* on = getenv("IMX_WARPWIN_R2D");
+        if (on && on[0] == '1' && imx::warpwin::applicable(img, B, C, H, W, Hi, Wi))
+            return imx::warpwin::resample2d_fwd(img, flow, out, B, C, H, W, Hi, Wi, (cudaStream_t)stream);
+    }
     const int cpb = pick_channels_per_block(B, C, H, W);
     const int nchunk = (C + cpb - 1) / cpb;
     IMX_REQUIRE((long)B * nchunk <= 65535, "resample2d_fwd: batch*channel-chunks too large");

@@ -16,9 +16,20 @@
 // per-pixel gathers for that tile only.  Arithmetic per output element is exactly that of warp.cu (bit-exact with
 // the oracles): the window only changes where a tap is read from.
 //
+// Measured (B=8, C=64, 512x1024, fraction of the 6544 GB/s HBM peak; profiles/r02_warp_window.md):
+//   grid_sample form   smooth flows (8 px on an 8x16 .. 1x1 grid) 0.67-0.76 against 0.57-0.65 per pixel; on the SURVEY
+//                      flow (8 px on a 32x64 grid, |d flow| ~0.5-0.7 px per px with as much shear) half the tiles fit
+//                      no box and the result is the per-pixel kernel's 0.47
+//   resample2d form    slower than the per-pixel kernel on every flow (0.40-0.55 against 0.48-0.61): its three
+//                      double-precision products per element cost six F2F conversions, and with four pixels per thread
+//                      they wait on the shared-memory reads in a block (96 registers, 2 CTAs per SM).  The entry point
+//                      in warp.cu therefore keeps the per-pixel kernel for resample2d; the instantiation stays for
+//                      IMX_WARPWIN_R2D=1 experiments.
+//
 // Tensor maps cover this GPU's image tensor only.
 #include <cuda.h>
 #include <climits>
+#include <cstdlib>
 #include <type_traits>
 #include "imx_common.cuh"
 #include "imx_ptx.cuh"
@@ -35,12 +46,13 @@ constexpr int PPT = 4;                   // pixels per thread (rows ty, ty + 4, 
 constexpr int CONSUMERS = 256;           // 8 warps
 constexpr int THREADS = CONSUMERS + 32;  // + the producer warp
 constexpr int STAGES = 4;
-constexpr int NBOX = 3;
-// Box k holds a stretch of up to ~1.1 / 1.35 / 1.6 px per px in x and more in y (plus the +1 tap and alignment).
-__host__ __device__ constexpr int box_w(int k) { return k == 0 ? 72 : (k == 1 ? 88 : 104); }
-__host__ __device__ constexpr int box_h(int k) { return k == 0 ? 20 : (k == 1 ? 24 : 28); }
-constexpr int STAGE_FLOATS = box_w(NBOX - 1) * box_h(NBOX - 1);   // 2912 floats = 11.4 KB
-constexpr int SMEM_BYTES = STAGES * STAGE_FLOATS * 4 + 1024;
+// Box (i, j) = width i x height j: widths hold a stretch of up to ~1.05 / 1.3 / 1.55 px per px in x (plus the +1 tap and
+// the 16-byte alignment of the box start), heights ~1.2 / 1.45 / 1.7 in y.  Width and height are chosen independently.
+constexpr int NBW = 3, NBH = 3, NBOX = NBW * NBH;
+__host__ __device__ constexpr int box_w(int i) { return i == 0 ? 72 : (i == 1 ? 88 : 104); }
+__host__ __device__ constexpr int box_h(int j) { return j == 0 ? 20 : (j == 1 ? 24 : 28); }
+constexpr int STAGE_FLOATS = box_w(NBW - 1) * box_h(NBH - 1);   // 2912 floats = 11.4 KB
+constexpr int SMEM_BYTES = STAGES * STAGE_FLOATS * 4;
 
 struct Maps {
     CUtensorMap m[NBOX];
@@ -126,8 +138,8 @@ template <class S>
 __global__ void __launch_bounds__(THREADS, std::is_same<S, R2DSampler>::value ? 2 : 3)
 warp_fwd_window_kernel(const __grid_constant__ Maps maps, const float* __restrict__ img, const float* __restrict__ flow,
                        float* __restrict__ out, int C, int H, int W, int Hi, int Wi, int cpb, int nchunk) {
-    extern __shared__ uint8_t smem_raw[];
-    float* ring = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+    // No integer round-trip on this pointer: the tap reads must stay LDS (shared state space), not generic loads.
+    extern __shared__ __align__(128) float ring[];
     __shared__ uint64_t full[STAGES], empty[STAGES];
     __shared__ int red[8][4];
     __shared__ int win[4];   // x0, y0, box index (-1: no box fits), unused
@@ -142,6 +154,7 @@ warp_fwd_window_kernel(const __grid_constant__ Maps maps, const float* __restric
     const size_t hw = (size_t)H * W, hwi = (size_t)Hi * Wi;
 
     if (tid == 0) {
+        if (ptx::smem_u32(ring) & 127u) __trap();      // TMA destinations sit on 128-byte boundaries
 #pragma unroll
         for (int s = 0; s < STAGES; ++s) {
             ptx::mbar_init(&full[s], 1);
@@ -187,13 +200,17 @@ warp_fwd_window_kernel(const __grid_constant__ Maps maps, const float* __restric
             x0 = min(x0, red[w][0]); x1 = max(x1, red[w][1]);
             y0 = min(y0, red[w][2]); y1 = max(y1, red[w][3]);
         }
-        int k = -1;
+        int bi = -1, bj = -1;
         if (x0 <= x1) {
+            x0 &= ~3;       // the box must start on a 16-byte boundary of the row (TMA's global address granularity)
 #pragma unroll
-            for (int q = NBOX - 1; q >= 0; --q)
-                if (x1 - x0 < box_w(q) && y1 - y0 < box_h(q)) k = q;
+            for (int q = NBW - 1; q >= 0; --q)
+                if (x1 - x0 < box_w(q)) bi = q;
+#pragma unroll
+            for (int q = NBH - 1; q >= 0; --q)
+                if (y1 - y0 < box_h(q)) bj = q;
         }
-        win[0] = x0; win[1] = y0; win[2] = k;
+        win[0] = x0; win[1] = y0; win[2] = (bi < 0 || bj < 0) ? -1 : bi * NBH + bj;
     }
     __syncthreads();
     const int wx0 = win[0], wy0 = win[1], kbox = win[2];
@@ -216,15 +233,18 @@ warp_fwd_window_kernel(const __grid_constant__ Maps maps, const float* __restric
         }
         return;
     }
-    const int pitch = box_w(kbox);
-    const uint32_t stage_bytes = (uint32_t)(pitch * box_h(kbox) * 4);
+    const int pitch = box_w(kbox / NBH);
+    const uint32_t stage_bytes = (uint32_t)(pitch * box_h(kbox % NBH) * 4);
 
     if (warp == CONSUMERS / 32) {
         // ---- producer: one bulk tensor copy per channel into the ring
         if (lane == 0) {
             // constant indices only: a dynamically indexed kernel parameter is copied to local memory, and a tensor
             // map must be read from parameter / constant / global space
-            const CUtensorMap* m = kbox == 0 ? &maps.m[0] : (kbox == 1 ? &maps.m[1] : &maps.m[2]);
+            const CUtensorMap* m = &maps.m[0];
+#pragma unroll
+            for (int q = 1; q < NBOX; ++q)
+                if (kbox == q) m = &maps.m[q];
             ptx::prefetch_tmap(m);
             for (int c = c0, it = 0; c < c1; ++c, ++it) {
                 const int s = it % STAGES;
@@ -280,6 +300,8 @@ static int encode_f32_box(CUtensorMap* m, const float* base, int Wi, int Hi, lon
 bool applicable(const float* img, int B, int C, int H, int W, int Hi, int Wi) {
     // TMA needs 16-byte aligned rows; small problems keep the per-pixel kernels (a 64 x 16 tile per CTA would leave
     // most SMs idle, and the window pays off over many channels only)
+    const char* off = getenv("IMX_WARPWIN");        // IMX_WARPWIN=0: per-pixel kernels only (A/B measurements)
+    if (off && off[0] == '0') return false;
     if ((Wi & 3) || !aligned16(img) || C < 8) return false;
     if ((long)B * C * H * W < (8L << 20)) return false;
     return true;
@@ -290,7 +312,7 @@ static int launch(const float* img, const float* flow, float* out, int B, int C,
                   cudaStream_t stream) {
     Maps maps;
     for (int k = 0; k < NBOX; ++k) {
-        int rc = encode_f32_box(&maps.m[k], img, Wi, Hi, (long)B * C, box_w(k), box_h(k));
+        int rc = encode_f32_box(&maps.m[k], img, Wi, Hi, (long)B * C, box_w(k / NBH), box_h(k % NBH));
         if (rc != IMX_OK) return rc;
     }
     static bool attr_set[kMaxDevices] = {};
@@ -298,8 +320,13 @@ static int launch(const float* img, const float* flow, float* out, int B, int C,
     cudaError_t e = ensure_dyn_smem(kern, SMEM_BYTES, attr_set);
     if (e != cudaSuccess) return set_error((int)e, "warp window: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     const long tiles = (long)B * ((H + TH - 1) / TH) * ((W + TW - 1) / TW);
-    int cpb = C;
-    while (cpb > 16 && tiles * ((C + cpb - 1) / cpb) < 3L * num_sms()) cpb = (cpb + 1) / 2;
+    // Channels per CTA.  Few: the CTAs of one wave then work on the same channels of neighbouring tiles at the same
+    // time, so the overlap of their windows (2-3x the tile) is served by L2; with all 64 channels in one CTA the
+    // CTAs drift apart after the first wave and DRAM reads grew to 1.5-2.4x the algorithmic bytes (ncu).  Many: the
+    // per-CTA set-up (flow tile, taps, bounding box, pipeline fill) is amortised.
+    const char* cpb_env = getenv("IMX_WARPWIN_CPB");
+    int cpb = cpb_env ? atoi(cpb_env) : 32;
+    if (cpb < 1 || cpb > C) cpb = C;
     const int nchunk = (C + cpb - 1) / cpb;
     if ((long)B * nchunk > 65535) return set_error(IMX_ERR_TOO_LARGE, "warp window: batch*channel-chunks too large");
     dim3 grid((W + TW - 1) / TW, (H + TH - 1) / TH, B * nchunk);

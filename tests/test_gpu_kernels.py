@@ -56,12 +56,13 @@ def test_resample2d_forward_bit_exact_vs_oracle(shape):
 @pytest.mark.parametrize('shape,scale', [((1, 16, 512, 1024), 8.0), ((2, 9, 500, 1028), 8.0), ((1, 16, 512, 1024), 24.0),
                                          ((1, 16, 512, 1024), 0.0)])
 @pytest.mark.parametrize('which', ['resample2d', 'gridsample'])
-def test_warp_forward_through_the_shared_memory_window_is_bit_exact(shape, scale, which):
+def test_warp_forward_through_the_shared_memory_window_is_bit_exact(shape, scale, which, monkeypatch):
     """Large launches read their taps from a TMA-staged source window (csrc/warp_window.cu): same arithmetic, so
     still bit-exact.  The flows cover all three box sizes (scale 0 / 8 / 24 px), ragged tiles (H = 500), and tiles
     whose taps fit no box (the out-of-range rows of the SURVEY flow set) that fall back to per-pixel gathers."""
     from imaginaire_b200 import ops
     from imaginaire_b200.model_utils.fs_vid2vid import resample
+    monkeypatch.setenv('IMX_WARPWIN_R2D', '1')     # resample2d keeps the per-pixel kernel by default; test both
     b, c, h, w = shape
     g = torch.Generator().manual_seed(21)
     img = torch.randn(b, c, h, w, generator=g)

@@ -58,6 +58,20 @@ def hbm():
     torch.cuda.synchronize()
 
 
+def warp():
+    """The flow warps alone at B=8, C=64, 512x1024 on the SURVEY flow."""
+    torch.manual_seed(0)
+    img = torch.randn(8, 64, 512, 1024, device='cuda')
+    flow = torch.nn.functional.interpolate(torch.randn(8, 2, 32, 64, device='cuda') * 8.0, size=(512, 1024),
+                                           mode='bilinear', align_corners=False).contiguous()
+    go = torch.randn(8, 64, 512, 1024, device='cuda')
+    for _ in range(2):
+        ops.resample2d_fwd(img, flow)
+        ops.gridsample_warp_fwd(img, flow)
+        ops.resample2d_bwd(img, flow, go)
+    torch.cuda.synchronize()
+
+
 def epi():
     """Epilogue-dominated convs: 1x1 256->512, 5x5 64->128, 3x3 512->512 with statistics + residual."""
     torch.manual_seed(0)
@@ -80,5 +94,5 @@ def epi():
 
 
 if __name__ == '__main__':
-    {'conv': conv, 'hbm': hbm, 'epi': epi}[sys.argv[1]]()
+    {'conv': conv, 'hbm': hbm, 'epi': epi, 'warp': warp}[sys.argv[1]]()
     print('ok')
