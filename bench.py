@@ -36,6 +36,7 @@ def parse_args():
     ap.add_argument('--config', default=CONFIG_NAME)
     ap.add_argument('--batch', type=int, default=None, help='per-GPU batch override (debugging only)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-graph', action='store_true', help='single-GPU run: time the eager loop instead of the CUDA-graph replay')
     ap.add_argument('--no-clocks', action='store_true', help='do not spawn the nvidia-smi clock sampler (ncu runs)')
     ap.add_argument('--one-step', action='store_true',
                     help='profiling aid: run exactly one training iteration (after --warmup) and exit, '
@@ -303,6 +304,17 @@ def run_ours(args):
 
     for _ in range(args.warmup):
         one_step(resident)
+    # One process, one GPU: the iteration is captured once as a CUDA graph and replayed (utils/cuda_graph.py); every
+    # call still copies its batch into the graph's input tensors.  Data-parallel runs keep the eager loop.
+    use_graph = world == 1 and not args.no_graph and os.environ.get('IMX_BENCH_GRAPH', '1') != '0' and not args.one_step
+    if use_graph:
+        from imaginaire_b200.utils.cuda_graph import GraphedTrainerStep
+        graphed = GraphedTrainerStep(trainer, resident)
+        eager_step = one_step
+
+        def one_step(data):     # noqa: F811
+            return graphed(data)
+        one_step(resident)      # capture + first replay, untimed
     if args.one_step:
         torch.cuda.synchronize()
         one_step(resident)
@@ -337,7 +349,8 @@ def run_ours(args):
     start.record()
     d2h = 0
     for _ in range(args.steps):
-        data = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+        # eager: fresh device tensors from the pinned host batch; graphed: the same copies, into the graph's inputs
+        data = host if use_graph else {k: v.to(dev, non_blocking=True) for k, v in host.items()}
         g_loss, d_loss = one_step(data)
         losses = torch.stack([g_loss.reshape(()), d_loss.reshape(())]).cpu()   # device -> host read of the step's result
         d2h = losses.numel() * losses.element_size()
@@ -353,6 +366,8 @@ def run_ours(args):
     # ---- roofline of the dominant kernel family: one more iteration with per-launch CUDA events ----
     # An un-probed iteration is queued first and NOT waited for, so the device stays backlogged while the probed
     # one is enqueued: each start event then fires when the previous kernel ends, not when the host got there.
+    if use_graph:
+        one_step = eager_step       # per-launch events need the eager loop
     one_step(resident)
     probe = ConvProbe()
     probe.install()
@@ -391,7 +406,7 @@ def run_ours(args):
         'config': {'workload': 'SPADE G+D training step (BASELINE configs[2]): base128 generator + SPADE discriminator, '
                                '256x512, 35-class one-hot labels, batch %d/GPU, SyncBN, Adam, EMA' % batch,
                    'config_file': 'configs/' + args.config, 'global_batch': world * batch,
-                   'parallelism': 'dp%d' % world, 'l2': 'working set (GBs of activations per step) is far larger than the 126 MB L2; no explicit flush'},
+                   'parallelism': 'dp%d' % world, 'cuda_graph': bool(use_graph), 'l2': 'working set (GBs of activations per step) is far larger than the 126 MB L2; no explicit flush'},
         'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d_bytes, 'd2h_bytes_per_step': d2h,
                 'ms_per_step': ms_e2e / args.steps},
         'gpu_launches': launches,

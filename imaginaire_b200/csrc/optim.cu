@@ -41,6 +41,13 @@ struct AdamHyper {
     float eps, weight_decay;
 };
 
+// Step counters on the device (imx_adam_multi_tensor_f32_capturable): the bias corrections are formed in the kernel
+// from the counter of the tensor, so that one captured launch stays valid as the counters advance.
+struct AdamDevSteps {
+    const float* step[kMaxTensors];   // null table entry: unused
+    double lr, beta1, beta2;
+};
+
 __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, const AdamHyper& h) {
     if (h.weight_decay != 0.0f) g = fmaf(h.weight_decay, p, g);
     m = h.omb1 == 1.0f ? g : fmaf(h.omb1, g - m, m);     // lerp(m, g, 1 - beta1); exact for beta1 = 0
@@ -49,9 +56,17 @@ __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, 
     p -= h.lr_over_bc1 * (m / denom);
 }
 
+template <bool kDevStep>
 __global__ void __launch_bounds__(kThreadsOpt)
-adam_multi_tensor_kernel(const __grid_constant__ AdamBatch b, const AdamHyper h) {
+adam_multi_tensor_kernel(const __grid_constant__ AdamBatch b, AdamHyper h, const __grid_constant__ AdamDevSteps ds) {
     const int t = b.blk_tensor[blockIdx.x];
+    if (kDevStep) {
+        // same double-precision formulas as the host path (one evaluation per thread: a few hundred cycles against
+        // the 32768-element chunk the CTA streams)
+        const double step = (double)__ldg(ds.step[t]);
+        h.lr_over_bc1 = (float)(ds.lr / (1.0 - pow(ds.beta1, step)));
+        h.inv_sqrt_bc2 = (float)(1.0 / sqrt(1.0 - pow(ds.beta2, step)));
+    }
     const long long n = b.n[t];
     const long long base = (long long)b.blk_chunk[blockIdx.x] * kChunk;
     const long long end = base + kChunk < n ? base + kChunk : n;
@@ -85,20 +100,20 @@ adam_multi_tensor_kernel(const __grid_constant__ AdamBatch b, const AdamHyper h)
 
 }  // namespace
 
-extern "C" int imx_adam_multi_tensor_f32(const void* const* params, const void* const* grads,
-                                         const void* const* exp_avg, const void* const* exp_avg_sq,
-                                         const int64_t* numel, int n_tensors,
-                                         double lr, double beta1, double beta2, double eps, double weight_decay,
-                                         int64_t step, imx_stream_t stream) {
+// steps == nullptr: `step` is the host-side step number; else steps[i] is tensor i's device counter.
+static int adam_launch(const void* const* params, const void* const* grads, const void* const* exp_avg,
+                       const void* const* exp_avg_sq, const void* const* steps, const int64_t* numel, int n_tensors,
+                       double lr, double beta1, double beta2, double eps, double weight_decay, int64_t step,
+                       imx_stream_t stream) {
     IMX_REQUIRE(n_tensors >= 0, "adam_multi_tensor: negative tensor count");
     if (n_tensors == 0) return IMX_OK;
     IMX_REQUIRE(params && grads && exp_avg && exp_avg_sq && numel, "adam_multi_tensor: null pointer table");
-    IMX_REQUIRE(step >= 1, "adam_multi_tensor: step counts from 1 (got %lld)", (long long)step);
+    IMX_REQUIRE(steps || step >= 1, "adam_multi_tensor: step counts from 1 (got %lld)", (long long)step);
     IMX_REQUIRE(beta1 >= 0.0 && beta1 < 1.0 && beta2 >= 0.0 && beta2 < 1.0 && eps >= 0.0 && lr >= 0.0,
                 "adam_multi_tensor: bad hyper-parameters");
     AdamHyper h;
-    const double bc1 = 1.0 - pow(beta1, (double)step);
-    const double bc2 = 1.0 - pow(beta2, (double)step);
+    const double bc1 = steps ? 1.0 : 1.0 - pow(beta1, (double)step);
+    const double bc2 = steps ? 1.0 : 1.0 - pow(beta2, (double)step);
     h.lr_over_bc1 = (float)(lr / bc1);
     h.inv_sqrt_bc2 = (float)(1.0 / sqrt(bc2));
     h.omb1 = (float)(1.0 - beta1); h.beta2 = (float)beta2; h.omb2 = (float)(1.0 - beta2);
@@ -106,10 +121,13 @@ extern "C" int imx_adam_multi_tensor_f32(const void* const* params, const void* 
     cudaStream_t s = (cudaStream_t)stream;
 
     AdamBatch b;
+    AdamDevSteps ds;
+    ds.lr = lr; ds.beta1 = beta1; ds.beta2 = beta2;
     int nt = 0, nb = 0;
     auto flush = [&]() -> int {
         if (nb == 0) return IMX_OK;
-        adam_multi_tensor_kernel<<<nb, kThreadsOpt, 0, s>>>(b, h);
+        if (steps) adam_multi_tensor_kernel<true><<<nb, kThreadsOpt, 0, s>>>(b, h, ds);
+        else adam_multi_tensor_kernel<false><<<nb, kThreadsOpt, 0, s>>>(b, h, ds);
         nt = 0; nb = 0;
         return imx::check_launch("adam_multi_tensor");
     };
@@ -129,6 +147,8 @@ extern "C" int imx_adam_multi_tensor_f32(const void* const* params, const void* 
             b.p[slot] = (float*)params[i]; b.g[slot] = (const float*)grads[i];
             b.m[slot] = (float*)exp_avg[i]; b.v[slot] = (float*)exp_avg_sq[i];
             b.n[slot] = n;
+            ds.step[slot] = steps ? (const float*)steps[i] : nullptr;
+            if (steps) IMX_REQUIRE(steps[i] != nullptr, "adam_multi_tensor: null step counter for tensor %d", i);
             while (c < chunks && nb < kMaxBlocks) {
                 b.blk_tensor[nb] = (unsigned char)slot;
                 b.blk_chunk[nb] = (int)c;
@@ -137,4 +157,23 @@ extern "C" int imx_adam_multi_tensor_f32(const void* const* params, const void* 
         }
     }
     return flush();
+}
+
+extern "C" int imx_adam_multi_tensor_f32(const void* const* params, const void* const* grads,
+                                         const void* const* exp_avg, const void* const* exp_avg_sq,
+                                         const int64_t* numel, int n_tensors,
+                                         double lr, double beta1, double beta2, double eps, double weight_decay,
+                                         int64_t step, imx_stream_t stream) {
+    return adam_launch(params, grads, exp_avg, exp_avg_sq, nullptr, numel, n_tensors, lr, beta1, beta2, eps, weight_decay,
+                       step, stream);
+}
+
+extern "C" int imx_adam_multi_tensor_f32_capturable(const void* const* params, const void* const* grads,
+                                                    const void* const* exp_avg, const void* const* exp_avg_sq,
+                                                    const void* const* steps, const int64_t* numel, int n_tensors,
+                                                    double lr, double beta1, double beta2, double eps,
+                                                    double weight_decay, imx_stream_t stream) {
+    IMX_REQUIRE(steps, "adam_multi_tensor_capturable: null step-counter table");
+    return adam_launch(params, grads, exp_avg, exp_avg_sq, steps, numel, n_tensors, lr, beta1, beta2, eps, weight_decay, 0,
+                       stream);
 }

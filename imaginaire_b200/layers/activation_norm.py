@@ -35,6 +35,10 @@ def _frozen_identity_affine(weight, bias):
     reads the device once per tensor version."""
     if weight is None or bias is None or weight.requires_grad or bias.requires_grad or not weight.is_cuda:
         return False
+    if getattr(weight, '_imx_trained', False) or getattr(bias, '_imx_trained', False):
+        # the optimizer has moved them (the reference's trainer unfreezes every generator parameter for the
+        # generator update, trainers/base.py:602): no longer (1, 0), and no device read-back per step to find out
+        return False
     hit = getattr(weight, '_imx_identity_affine', None)     # cached on the tensor: dies with it
     if hit is None or hit[0] != weight._version or hit[1] != bias._version or hit[2] is not bias:
         with torch.no_grad():

@@ -68,10 +68,27 @@ class ModelAverage(nn.Module):
                 sn.append((t, src[key], None, None))   # integer buffers: plain copy
         self._pairs = (plain_t, plain_s, sn)
 
-    @torch.no_grad()
-    def update_average(self):
+    def _sync_steps(self):
         if self._steps is None:
             self._steps = int(self.num_updates_tracked.item())
+
+    def next_beta(self):
+        """beta the NEXT update_average() will use (utils/cuda_graph.py keys its captured iteration on it)."""
+        self._sync_steps()
+        return 0.0 if self._steps + 1 <= self.start_iteration else self.beta
+
+    def note_graph_replay(self):
+        """A captured update_average() has run on the device: advance the host mirror of num_updates_tracked."""
+        self._sync_steps()
+        self._steps += 1
+        if not self.num_updates_tracked.is_cuda:
+            # the reference builds ModelAverage after the network went to the GPU and never moves it (utils/trainer.py
+            # :93-141): the counter is a host tensor, and a captured `+= 1` on it ran only at capture time
+            self.num_updates_tracked += 1
+
+    @torch.no_grad()
+    def update_average(self):
+        self._sync_steps()
         self.num_updates_tracked += 1
         self._steps += 1
         beta = 0.0 if self._steps <= self.start_iteration else self.beta

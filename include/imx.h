@@ -485,6 +485,17 @@ IMX_API int imx_adam_multi_tensor_f32(const void* const* params, const void* con
                               double lr, double beta1, double beta2, double eps, double weight_decay,
                               int64_t step, imx_stream_t stream);
 
+/* The same step with the step numbers on the DEVICE: steps[i] points to tensor i's counter (one fp32, already
+ * incremented for this update, as torch.optim.Adam(capturable=True) keeps it); the bias corrections are formed in
+ * the kernel.  A launch of this entry point captured in a CUDA graph stays valid as the counters advance (the host
+ * number baked into imx_adam_multi_tensor_f32's arguments would not).
+ * ref: same as imx_adam_multi_tensor_f32 */
+IMX_API int imx_adam_multi_tensor_f32_capturable(const void* const* params, const void* const* grads,
+                                                 const void* const* exp_avg, const void* const* exp_avg_sq,
+                                                 const void* const* steps, const int64_t* numel, int n_tensors,
+                                                 double lr, double beta1, double beta2, double eps,
+                                                 double weight_decay, imx_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

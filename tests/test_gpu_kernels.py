@@ -488,6 +488,33 @@ def test_bilinear_up2x_add_vs_torch(shape):
     assert H.rel_err(only_up.float().cpu(), F.interpolate(src, scale_factor=2, mode='bilinear', align_corners=False)) < 4e-3
 
 
+def test_fused_adam_device_step_counters_match_torch_adam():
+    """FusedAdam(capturable=True): step numbers on the device, bias corrections formed in the kernel
+    (imx_adam_multi_tensor_f32_capturable) -- the form a CUDA-graph replay needs.  Five steps against torch.optim.Adam;
+    an optimizer that already stepped with host counters converts with make_capturable()."""
+    from imaginaire_b200.optim import FusedAdam
+    g = torch.Generator().manual_seed(71)
+    shapes = [(64, 32, 3, 3), (128,), (7, 5), (40000,)]
+    ps = [torch.randn(*s, generator=g) for s in shapes]
+    ours = [torch.nn.Parameter(p.clone().to(DEV)) for p in ps]
+    mixed = [torch.nn.Parameter(p.clone().to(DEV)) for p in ps]
+    ref = [torch.nn.Parameter(p.clone().to(DEV)) for p in ps]
+    kw = dict(lr=3e-3, betas=(0.5, 0.99), eps=1e-8)
+    o1, o2, o3 = FusedAdam(ours, capturable=True, **kw), FusedAdam(mixed, **kw), torch.optim.Adam(ref, **kw)
+    for it in range(5):
+        if it == 2:
+            o2.make_capturable()
+        for a, m, r in zip(ours, mixed, ref):
+            grad = torch.randn(a.shape, generator=g).to(DEV)
+            a.grad, m.grad, r.grad = grad.clone(), grad.clone(), grad.clone()
+        o1.step(); o2.step(); o3.step()
+    for a, m, r in zip(ours, mixed, ref):
+        assert H.rel_err(a.detach().cpu(), r.detach().cpu()) < 2e-6
+        assert H.rel_err(m.detach().cpu(), r.detach().cpu()) < 2e-6
+    st = o1.state[ours[0]]['step']
+    assert st.is_cuda and float(st) == 5.0 and float(o2.state[mixed[0]]['step']) == 5.0
+
+
 # ------------------------------------------------- FlowNet2 operators
 
 @pytest.mark.parametrize('shape', [(2, 3, 17, 23), (1, 2, 64, 96), (3, 64, 5, 7), (1, 1, 1, 1)])
