@@ -304,9 +304,13 @@ def run_ours(args):
 
     for _ in range(args.warmup):
         one_step(resident)
-    # One process, one GPU: the iteration is captured once as a CUDA graph and replayed (utils/cuda_graph.py); every
-    # call still copies its batch into the graph's input tensors.  Data-parallel runs keep the eager loop.
-    use_graph = world == 1 and not args.no_graph and os.environ.get('IMX_BENCH_GRAPH', '1') != '0' and not args.one_step
+    # The iteration is captured once as a CUDA graph and replayed (utils/cuda_graph.py); every call still copies its
+    # batch into the graph's input tensors.
+    from torch.nn.parallel import DistributedDataParallel as _DDP
+    # (with several ranks only when no DistributedDataParallel wrapper is in the loop: its autograd hooks and bucket
+    # bookkeeping are host-side; the peer-memory gradient path + flat all-reduce of utils/trainer.py is all kernels)
+    use_graph = not args.no_graph and os.environ.get('IMX_BENCH_GRAPH', '1') != '0' and not args.one_step and \
+        not isinstance(net_G, _DDP) and not isinstance(net_D, _DDP)
     if use_graph:
         from imaginaire_b200.utils.cuda_graph import GraphedTrainerStep
         graphed = GraphedTrainerStep(trainer, resident)
@@ -427,7 +431,15 @@ def run_ours(args):
                           '(%.2f s); train img/s = forward img/s x F_G/(4F_G+4.5F_D+3F_VGG) = %.4f x %.4f'
                           % (dt, fwd, STEP_FLOP_SHARE_OF_G_FWD)}
         print(json.dumps(line), flush=True)
+    if use_graph:
+        graphed.close()
     if world > 1:
+        # a teardown that hangs (a communicator waiting for a peer that already left) must not hold the GPUs: the result
+        # line is out, so after a grace period the process just ends
+        import threading
+        t = threading.Timer(45.0, lambda: os._exit(0))
+        t.daemon = True
+        t.start()
         dist.barrier()
         dist.destroy_process_group()
 

@@ -10,7 +10,7 @@ import math
 import torch
 import torch.distributed as dist
 
-from . import grad_sync, ops
+from . import grad_sync, ops, peer_exchange
 
 ACT_CODES = ops.ACT_CODES
 
@@ -341,10 +341,16 @@ def compute_norm_stats(x, ns, up2x=False):
         # Equal per-rank batches (DistributedSampler; the backward assumes the same): the global count
         # is known on the host, so only [sum, sumsq] cross the wire and the single-GPU finalize kernel
         # does the rest (mean, rstd, running statistics) - 3 launches instead of ~15 small ATen ops.
-        gsums = sums.clone()          # the local sums may be shared with a sibling norm layer
-        dist.all_reduce(gsums, op=dist.ReduceOp.SUM, group=ns.process_group)
         update = ns.track_running_stats and ns.running_mean is not None
         momentum = _momentum(ns) if update else 0.0
+        ex = peer_exchange.get(ns.process_group) if sums.numel() <= peer_exchange.PeerExchange.MAX_FLOATS else None
+        if ex is not None:
+            # one single-CTA kernel over NVLink peer memory: push, flag, wait, sum in rank order, finalize
+            mean, rstd = ex.bn_finalize(sums, count * world, ns.eps, ns.running_mean if update else None,
+                                        ns.running_var if update else None, momentum)
+            return mean, rstd, count * world
+        gsums = sums.clone()          # the local sums may be shared with a sibling norm layer
+        dist.all_reduce(gsums, op=dist.ReduceOp.SUM, group=ns.process_group)
         mean, rstd = ops.bn_finalize(gsums, count * world, ns.eps, ns.running_mean if update else None,
                                      ns.running_var if update else None, momentum)
         return mean, rstd, count * world
@@ -416,7 +422,11 @@ class _SpadeNormAct(torch.autograd.Function):
 
             def hook(red):
                 # SyncBatchNorm backward: all-reduce [sum dy', sum dy'*xn] (2C floats)
-                dist.all_reduce(red, op=dist.ReduceOp.SUM, group=group)
+                ex = peer_exchange.get(group) if red.numel() <= peer_exchange.PeerExchange.MAX_FLOATS else None
+                if ex is not None:
+                    ex.allreduce_sum_(red)
+                else:
+                    dist.all_reduce(red, op=dist.ReduceOp.SUM, group=group)
                 return count
         dx, dg, db, dwt, dbs = ops.spade_modulate_bwd(x, _as_nhwc(dy), mean, rstd, weight, bias, gamma, beta,
                                                       per_instance, act, count, use_batch_stats, hook)

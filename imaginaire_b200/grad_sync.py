@@ -165,9 +165,55 @@ class PeerGradSync:
         self.pending_sn.clear()
 
 
+class FlatGradSync:
+    """Averages the gradients of everything PeerGradSync does not carry (biases, norm parameters, linear layers,
+    filters with <= 8 channels on one side: ~1 % of the parameters) with ONE all-reduce of a flat buffer after the
+    backward: gather into the buffer (torch.cat), NCCL all-reduce, scatter back (_foreach_copy_).  It replaces the
+    DistributedDataParallel wrapper for these parameters: no autograd hooks, no bucket bookkeeping, no
+    unused-parameter search, and nothing that a CUDA-graph capture of the iteration cannot record.
+    ref: the gradient averaging of the reference's DDP wrapper, imaginaire/utils/trainer.py:193-216."""
+
+    def __init__(self, params, group=None):
+        self.group = group if group is not None else dist.group.WORLD
+        self.world = dist.get_world_size(self.group)
+        self.params = [p for p in params]
+        _FLAT.append(self)
+
+    def close(self):
+        if self in _FLAT:
+            _FLAT.remove(self)
+
+    def finish(self):
+        grads = [p.grad for p in self.params if p.grad is not None]
+        if not grads:
+            return
+        flat = torch.cat([g.reshape(-1) for g in grads])
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
+        flat.mul_(1.0 / self.world)
+        torch._foreach_copy_(grads, [c.view_as(g) for c, g in zip(flat.split([g.numel() for g in grads]), grads)])
+
+
+_FLAT = []
+
+
+def broadcast_state(model, group=None, src=0):
+    """Rank `src`'s parameters and buffers to every rank (what the DDP constructor does), coalesced per dtype."""
+    tensors = [t for t in list(model.parameters()) + list(model.buffers()) if t.is_cuda]
+    by_dtype = {}
+    for t in tensors:
+        by_dtype.setdefault(t.dtype, []).append(t)
+    with torch.no_grad():
+        for ts in by_dtype.values():
+            flat = torch.cat([t.reshape(-1) for t in ts])
+            dist.broadcast(flat, src=src, group=group)
+            torch._foreach_copy_(ts, [c.view_as(t) for c, t in zip(flat.split([t.numel() for t in ts]), ts)])
+
+
 def finish_all():
     for s in {id(v): v for v in _ACTIVE.values()}.values():
         s.finish()
+    for f in _FLAT:
+        f.finish()
 
 
 def eligible_filters(model):

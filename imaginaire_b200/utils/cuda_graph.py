@@ -14,8 +14,11 @@ replays them.  What makes the replay equal to the eager loop:
     key: when the next iteration's key differs, the iteration is captured again;
   * host-side counters that the captured Python body would have advanced (the EMA's warm-up count) are advanced here.
 
-Random draws (the style encoder's noise) go through torch's graph-safe CUDA generator.  Single-process use; the
-data-parallel wrappers keep the eager loop.  Run at least one eager iteration first (lazy set-up: kernel
+Random draws (the style encoder's noise) go through torch's graph-safe CUDA generator.  Data-parallel runs: every
+rank captures and replays in step; what crosses ranks inside the iteration is kernels only (the peer-memory
+exchanges of peer_exchange.py / grad_sync.py with device-side counters, symmetric-memory barriers, one NCCL
+all-reduce of the flat small-parameter gradients), all of which a capture records.  A DistributedDataParallel
+wrapper (host-side hooks and buckets) keeps the eager loop.  Run at least one eager iteration first (lazy set-up: kernel
 attributes, spectral-norm plans, optimizer state); ``warmup=n`` runs n more eager iterations on the first batch.
 """
 import torch
@@ -62,7 +65,9 @@ class GraphedTrainerStep:
         steps_before = ema._steps if ema is not None else None
         tracked_before = ema.num_updates_tracked.clone() if ema is not None and not ema.num_updates_tracked.is_cuda else None
         self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph):
+        # thread_local: the NCCL watchdog thread of a data-parallel run keeps querying its events while this thread
+        # captures; under the default (global) mode those queries are capture violations
+        with torch.cuda.graph(self.graph, capture_error_mode='thread_local'):
             self._body()
         self.launches_per_replay = lib.launches - before
         if ema is not None:
@@ -70,6 +75,13 @@ class GraphedTrainerStep:
             if tracked_before is not None:
                 ema.num_updates_tracked.copy_(tracked_before)
         self.key = self._key()
+
+    def close(self):
+        """Drops the captured graph.  Call before torch.distributed.destroy_process_group(): a graph that recorded NCCL
+        work must not outlive its communicator."""
+        torch.cuda.synchronize()
+        self.graph = None
+        self.key = None
 
     def __call__(self, data):
         """Runs one iteration on `data` (device or pinned-host tensors); returns (generator total, discriminator

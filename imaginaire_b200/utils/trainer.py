@@ -147,6 +147,13 @@ def _wrap_model(model, find_unused=None, max_uses=1):
                     ok.zero_()
                 dist.all_reduce(ok, op=dist.ReduceOp.MIN)
                 if float(ok) > 0:
+                    if os.environ.get('IMX_FLAT_GRADS', '1') != '0':
+                        # everything else: one flat all-reduce after the backward instead of a DDP wrapper (no autograd
+                        # hooks / buckets / unused-parameter search; the iteration stays capturable as a CUDA graph)
+                        carried = {id(p) for _, p in filters}
+                        grad_sync.broadcast_state(model)
+                        grad_sync.FlatGradSync([p for p in model.parameters() if id(p) not in carried])
+                        return WrappedModel(model)
                     DistributedDataParallel._set_params_and_buffers_to_ignore_for_model(model, [n for n, _ in filters])
                 elif sync is not None:
                     sync.close()

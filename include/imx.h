@@ -467,6 +467,30 @@ IMX_API int imx_correlation_bwd_f32(const float* input1, const float* input2, co
                             int B, int C, int H, int W, int pad_size, int kernel_size, int max_displacement,
                             int stride1, int stride2, imx_stream_t stream);
 
+/* ---------------------------------------------------- peer-memory exchange -- */
+
+/* Small-vector all-reduce between the GPUs of one node through symmetric (peer-mapped) memory, for
+ * SyncBatchNorm's statistics.  regions: HOST array of `world` device pointers, regions[q] = rank q's exchange
+ * region (imx_peer_exchange_region_bytes() bytes of symmetric memory, zero-filled once before the first call;
+ * regions[rank] is local).  Every rank of the group must issue the same sequence of calls.  One single-CTA
+ * kernel per call on the caller's stream: push to all peers, flag, wait on local flags, sum in rank order (all
+ * ranks get bit-identical sums).  n <= 8192 floats; `out` may be `in`.  The call counter lives in the region and is advanced by the
+ * kernel, so a captured launch stays valid on replay.
+ * ref: torch.nn.SyncBatchNorm's exchanges (torch/nn/modules/_functions.py:49-165: all_gather of
+ *      [mean, invstd, count] forward, all_reduce of [sum_dy, sum_dy_xmu] backward), which
+ *      imaginaire/layers/activation_norm.py:403-410 instantiates */
+IMX_API int64_t imx_peer_exchange_region_bytes(void);
+IMX_API int imx_peer_allreduce_sum_f32(const void* const* regions, int world, int rank, const float* in, float* out,
+                                       int n, imx_stream_t stream);
+
+/* The forward exchange fused with imx_bn_finalize: sums = this rank's [sum x (C) | sum x^2 (C)], count = the
+ * GLOBAL number of elements per channel; writes mean / rstd (C) and, if given, updates the running statistics
+ * (momentum, unbiased variance) -- identical on every rank.
+ * ref: as above + torch batch_norm_gather_stats_with_counts */
+IMX_API int imx_peer_bn_finalize_f32(const void* const* regions, int world, int rank, const float* sums, int C,
+                                     float count, float eps, float* mean, float* rstd, float* running_mean,
+                                     float* running_var, float momentum, imx_stream_t stream);
+
 /* ------------------------------------------------------------ optimizer -- */
 
 /* One Adam step (torch.optim.Adam arithmetic, no amsgrad) over n_tensors fp32 tensors:

@@ -570,6 +570,61 @@ def test_correlation_rejects_geometry_the_reference_reads_out_of_bounds_for():
         ops.correlation_fwd(x.cpu(), x.cpu(), 4, 1, 4, 1, 2)              # no CPU fallback
 
 
+# ------------------------------------------------- SyncBatchNorm exchange over peer memory
+
+@pytest.mark.parametrize('world', [2, 4, 8])
+def test_peer_exchange_allreduce_and_bn_finalize_emulated_on_one_gpu(world):
+    """csrc/peer_exchange.cu with `world` ranks emulated on one GPU: one region, one stream and one single-CTA kernel
+    per rank, all resident at once and waiting for each other's flags exactly as across NVLink.  Six calls in a row
+    exercise both slot sets; results must be identical on every rank and equal to the sum / to bn_finalize of the
+    summed statistics (torch.nn.SyncBatchNorm forward: nn/modules/_functions.py:49-86)."""
+    from imaginaire_b200 import ops, _C
+    from imaginaire_b200.peer_exchange import PeerExchange
+    nbytes = int(_C.lib().raw('imx_peer_exchange_region_bytes')())
+    regions = [torch.zeros(nbytes // 4, dtype=torch.float32, device=DEV) for _ in range(world)]
+    ranks = [PeerExchange(regions=regions, rank=r) for r in range(world)]
+    streams = [torch.cuda.Stream() for _ in range(world)]
+    g = torch.Generator().manual_seed(81)
+    torch.cuda.synchronize()
+    for call in range(6):
+        c = [64, 2048, 40, 4096, 8, 1024][call]
+        if call % 2 == 0:
+            vecs = [torch.randn(2, 1, c, generator=g).to(DEV) for _ in range(world)]
+            torch.cuda.synchronize()
+            outs = []
+            for r in range(world):
+                with torch.cuda.stream(streams[r]):
+                    outs.append(ranks[r].allreduce_sum(vecs[r]))
+            torch.cuda.synchronize()
+            expect = torch.stack(vecs).sum(0)
+            for o in outs:
+                assert torch.equal(o, outs[0])                       # same summation order everywhere
+                assert H.rel_err(o.cpu(), expect.cpu()) < 1e-6
+        else:
+            xs = [torch.randn(3, c, 5, 7, generator=g) * 2 + 0.5 for _ in range(world)]
+            sums = [torch.stack([x.sum((0, 2, 3)), (x * x).sum((0, 2, 3))]).view(2, 1, c).to(DEV) for x in xs]
+            count = world * 3 * 5 * 7
+            rm = [torch.zeros(c, device=DEV) for _ in range(world)]
+            rv = [torch.ones(c, device=DEV) for _ in range(world)]
+            torch.cuda.synchronize()
+            res = []
+            for r in range(world):
+                with torch.cuda.stream(streams[r]):
+                    res.append(ranks[r].bn_finalize(sums[r], count, 1e-5, rm[r], rv[r], 0.1))
+            torch.cuda.synchronize()
+            allx = torch.cat(xs, 0)
+            mean = allx.mean((0, 2, 3))
+            var = allx.var((0, 2, 3), unbiased=False)
+            for r in range(world):
+                assert torch.equal(res[r][0], res[0][0]) and torch.equal(res[r][1], res[0][1])
+                assert H.rel_err(res[r][0].cpu(), mean) < 1e-5
+                assert H.rel_err(res[r][1].cpu(), torch.rsqrt(var + 1e-5)) < 1e-4
+                assert H.rel_err(rm[r].cpu(), 0.1 * mean) < 1e-5
+                assert H.rel_err(rv[r].cpu(), 0.9 + 0.1 * allx.var((0, 2, 3), unbiased=True)) < 1e-4
+    with pytest.raises(_C.ImxError, match='exceed'):
+        ranks[0].allreduce_sum(torch.zeros(8193, device=DEV))
+
+
 # ------------------------------------------------- data-parallel weight gradient over peer memory
 
 @pytest.mark.parametrize('case', [(2, 64, 96, 16, 24, 3, 1, 1, 2), (1, 40, 72, 13, 11, 5, 1, 2, 3), (2, 128, 256, 8, 8, 1, 1, 0, 8)])
