@@ -4,13 +4,22 @@ ref: the reference wraps its networks in (apex / torch) DistributedDataParallel,
 NCCL all-reduce averages the gradients after the backward (imaginaire/utils/trainer.py:193-216).
 Here the convolution filters (99 % of the parameters) take another route: the weight-gradient
 GEMM already ends in a reduction over split-K partial sums; with every rank's partials in
-symmetric (peer-mapped) memory that reduction simply also runs over the ranks:
+symmetric (peer-mapped) memory that reduction simply also runs over the ranks (``IMX_PEER_GRADS_MODE=partials``):
 
     per layer:    GEMM -> partials (own region of a symmetric workspace) imx_conv2d_igemm_wgrad_partials_bf16
     per backward: barrier (device side, current stream)
                  per layer: sum over ranks x splits of MY 1/world of the channels  imx_wgrad_reduce_peers_f32
                  barrier, fetch the other ranks' channel ranges        imx_gather_rows_peers_f32
                  spectral-norm gradient correction on the averaged gradients (it is linear)
+
+That moves `splits` x the gradient bytes over NVLink (7.5 ms of reduction kernels per iteration on 2 GPUs, ncu /
+torch.profiler).  The default (``IMX_PEER_GRADS_MODE=flat``) keeps the split-K reduction local and exchanges finished
+gradients only:
+
+    per layer:    the ordinary weight gradient (GEMM + local split-K reduction) written into the rank's arena
+    per backward: barrier; ONE reduce-scatter kernel over all gradients of the backward (imx_peer_reduce_scatter_f32:
+                 my 1/world chunk of every tensor summed over the ranks); barrier; ONE all-gather kernel
+                 (imx_peer_all_gather_f32); barrier; spectral-norm correction
 
 No NCCL kernels compete with the persistent convolution kernels for SMs, and the averaged
 gradient is produced by kernels that had to run anyway.  Everything else (biases, norm
@@ -57,10 +66,13 @@ class PeerGradSync:
                 total += (w.numel() + 63) // 64 * 64          # 256-byte aligned slots
         self.arena = symm_mem.empty(total, dtype=torch.float32, device=dev)
         self.arena_hdl = symm_mem.rendezvous(self.arena, self.group.group_name)
-        self.ws = symm_mem.empty(workspace_bytes // 4, dtype=torch.float32, device=dev)
-        self.ws_hdl = symm_mem.rendezvous(self.ws, self.group.group_name)
+        import os
+        self.flat = os.environ.get('IMX_PEER_GRADS_MODE', 'flat') != 'partials'
         self.arena_ptrs = [int(p) for p in self.arena_hdl.buffer_ptrs]
-        self.ws_ptrs = [int(p) for p in self.ws_hdl.buffer_ptrs]
+        if not self.flat:      # the split-K partial sums are exchanged: they need a symmetric workspace
+            self.ws = symm_mem.empty(workspace_bytes // 4, dtype=torch.float32, device=dev)
+            self.ws_hdl = symm_mem.rendezvous(self.ws, self.group.group_name)
+            self.ws_ptrs = [int(p) for p in self.ws_hdl.buffer_ptrs]
         self.ws_bytes = workspace_bytes
         self.ws_regions = {}      # (data_ptr, use index) -> byte offset; same order on every rank
         self.ws_top = 0
@@ -69,6 +81,8 @@ class PeerGradSync:
         self.records = []
         self.by_ptr = {w.data_ptr(): w for w in self.params}
         self._gather_descs = {}
+        self._seg_descs = {}
+        self._arena_table = (ctypes.c_void_p * self.world)(*self.arena_ptrs)
         for w in self.params:
             _ACTIVE[w.data_ptr()] = self
 
@@ -107,6 +121,15 @@ class PeerGradSync:
         if use >= self.max_uses:
             raise RuntimeError('PeerGradSync: a filter is used %d times in one backward but max_uses is %d'
                                % (use + 1, self.max_uses))
+        if self.flat:
+            # the complete local gradient (GEMM + local split-K reduction) straight into this rank's arena slot
+            ws = torch.empty((max(int(nbytes), 16),), dtype=torch.uint8, device=x.device)
+            lib.call('imx_conv2d_igemm_wgrad_bf16', x.data_ptr(), dy.data_ptr(), self.grad_view(weight, use).data_ptr(),
+                     ws.data_ptr(), int(nbytes), n, h, w, cin, cin_p, cout, cout_p, kh, kw, stride, pad, ops._stream())
+            self.uses[key] = use + 1
+            if sn is not None:
+                self.pending_sn.append((key, use) + tuple(sn))
+            return
         off = self._region((key, use), int(nbytes))
         plan = (ctypes.c_int * 3)()
         stream = ops._stream()
@@ -140,6 +163,21 @@ class PeerGradSync:
             self._gather_descs[used] = descs
         lib = _C.lib()
         stream = ops._stream()
+        if self.flat:
+            segs = self._seg_descs.get(used)
+            if segs is None:
+                rows = [[self.offset[ku], self.by_ptr[ku[0]].numel()] for ku in used]
+                segs = (torch.tensor(rows, dtype=torch.int64).to(self.arena.device), max(r[1] for r in rows))
+                self._seg_descs[used] = segs
+            self.arena_hdl.barrier(channel=0)              # every rank's local gradients of this backward are written
+            lib.call('imx_peer_reduce_scatter_f32', self._arena_table, self.world, self.rank, segs[0].data_ptr(), len(used),
+                     int(segs[1]), 1.0 / self.world, stream)
+            self.arena_hdl.barrier(channel=1)              # every rank has reduced its chunks
+            lib.call('imx_peer_all_gather_f32', self._arena_table, self.world, self.rank, segs[0].data_ptr(), len(used),
+                     int(segs[1]), stream)
+            self.arena_hdl.barrier(channel=2)              # nobody reads my chunks any more: in-place edits are safe
+            self._finish_local()
+            return
         self.ws_hdl.barrier(channel=0)                     # every rank's partial sums of this backward are written
         for key, use, off, splits, co_r, ci_r, cin, cout, taps in self.records:
             peers = (ctypes.c_void_p * self.world)(*[p + off for p in self.ws_ptrs])
@@ -153,6 +191,9 @@ class PeerGradSync:
         lib.call('imx_gather_rows_peers_f32', peers, self.world, self.rank, descs[0].data_ptr(), len(used), int(descs[1]),
                  ops._stream())
         self.arena_hdl.barrier(channel=2)                  # nobody reads my channel ranges any more: in-place edits are safe
+        self._finish_local()
+
+    def _finish_local(self):
         for key, use, weight, u, v, inv_sigma in self.pending_sn:
             ops.spectral_norm_weight_grad_(self.grad_view(self.by_ptr[key], use), weight, u, v, inv_sigma)
         for k, n in self.uses.items():

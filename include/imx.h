@@ -395,6 +395,20 @@ IMX_API int imx_wgrad_reduce_peers_f32(const void* const* ws_peers, int world, f
 IMX_API int imx_gather_rows_peers_f32(const void* const* arena_peers, int world, int rank, const void* descs,
                               int n_tensors, int64_t max_elems, imx_stream_t stream);
 
+/* The same averaging with the split-K reduction kept local: every rank writes its own complete gradients (e.g.
+ * imx_conv2d_igemm_wgrad_bf16 with dw pointing into the arena) into the same offsets of its arena of symmetric
+ * memory; after a barrier of all ranks, imx_peer_reduce_scatter_f32 leaves scale * (sum over ranks) in the
+ * rank-th of `world` contiguous chunks of every segment of THIS rank's arena (chunk boundaries rounded to 4
+ * floats); after another barrier imx_peer_all_gather_f32 fetches the other chunks from their owners; a third
+ * barrier before anybody writes its arena again.  segs: DEVICE array of int64 pairs {offset, numel} (offsets in
+ * floats, multiples of 4), identical on every rank; max_numel sizes the grid.  (world-1)/world of the gradient
+ * bytes are read remotely in each phase, as coalesced 16-byte loads.
+ * ref: DDP's gradient all-reduce, imaginaire/utils/trainer.py:193-216 */
+IMX_API int imx_peer_reduce_scatter_f32(const void* const* arena_peers, int world, int rank, const void* segs,
+                                        int n_seg, int64_t max_numel, float scale, imx_stream_t stream);
+IMX_API int imx_peer_all_gather_f32(const void* const* arena_peers, int world, int rank, const void* segs, int n_seg,
+                                    int64_t max_numel, imx_stream_t stream);
+
 /* The weight gradient again, for callers that are not able to allocate device memory (no
  * counterpart in the reference: its extensions always let torch allocate).  Think of a host
  * that reserves its whole device-memory budget at start-up and forbids cudaMalloc afterwards,

@@ -570,6 +570,39 @@ def test_correlation_rejects_geometry_the_reference_reads_out_of_bounds_for():
         ops.correlation_fwd(x.cpu(), x.cpu(), 4, 1, 4, 1, 2)              # no CPU fallback
 
 
+@pytest.mark.parametrize('world', [2, 3, 8])
+def test_peer_reduce_scatter_and_all_gather_average_the_arenas(world):
+    """csrc/peer_grads.cu with the ranks' arenas emulated by tensors on one GPU: after the reduce-scatter of every
+    rank and then the all-gather of every rank, every arena holds the average of the original arenas on the listed
+    segments (ragged sizes: chunk boundaries are rounded to 4 floats) and is untouched elsewhere."""
+    import ctypes
+    from imaginaire_b200 import _C, ops
+    g = torch.Generator().manual_seed(91)
+    sizes = [4096, 7, 130, 100000, 1, 64 * 9 * 33]
+    offsets, top = [], 64
+    for n in sizes:
+        offsets.append(top)
+        top += (n + 63) // 64 * 64 + 64                 # a gap after every segment
+    arenas = [torch.randn(top, generator=g).to(DEV) for _ in range(world)]
+    orig = [a.clone() for a in arenas]
+    segs = torch.tensor([[o, n] for o, n in zip(offsets, sizes)], dtype=torch.int64, device=DEV)
+    table = (ctypes.c_void_p * world)(*[a.data_ptr() for a in arenas])
+    lib = _C.lib()
+    for r in range(world):
+        lib.call('imx_peer_reduce_scatter_f32', table, world, r, segs.data_ptr(), len(sizes), max(sizes), 1.0 / world, ops._stream())
+    for r in range(world):
+        lib.call('imx_peer_all_gather_f32', table, world, r, segs.data_ptr(), len(sizes), max(sizes), ops._stream())
+    torch.cuda.synchronize()
+    mean = torch.stack(orig).mean(0)
+    mask = torch.zeros(top, dtype=torch.bool, device=DEV)
+    for o, n in zip(offsets, sizes):
+        mask[o:o + n] = True
+    for r in range(world):
+        assert H.rel_err(arenas[r][mask].cpu(), mean[mask].cpu()) < 1e-6
+        assert torch.equal(arenas[r][~mask], orig[r][~mask])
+        assert torch.equal(arenas[r][mask], arenas[0][mask])         # bit-identical on every rank
+
+
 # ------------------------------------------------- SyncBatchNorm exchange over peer memory
 
 @pytest.mark.parametrize('world', [2, 4, 8])
