@@ -36,6 +36,7 @@ def parse_args():
     ap.add_argument('--config', default=CONFIG_NAME)
     ap.add_argument('--batch', type=int, default=None, help='per-GPU batch override (debugging only)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-hbm-probe', action='store_true', help='skip the norm / warp HBM microbenchmarks')
     ap.add_argument('--no-graph', action='store_true', help='single-GPU run: time the eager loop instead of the CUDA-graph replay')
     ap.add_argument('--no-clocks', action='store_true', help='do not spawn the nvidia-smi clock sampler (ncu runs)')
     ap.add_argument('--one-step', action='store_true',
@@ -135,8 +136,10 @@ class ConvProbe:
             return wrapper
 
         def fprop_flops(out, x, wpk, cout, kh, kw, *a, **k):
+            # algorithmic: the logical channel counts (a 35-channel label map is stored with 40 channels, an image
+            # with 8; the padding is the kernel's business, not work the reference does)
             n, _, ho, wo = out.shape
-            return 2.0 * n * ho * wo * cout * x.shape[1] * kh * kw
+            return 2.0 * n * ho * wo * cout * getattr(wpk, '_imx_inner', x.shape[1]) * kh * kw
 
         def wgrad_flops(out, x, dy, cin, cout, kh, kw, *a, **k):
             n, _, ho, wo = dy.shape
@@ -182,6 +185,71 @@ class ConvProbe:
         tot_fl = sum(v[0] for v in by.values())
         tot_ms = sum(v[1] for v in by.values())
         return by, tot_fl, tot_ms
+
+
+def conv_traffic_from_profile():
+    """DRAM bytes of one launch of the dominant convolution shape as ncu measured them (tools/ncu_traffic.py writes
+    the file from a `--set full` capture); None if the capture is not in the tree."""
+    try:
+        with open(os.path.join(ROOT, 'profiles', 'r02_conv_traffic.json')) as f:
+            d = json.load(f)
+        return float(d['dram_bytes_read']) + float(d['dram_bytes_write'])
+    except (OSError, KeyError, ValueError):
+        return None
+
+
+def hbm_rooflines(dev, hbm_peak_gbs):
+    """Second half of BASELINE.json's metric: achieved HBM GB/s of the norm / modulation / warp kernels, each timed
+    alone with CUDA events (5 calls after 2 warm-ups) on tensors far larger than L2: the C3 layer 8 x 512 x 128 x 256
+    (bf16 NHWC) for the norm kernels, 8 x 64 x 512 x 1024 fp32 on the SURVEY 8(d) flow for the warps.  Bytes are the
+    algorithmic ones of DESIGN.md section 3."""
+    import torch
+    from imaginaire_b200 import ops
+
+    def timed(fn):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(5):
+            fn()
+        e.record()
+        torch.cuda.synchronize()
+        return s.elapsed_time(e) / 5 * 1e-3
+
+    out = {}
+
+    def rec(name, nbytes, fn):
+        t = timed(fn)
+        out[name] = {'GBps': nbytes / t / 1e9, 'frac': nbytes / t / 1e9 / hbm_peak_gbs, 'bytes': nbytes, 'us': t * 1e6}
+
+    g = torch.Generator(device=dev).manual_seed(7)
+    n, c, h, w = 8, 512, 128, 256
+    t1 = n * c * h * w * 2                      # one bf16 activation tensor
+    mk = lambda: torch.randn(n, c, h, w, device=dev, generator=g).bfloat16().contiguous(memory_format=torch.channels_last)  # noqa: E731
+    x, gam, bet, dy = mk(), mk(), mk(), mk()
+    aff_w, aff_b = torch.ones(c, device=dev), torch.zeros(c, device=dev)
+    sums = ops.bn_stats(x, False)
+    mean, rstd = ops.bn_finalize(sums, n * h * w, 1e-5)
+    y = ops.spade_modulate_fwd(x, mean, rstd, aff_w, aff_b, gam, bet, False, 1)
+    rec('stats_kernel', t1, lambda: ops.bn_stats(x, False))
+    rec('modulate_fwd (x, gamma, beta -> y)', 4 * t1, lambda: ops.spade_modulate_fwd(x, mean, rstd, aff_w, aff_b, gam, bet, False, 1))
+    # backward = pass 1 (x, dy, gamma, beta -> dgamma, dbeta: 6 tensors) + pass 2 (x, dy, gamma -> dx: 4 tensors)
+    rec('modulate_bwd (both passes)', 10 * t1,
+        lambda: ops.spade_modulate_bwd(x, dy, mean, rstd, aff_w, aff_b, gam, bet, False, 1, n * h * w))
+    rec('act_bwd_sum_kernel', 3 * t1, lambda: ops.act_bwd_bias(dy, y, 1, True))
+    del x, gam, bet, dy, y
+    b_, c_, hh, ww = 8, 64, 512, 1024
+    img = torch.randn(b_, c_, hh, ww, device=dev, generator=g)
+    flow = torch.nn.functional.interpolate(torch.randn(b_, 2, 32, 64, device=dev, generator=g) * 8.0, size=(hh, ww),
+                                           mode='bilinear', align_corners=False).contiguous()
+    go = torch.randn(b_, c_, hh, ww, device=dev, generator=g)
+    px = b_ * hh * ww * 4
+    rec('resample2d_fwd', (2 * c_ + 2) * px, lambda: ops.resample2d_fwd(img, flow))
+    rec('gridsample_warp_fwd', (2 * c_ + 2) * px, lambda: ops.gridsample_warp_fwd(img, flow))
+    rec('resample2d_bwd', (3 * c_ + 4) * px, lambda: ops.resample2d_bwd(img, flow, go))
+    return out
 
 
 # ---------------------------------------------------------------------- CPU baseline
@@ -248,7 +316,8 @@ def run_reference(args):
         'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': steps,
         'warmup': warmup, 'ms_per_step': 1000.0 * t / steps, 'higher_is_better': True, 'scaling': 'weak',
         'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-        'config': {'workload': 'SPADE G+D training step, base128 generator, 256x512, 35 labels (CPU sample: generator forward)',
+        'config': {'workload': 'SPADE G+D training step, base128 generator, 256x512, 35 labels (CPU sample: generator '
+                               'forward at batch 1, extrapolated to the training step by its share of the algorithmic FLOPs)',
                    'config_file': 'configs/' + args.config},
         'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
         'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
@@ -388,9 +457,9 @@ def run_ours(args):
         'bound': 'tensor', 'kernel': 'conv_igemm_kernel / conv_wgrad_kernel (tcgen05 implicit GEMM), all launches of one iteration',
         'achieved': achieved, 'peak': peaks['tf_sustained'], 'unit': 'TFLOP/s', 'frac': achieved / peaks['tf_sustained'],
         # dram__bytes_read.sum + dram__bytes_write.sum of the family's most frequent launch (conv_igemm_kernel<256,0,1>,
-        # 3x3 512->512 at 8x128x256) from profiles/r01b_ncu_full_conv_summary.md; its algorithmic traffic is 541 MB
-        # (x 268 + filter 4.7 + y 268; part of y was still in L2 when the kernel ended)
-        'traffic': 273.9e6 + 223.5e6, 'traffic_unit': 'bytes per launch (ncu --set full, one launch of the dominant shape)',
+        # 3x3 512->512 at 8x128x256; algorithmic 541 MB = x 268 + filter 4.7 + y 268), read from the committed ncu
+        # summary of that launch -- null when the file is not there
+        'traffic': conv_traffic_from_profile(), 'traffic_unit': 'bytes per launch (ncu --set full, one launch of the dominant shape; profiles/r02_conv_traffic.json)',
         'peak_source': peaks['source'] + ' bf16_tflops_sustained (kernel timed inside a long step)',
         'conv_share_of_step': conv_ms / ms_per_step if ms_per_step > 0 else None,
         'by_kind': {k: {'tflops': v[0] / (v[1] * 1e-3) / 1e12 if v[1] > 0 else 0.0, 'ms': v[1], 'launches': v[2]}
@@ -416,6 +485,7 @@ def run_ours(args):
         'gpu_launches': launches,
         'roofline': roofline,
         'clocks': clocks,
+        'roofline_hbm': hbm_rooflines(dev, peaks['hbm']) if rank == 0 and not args.no_hbm_probe else None,
         'step_tflops': world * batch * (4 * F_G + 4.5 * F_D + 3 * F_VGG) / 1e3 / (ms_per_step * 1e-3) / max(world, 1),
     }
     if rank == 0:

@@ -119,13 +119,18 @@ def _packed_weight(weight, inner_p, transpose_flip, inv_sigma=None):
     weight norm: frozen VGG filters, un-normalised SPADE projections) keep their packed copy
     until the optimizer changes them (tensor version counter); spectrally normalised filters
     are new tensors every forward and are packed each time."""
+    # _imx_inner: the logical (unpadded) length of the contraction axis, for whoever counts algorithmic FLOPs
+    inner = weight.shape[0] if transpose_flip else weight.shape[1]
     if inv_sigma is not None or not isinstance(weight, torch.nn.Parameter):
-        return ops.pack_conv_weight(weight, inv_sigma, cin_p=inner_p, transpose_flip=transpose_flip)
+        packed = ops.pack_conv_weight(weight, inv_sigma, cin_p=inner_p, transpose_flip=transpose_flip)
+        packed._imx_inner = inner
+        return packed
     key = (id(weight), inner_p, transpose_flip)
     hit = _PACK_CACHE.get(key)
     if hit is not None and hit[0] == weight._version and hit[1] == weight.data_ptr():
         return hit[2]
     packed = ops.pack_conv_weight(weight, None, cin_p=inner_p, transpose_flip=transpose_flip)
+    packed._imx_inner = inner
     _PACK_CACHE[key] = (weight._version, weight.data_ptr(), packed)
     return packed
 

@@ -1,6 +1,8 @@
 """GPU parity of the C-ABI kernels against the CPU oracle (oracle/) and the golden vectors.
 Bit-exact where the arithmetic is reproducible (warp forwards, resizes, packs), stated
 tolerances elsewhere."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -191,6 +193,59 @@ def test_conv2d_fprop_vs_oracle(case):
     assert float(y[:, cout:].float().abs().max() if y.shape[1] > cout else 0.0) == 0.0
 
 
+# The shapes the timed C3 iteration runs (batch reduced where the tile schedule does not depend on it): 256-pixel
+# tiles (MT = 2) with more than one wave, BN = 256 over several waves at 128 x 256, 2048-channel K loops, the 5x5
+# projections on 35 -> 128 -> C channels, the discriminator's first k4 s2 layer, the to-RGB layer.
+BENCH_CONV_CASES = [
+    # N, Cin, Cout, H, W, k, stride, pad
+    (2, 512, 512, 128, 256, 3, 1, 1),      # BN = 256, 1024 tiles: many waves of the persistent loop
+    (2, 512, 256, 128, 256, 3, 1, 1),
+    (2, 128, 512, 128, 256, 5, 1, 2),      # gamma / beta projection at the largest resolution
+    (8, 40, 128, 64, 128, 5, 1, 2),        # label -> hidden (35 labels padded to 40), BN = 128 with MT = 2
+    (8, 128, 1024, 32, 64, 5, 1, 2),
+    (8, 2048, 2048, 16, 32, 3, 1, 1),      # 2048-channel K loop, split-K territory (128 tiles)
+    (8, 2048, 1024, 32, 64, 1, 1, 0),      # learned shortcut
+    (4, 40, 128, 256, 512, 4, 2, 1),       # discriminator layer 0
+    (2, 256, 3, 256, 512, 5, 1, 2),        # to-RGB (shift-add path is taken by the module; this is the kernel)
+]
+
+
+@pytest.mark.parametrize('case', BENCH_CONV_CASES)
+def test_conv2d_fprop_at_the_timed_shapes(case):
+    """fprop against the fp32 CPU convolution on bf16-rounded operands, every output element, at the layer shapes of
+    the timed iteration (tests/test_gpu_kernels.py::CONV_CASES stops at 4 x 512 -> 1024 @ 32 x 64)."""
+    from imaginaire_b200 import ops
+    n, cin, cout, h, w, k, s, p = case
+    g = torch.Generator().manual_seed(131)
+    x = torch.randn(n, cin, h, w, generator=g).bfloat16().float()
+    wt = (torch.randn(cout, cin, k, k, generator=g) / (cin * k * k) ** 0.5).bfloat16().float()
+    b = torch.randn(cout, generator=g)
+    y = ops.conv2d_fprop(nhwc(x), ops.pack_conv_weight(wt.to(DEV), cin_p=cin), cout, k, k, s, p, bias=b.to(DEV))
+    torch.set_num_threads(max(1, (os.cpu_count() or 1)))
+    ref = F.conv2d(x, wt, b, stride=s, padding=p)
+    assert H.rel_err(y[:, :cout].float().cpu(), ref) < 4e-3
+
+
+@pytest.mark.parametrize('case', [(8, 2048, 2048, 16, 32, 3, 1, 1),     # 587 TF/s shape: few pixels, many taps x tiles
+                                  (8, 128, 2048, 16, 32, 5, 1, 2),
+                                  (4, 64, 128, 256, 512, 5, 1, 2),      # many pixels: deep split over the pixel axis
+                                  (2, 512, 512, 128, 256, 3, 1, 1),
+                                  (8, 1024, 512, 64, 128, 1, 1, 0)])
+def test_conv2d_wgrad_at_the_timed_shapes(case):
+    """The split planner at C3 sizes: filter gradient against torch's CPU computation (exact bf16 products, fp32
+    accumulation on both sides; the GPU sums its split-K partials in another order)."""
+    from imaginaire_b200 import ops
+    n, cin, cout, h, w, k, s, p = case
+    g = torch.Generator().manual_seed(133)
+    ho, wo_ = (h + 2 * p - k) // s + 1, (w + 2 * p - k) // s + 1
+    x = torch.randn(n, cin, h, w, generator=g).bfloat16().float()
+    dy = (torch.randn(n, cout, ho, wo_, generator=g) / (n * ho * wo_) ** 0.5).bfloat16().float()
+    dw = ops.conv2d_wgrad(nhwc(x), nhwc(dy), cin, cout, k, k, s, p)
+    torch.set_num_threads(max(1, (os.cpu_count() or 1)))
+    ref = torch.nn.grad.conv2d_weight(x, (cout, cin, k, k), dy, stride=s, padding=p)
+    assert H.rel_err(dw.cpu(), ref) < 2e-4
+
+
 def test_conv2d_epilogues_vs_oracle():
     from imaginaire_b200 import ops
     g = torch.Generator().manual_seed(32)
@@ -363,6 +418,28 @@ def test_bn_stats_and_finalize_vs_oracle(shape, inst):
         # oracle: running = 0.9 * running + 0.1 * {mean, unbiased var}  (spade_oracle.inner_norm)
         assert H.rel_err(rv.cpu(), 0.9 + 0.1 * x.var(dims, unbiased=True)) < 1e-4
         assert H.rel_err(rm.cpu(), 0.1 * x.mean(dims)) < 1e-4
+
+
+@pytest.mark.parametrize('inst', [False, True])
+def test_bn_stats_with_a_large_mean_and_many_elements(inst):
+    """variance by E[x^2] - E[x]^2 in fp32 cancels when |mean| >> sigma and the count is large.
+    1 M elements per channel (262 k per instance), |mean| / sigma up to 30: mean and rstd against float64."""
+    from imaginaire_b200 import ops
+    g = torch.Generator().manual_seed(52)
+    n, c, h, w = 4, 16, 512, 512
+    ratio = torch.tensor([0.0, 1.0, 3.0, 10.0, 30.0, -30.0, 20.0, 5.0] * 2)
+    x = (torch.randn(n, c, h, w, generator=g) + ratio.view(1, c, 1, 1)).bfloat16().float()
+    sums = ops.bn_stats(nhwc(x), inst)
+    count = h * w if inst else n * h * w
+    mean, rstd = ops.bn_finalize(sums, count, 1e-5)
+    xd = x.double()
+    dims = (2, 3) if inst else (0, 2, 3)
+    m_ref = xd.mean(dims).reshape(-1)
+    r_ref = torch.rsqrt(xd.var(dims, unbiased=False) + 1e-5).reshape(-1)
+    assert H.rel_err(mean.cpu(), m_ref) < 1e-5
+    err = float(((rstd.cpu().double() - r_ref) / r_ref).abs().max())
+    print('worst relative rstd error %.2e at |mean|/sigma up to 30, %d elements per statistic' % (err, count))
+    assert err < 2e-3          # a bf16 activation carries 4e-3; the cancellation must stay below that
 
 
 def test_spade_gb_fused_equals_materialised():

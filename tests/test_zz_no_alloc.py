@@ -48,6 +48,10 @@ def test_noalloc_wgrad_matches_workspace_entry_point_on_two_calls_in_a_row():
         torch.cuda.synchronize()
         assert torch.isfinite(out).all()
         assert H.rel_err(out.cpu(), ref.cpu()) < 1e-4      # the tolerance of the wgrad parity tests
+        # and against the CPU computation itself (fp32 accumulation of the exact bf16 products), so that the
+        # numbers are checked and not only the scratch plumbing
+        cpu = torch.nn.grad.conv2d_weight(x.float().cpu(), (cout, cin, k, k), dy.float().cpu(), stride=stride, padding=pad)
+        assert H.rel_err(out.cpu(), cpu) < 1e-4
     # the tensor-level wrapper goes through the same entry point
     x, dy = _case(3, 1, 40, 72, 13, 11, 5, 1, 2)
     pad_c = lambda t, c: torch.nn.functional.pad(t.float(), (0, 0, 0, 0, 0, c - t.shape[1])).bfloat16() \
