@@ -70,7 +70,7 @@ class _Lib:
         return self._dll.imx_last_error().decode('utf-8', 'replace')
 
     # kernels launched per successful call (everything else launches exactly one)
-    _LAUNCHES = {'imx_conv2d_igemm_wgrad_bf16': 2, 'imx_conv2d_igemm_wgrad_bf16_noalloc': 2,
+    _LAUNCHES = {'imx_conv2d_igemm_wgrad_bf16': 2, 'imx_conv2d_igemm_wgrad_dot_bf16': 2, 'imx_conv2d_igemm_wgrad_bf16_noalloc': 2,
                  'imx_conv2d_igemm_fprop_splitk_bf16': 2, 'imx_spectral_norm_sigma_f32': 4, 'imx_spectral_norm_sigma_batched_f32': 4, 'imx_spectral_norm_weight_grad_f32': 2}
 
     def call(self, name, *args):

@@ -281,6 +281,86 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restr
     }
 }
 
+// The same reduction with coalesced stores, and optionally <dw, W> for the spectral-norm gradient on the way.
+// A CTA owns `kRedRows` output channels x a tile of 128 input channels: each thread sums the splits of one (co, ci)
+// for every tap (consecutive threads -> consecutive ci: 512-byte workspace rows), parks the taps in shared memory and
+// the CTA writes its run of 128 * taps floats of dw[co][ci0..][:] contiguously.  wgrad_reduce_kernel's stores are
+// `taps` floats apart (one 4-byte word per 36-byte stride for a 3x3 filter), which held it at ~1.4 TB/s.
+// dot (fp32, zeroed by the caller) += sum dw * W over the CTA's elements: W has dw's layout, so it is read in the
+// same contiguous runs; one atomic per CTA.
+constexpr int kRedRows = 2, kRedTile = 128;
+
+__global__ void __launch_bounds__(kRedRows * kRedTile)
+wgrad_reduce_tiled_kernel(const float* __restrict__ ws, float* __restrict__ dw, const float* __restrict__ Wt,
+                          float* __restrict__ dot, int Cout, int Cin, int taps, int splits, int co_r, int ci_r) {
+    extern __shared__ float rtile[];            // [kRedRows][kRedTile][taps + 1]
+    __shared__ float rsum[kRedRows * kRedTile / 32];
+    const int sub = threadIdx.x / kRedTile, j = threadIdx.x % kRedTile;
+    const int co = blockIdx.y * kRedRows + sub;
+    const int ci0 = blockIdx.x * kRedTile;
+    const int n_ci = min(kRedTile, Cin - ci0);
+    const int pitch = taps + 1;
+    float* tile = rtile + (size_t)sub * kRedTile * pitch;
+    if (co < Cout && j < n_ci) {
+        const float* src = ws + (size_t)co * ci_r + ci0 + j;
+        const size_t tap_stride = (size_t)co_r * ci_r, split_stride = (size_t)taps * tap_stride;
+        // four taps at a time: four independent loads per split in flight (one by one the loop is a chain of
+        // dependent 4-byte loads and the kernel ran at ~1.2 TB/s; 16-byte loads with a warp per output channel were
+        // tried and lost: the 5x5 layers then fit only two rows of shared memory per CTA)
+        for (int t0 = 0; t0 < taps; t0 += 4) {
+            float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+            for (int sp = 0; sp < splits; ++sp) {
+                float v[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    v[u] = (t0 + u < taps) ? __ldcs(src + sp * split_stride + (size_t)(t0 + u) * tap_stride) : 0.0f;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) acc[u] += v[u];
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (t0 + u < taps) tile[j * pitch + t0 + u] = acc[u];
+        }
+    }
+    __syncthreads();
+    float part = 0.0f;
+    if (co < Cout) {
+        const size_t base = ((size_t)co * Cin + ci0) * taps;
+        for (int e = j; e < n_ci * taps; e += kRedTile) {
+            const float v = tile[(e / taps) * pitch + e % taps];
+            dw[base + e] = v;
+            if (Wt) part = fmaf(v, __ldg(Wt + base + e), part);
+        }
+    }
+    if (Wt) {
+        part = imx::warp_sum(part);
+        if ((threadIdx.x & 31) == 0) rsum[threadIdx.x >> 5] = part;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float tot = 0.0f;
+            for (int i = 0; i < kRedRows * kRedTile / 32; ++i) tot += rsum[i];
+            atomicAdd(dot, tot);
+        }
+    }
+}
+
+int launch_reduce(const float* ws, float* dw, const float* Wt, float* dot, int Cout, int Cin, int taps, int splits,
+                  int co_r, int ci_r, cudaStream_t s) {
+    const size_t smem = (size_t)kRedRows * kRedTile * (taps + 1) * sizeof(float);
+    const int gy = (Cout + kRedRows - 1) / kRedRows;
+    if (smem <= 48 * 1024 && gy <= 65535) {
+        dim3 grid((Cin + kRedTile - 1) / kRedTile, gy);
+        wgrad_reduce_tiled_kernel<<<grid, kRedRows * kRedTile, smem, s>>>(ws, dw, Wt, dot, Cout, Cin, taps, splits, co_r, ci_r);
+        return imx::check_launch("conv2d_wgrad_reduce");
+    }
+    if (Wt) return imx::set_error(IMX_ERR_UNSUPPORTED, "conv2d_wgrad: fused <dw, W> needs taps <= 47 and Cout <= 131070");
+    const long total = (long)Cout * Cin * taps;
+    long blocks = (total + 255) / 256;
+    if (blocks > 16L * imx::kNumSMs) blocks = 16L * imx::kNumSMs;
+    wgrad_reduce_kernel<<<(int)blocks, 256, 0, s>>>(ws, dw, Cout, Cin, taps, splits, co_r, ci_r);
+    return imx::check_launch("conv2d_wgrad_reduce");
+}
+
 constexpr int kMaxPeers = 8;
 struct PeerPtrs { const float* p[kMaxPeers]; };
 
@@ -478,11 +558,24 @@ extern "C" int imx_conv2d_igemm_wgrad_bf16(const imx_bf16* x, const imx_bf16* dy
     Plan pl;
     int rc = wgrad_gemm(x, dy, workspace, workspace_bytes, N, H, W, Cin, Cin_p, Cout, Cout_p, KH, KW, stride, pad, s, a, pl);
     if (rc) return rc;
-    const long total = (long)Cout * Cin * KH * KW;
-    long blocks = (total + 255) / 256;
-    if (blocks > 16L * imx::kNumSMs) blocks = 16L * imx::kNumSMs;
-    wgrad_reduce_kernel<<<(int)blocks, 256, 0, s>>>(a.ws, dw, Cout, Cin, KH * KW, pl.splits, a.co_r, a.ci_r);
-    return imx::check_launch("conv2d_wgrad_reduce");
+    return launch_reduce(a.ws, dw, nullptr, nullptr, Cout, Cin, KH * KW, pl.splits, a.co_r, a.ci_r, s);
+}
+
+// The weight gradient plus dot += <dw, w_orig> (the inner product the spectral-norm gradient needs), formed while the
+// split-K partial sums are reduced.  dot: one fp32, zeroed by the caller.
+extern "C" int imx_conv2d_igemm_wgrad_dot_bf16(const imx_bf16* x, const imx_bf16* dy, float* dw, const float* w_orig,
+                                               float* dot, void* workspace, int64_t workspace_bytes,
+                                               int N, int H, int W, int Cin, int Cin_p,
+                                               int Cout, int Cout_p, int KH, int KW,
+                                               int stride, int pad, imx_stream_t stream) {
+    IMX_REQUIRE(dw && w_orig && dot, "conv2d_wgrad_dot: null pointer");
+    IMX_REQUIRE(N > 0, "conv2d_wgrad_dot: empty batch");
+    cudaStream_t s = (cudaStream_t)stream;
+    WgradArgs a;
+    Plan pl;
+    int rc = wgrad_gemm(x, dy, workspace, workspace_bytes, N, H, W, Cin, Cin_p, Cout, Cout_p, KH, KW, stride, pad, s, a, pl);
+    if (rc) return rc;
+    return launch_reduce(a.ws, dw, w_orig, dot, Cout, Cin, KH * KW, pl.splits, a.co_r, a.ci_r, s);
 }
 
 // Data-parallel variant, step 1: only the split-K GEMM.  plan_out = {splits, co_r, ci_r}.

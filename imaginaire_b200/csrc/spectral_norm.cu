@@ -232,6 +232,19 @@ extern "C" int imx_spectral_norm_weight_grad_f32(float* G, const float* W, const
     return imx::check_launch("spectral_norm_weight_grad");
 }
 
+// The correction alone, for a caller that already holds dot = <G, W> (imx_conv2d_igemm_wgrad_dot_bf16 forms it while
+// it reduces the split-K partial sums).
+extern "C" int imx_spectral_norm_weight_grad_apply_f32(float* G, const float* u, const float* v, const float* inv_sigma,
+                                                       const float* dot, int R, int C, imx_stream_t stream) {
+    IMX_REQUIRE(R > 0 && C > 0, "spectral_norm_weight_grad_apply: bad size");
+    IMX_REQUIRE(G && u && v && inv_sigma && dot, "spectral_norm_weight_grad_apply: null pointer");
+    const long n = (long)R * C;
+    long b2 = (n + kT - 1) / kT;
+    if (b2 > 8L * imx::kNumSMs) b2 = 8L * imx::kNumSMs;
+    sn_grad_kernel<<<(int)b2, kT, 0, (cudaStream_t)stream>>>(G, u, v, inv_sigma, dot, R, C);
+    return imx::check_launch("spectral_norm_weight_grad_apply");
+}
+
 // ---------------------------------------------------------------------------------------------
 // All spectrally normalised layers of a network in one go.  The per-layer version above is a
 // chain of four small launches; a generator forward has ~90 such layers whose iterations depend

@@ -199,11 +199,10 @@ class _Conv2d(torch.autograd.Function):
             sync.wgrad(weight, x, dy, cin, cout, kh, kw, ctx.stride, ctx.pad,
                        sn=(weight.detach(), u, v, inv_sigma) if inv_sigma is not None else None)
         elif ctx.needs_input_grad[1]:
-            dw = _conv2d_wgrad(x, dy, cin, cout, kh, kw, ctx.stride, ctx.pad)   # d/d(w * inv_sigma)
-            if inv_sigma is not None:
-                # W_eff = W / sigma, sigma = u^T W v (u, v constants):
-                # dL/dW = G / sigma - (<G, W> / sigma^2) u v^T
-                ops.spectral_norm_weight_grad_(dw, weight.detach(), u, v, inv_sigma)
+            # W_eff = W / sigma, sigma = u^T W v (u, v constants): dL/dW = G / sigma - (<G, W> / sigma^2) u v^T with
+            # G = d/d(w * inv_sigma); the generic kernel forms <G, W> while it reduces its split-K partial sums
+            sn = (weight.detach(), u, v, inv_sigma) if inv_sigma is not None else None
+            dw = _conv2d_wgrad(x, dy, cin, cout, kh, kw, ctx.stride, ctx.pad, sn)
         if want_db:
             # over the padded channels, then the logical ones
             db = (chsum if chsum is not None else ops.channel_sum(dy))[:cout]
@@ -230,19 +229,24 @@ def _small_cout_conv(x, w_taps, bias, kh, kw, pad, cout, inv_sigma):
     return ops.shift_add_taps(prod, bias, kh, kw, pad, cout)
 
 
-def _conv2d_wgrad(x, dy, cin, cout, kh, kw, stride, pad):
-    """Filter gradient [Cout, Cin, KH, KW] (fp32) of conv2d(x) given dy."""
+def _conv2d_wgrad(x, dy, cin, cout, kh, kw, stride, pad, sn=None):
+    """Filter gradient [Cout, Cin, KH, KW] (fp32) of conv2d(x) given dy; with sn = (weight_orig, u, v, inv_sigma) the
+    gradient for a spectrally normalised layer's weight_orig."""
     if _small_cin(x.shape[1], kh, kw):
         col = ops.im2col_c8(x, kh, kw, stride, pad)
         g = ops.conv2d_wgrad(col, dy, kh * kw * 8, cout, 1, 1, 1, 0)            # [Cout, (tap, ci)]
-        return g.view(cout, kh, kw, 8).permute(0, 3, 1, 2)[:, :cin].contiguous()
-    if dy.shape[1] == 8 and _small_cout(cout, kh, kw, stride, pad):
+        dw = g.view(cout, kh, kw, 8).permute(0, 3, 1, 2)[:, :cin].contiguous()
+    elif dy.shape[1] == 8 and _small_cout(cout, kh, kw, stride, pad):
         # dW[co][ci][t] = sum_p x[p][ci] * dy[p - t + pad][co]: patches of dy with flipped taps
         cin_p = x.shape[1]
         col = ops.im2col_c8(dy, kh, kw, 1, kh - 1 - pad)
         g = ops.conv2d_wgrad(col, x, kh * kw * 8, cin_p, 1, 1, 1, 0)            # [Cin_p, (flipped tap, co)]
-        return g.view(cin_p, kh, kw, 8).flip(1, 2).permute(3, 0, 1, 2)[:cout, :cin].contiguous()
-    return ops.conv2d_wgrad(x, dy, cin, cout, kh, kw, stride, pad)
+        dw = g.view(cin_p, kh, kw, 8).flip(1, 2).permute(3, 0, 1, 2)[:cout, :cin].contiguous()
+    else:
+        return ops.conv2d_wgrad(x, dy, cin, cout, kh, kw, stride, pad, sn=sn)
+    if sn is not None:
+        ops.spectral_norm_weight_grad_(dw, *sn)
+    return dw
 
 
 def conv2d_dgrad(dy, weight, stride, pad, h, w, cin_p, inv_sigma=None):

@@ -122,13 +122,11 @@ class PeerGradSync:
             raise RuntimeError('PeerGradSync: a filter is used %d times in one backward but max_uses is %d'
                                % (use + 1, self.max_uses))
         if self.flat:
-            # the complete local gradient (GEMM + local split-K reduction) straight into this rank's arena slot
-            ws = torch.empty((max(int(nbytes), 16),), dtype=torch.uint8, device=x.device)
-            lib.call('imx_conv2d_igemm_wgrad_bf16', x.data_ptr(), dy.data_ptr(), self.grad_view(weight, use).data_ptr(),
-                     ws.data_ptr(), int(nbytes), n, h, w, cin, cin_p, cout, cout_p, kh, kw, stride, pad, ops._stream())
+            # the complete local gradient (GEMM + local split-K reduction + this application's spectral-norm
+            # correction, which is linear in the gradient: correcting before the average equals correcting after, and
+            # nothing order-dependent is left to do once the ranks hold the same bits) straight into this rank's slot
+            ops.conv2d_wgrad(x, dy, cin, cout, kh, kw, stride, pad, out=self.grad_view(weight, use), sn=sn)
             self.uses[key] = use + 1
-            if sn is not None:
-                self.pending_sn.append((key, use) + tuple(sn))
             return
         off = self._region((key, use), int(nbytes))
         plan = (ctypes.c_int * 3)()

@@ -517,8 +517,11 @@ def shift_add_taps(p, bias, kh, kw, pad, cout):
     return y
 
 
-def conv2d_wgrad(x, dy, cin, cout, kh, kw, stride=1, pad=0):
-    """dW (fp32, [Cout, Cin, KH, KW]) from x (NHWC bf16, C = Cin_p) and dy (NHWC bf16, C = Cout_p)."""
+def conv2d_wgrad(x, dy, cin, cout, kh, kw, stride=1, pad=0, out=None, sn=None):
+    """dW (fp32, [Cout, Cin, KH, KW]) from x (NHWC bf16, C = Cin_p) and dy (NHWC bf16, C = Cout_p); written into `out`
+    when given.  sn = (weight_orig, u, v, inv_sigma): the layer is spectrally normalised and the result is the
+    gradient for weight_orig, G / sigma - (<G, W> / sigma^2) u v^T -- the inner product is formed while the split-K
+    partial sums are reduced (imx_conv2d_igemm_wgrad_dot_bf16), the correction is one more pass."""
     _req_cuda(x, dy); _req_nhwc(x, 'x'); _req_nhwc(dy, 'dy')
     n, cin_p, h, w = x.shape
     cout_p = dy.shape[1]
@@ -527,9 +530,20 @@ def conv2d_wgrad(x, dy, cin, cout, kh, kw, stride=1, pad=0):
     if nbytes < 0:
         raise _C.ImxError('imx_conv2d_wgrad_workspace_bytes: %s' % lib.last_error())
     ws = torch.empty((max(int(nbytes), 16),), dtype=torch.uint8, device=x.device)
-    dw = torch.empty((cout, cin, kh, kw), dtype=torch.float32, device=x.device)
-    lib.call('imx_conv2d_igemm_wgrad_bf16', _ptr(x), _ptr(dy), _ptr(dw), _ptr(ws), int(nbytes), n, h, w, cin, cin_p,
-             cout, cout_p, kh, kw, stride, pad, _stream())
+    dw = out if out is not None else torch.empty((cout, cin, kh, kw), dtype=torch.float32, device=x.device)
+    if sn is None or n == 0 or kh * kw > 47:
+        lib.call('imx_conv2d_igemm_wgrad_bf16', _ptr(x), _ptr(dy), _ptr(dw), _ptr(ws), int(nbytes), n, h, w, cin, cin_p,
+                 cout, cout_p, kh, kw, stride, pad, _stream())
+        if sn is not None:
+            spectral_norm_weight_grad_(dw, *sn)
+        return dw
+    weight, u, v, inv_sigma = sn
+    _req_f32c(weight, 'weight')
+    dot = torch.zeros((1,), dtype=torch.float32, device=x.device)
+    lib.call('imx_conv2d_igemm_wgrad_dot_bf16', _ptr(x), _ptr(dy), _ptr(dw), _ptr(weight), _ptr(dot), _ptr(ws), int(nbytes),
+             n, h, w, cin, cin_p, cout, cout_p, kh, kw, stride, pad, _stream())
+    lib.call('imx_spectral_norm_weight_grad_apply_f32', _ptr(dw), _ptr(u), _ptr(v), _ptr(inv_sigma), _ptr(dot), cout,
+             cin * kh * kw, _stream())
     return dw
 
 

@@ -201,6 +201,10 @@ IMX_API int imx_spectral_norm_ema_update_f32(const void* descs, const void* targ
 IMX_API int imx_spectral_norm_weight_grad_f32(float* G, const float* W, const float* u, const float* v,
                                               const float* inv_sigma, float* dot_scratch, int R, int C,
                                               imx_stream_t stream);
+/* The second half of imx_spectral_norm_weight_grad_f32 for a caller that already holds dot = <G, W>:
+ * G = G * inv_sigma - dot * inv_sigma^2 * u v^T, in place.  ref: as above */
+IMX_API int imx_spectral_norm_weight_grad_apply_f32(float* G, const float* u, const float* v, const float* inv_sigma,
+                                                    const float* dot, int R, int C, imx_stream_t stream);
 
 /* ----------------------------------------------- normalisation + SPADE -- */
 
@@ -367,6 +371,16 @@ IMX_API int imx_conv2d_igemm_wgrad_bf16(const imx_bf16* x, const imx_bf16* dy, f
 IMX_API int64_t imx_conv2d_wgrad_workspace_bytes(int N, int H, int W, int Cin, int Cin_p,
                                          int Cout, int Cout_p, int KH, int KW,
                                          int stride, int pad);
+
+/* imx_conv2d_igemm_wgrad_bf16 plus *dot += <dw, w_orig> (w_orig: fp32, dw's layout; dot: one fp32 the caller zeroed),
+ * accumulated while the split-K partial sums are reduced: the inner product of the spectral-norm gradient
+ * (imx_spectral_norm_weight_grad_f32) without another pass over both tensors.
+ * ref: autograd of torch.nn.utils.spectral_norm's weight = weight_orig / sigma (imaginaire/layers/weight_norm.py:85) */
+IMX_API int imx_conv2d_igemm_wgrad_dot_bf16(const imx_bf16* x, const imx_bf16* dy, float* dw, const float* w_orig,
+                                            float* dot, void* workspace, int64_t workspace_bytes,
+                                            int N, int H, int W, int Cin, int Cin_p,
+                                            int Cout, int Cout_p, int KH, int KW,
+                                            int stride, int pad, imx_stream_t stream);
 
 /* Data-parallel weight gradient without a separate gradient collective: the
  * split-K partial sums of every rank live in peer-mapped NVLink memory (e.g.

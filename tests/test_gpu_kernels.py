@@ -565,6 +565,35 @@ def test_bilinear_up2x_add_vs_torch(shape):
     assert H.rel_err(only_up.float().cpu(), F.interpolate(src, scale_factor=2, mode='bilinear', align_corners=False)) < 4e-3
 
 
+@pytest.mark.parametrize('case', [(2, 64, 64, 16, 32, 3, 1, 1), (1, 40, 72, 13, 11, 5, 1, 2), (4, 256, 128, 32, 64, 1, 1, 0),
+                                  (2, 130, 70, 9, 9, 4, 2, 1)])
+def test_wgrad_with_fused_spectral_norm_inner_product(case):
+    """ops.conv2d_wgrad(sn=...): <G, W> is formed while the split-K partial sums are reduced
+    (imx_conv2d_igemm_wgrad_dot_bf16), then G / sigma - (<G, W> / sigma^2) u v^T.  Against the same two steps on
+    the CPU in float64 from torch's weight gradient."""
+    from imaginaire_b200 import ops
+    n, cin, cout, h, w, k, s, p = case
+    g = torch.Generator().manual_seed(141)
+    ho, wo_ = (h + 2 * p - k) // s + 1, (w + 2 * p - k) // s + 1
+    x = torch.randn(n, cin, h, w, generator=g).bfloat16().float()
+    dy = torch.randn(n, cout, ho, wo_, generator=g).bfloat16().float()
+    wt = torch.randn(cout, cin, k, k, generator=g)
+    u = torch.nn.functional.normalize(torch.randn(cout, generator=g), dim=0)
+    v = torch.nn.functional.normalize(torch.randn(cin * k * k, generator=g), dim=0)
+    inv_sigma = torch.tensor([1.0 / 3.7])
+    cin_p, cout_p = ops.round_up(cin, 8), ops.round_up(cout, 8)
+    xp = torch.zeros(n, cin_p, h, w); xp[:, :cin] = x
+    dp = torch.zeros(n, cout_p, ho, wo_); dp[:, :cout] = dy
+    out = torch.full((cout, cin, k, k), float('nan'), device=DEV)
+    got = ops.conv2d_wgrad(nhwc(xp), nhwc(dp), cin, cout, k, k, s, p, out=out,
+                           sn=(wt.to(DEV), u.to(DEV), v.to(DEV), inv_sigma.to(DEV)))
+    assert got.data_ptr() == out.data_ptr()
+    G = torch.nn.grad.conv2d_weight(x, (cout, cin, k, k), dy, stride=s, padding=p).double()
+    dot = (G * wt.double()).sum()
+    ref = G * float(inv_sigma) - dot * float(inv_sigma) ** 2 * torch.outer(u.double(), v.double()).view_as(G)
+    assert H.rel_err(got.cpu(), ref) < 2e-4
+
+
 def test_fused_adam_device_step_counters_match_torch_adam():
     """FusedAdam(capturable=True): step numbers on the device, bias corrections formed in the kernel
     (imx_adam_multi_tensor_f32_capturable) -- the form a CUDA-graph replay needs.  Five steps against torch.optim.Adam;
