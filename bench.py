@@ -418,13 +418,29 @@ def run_ours(args):
     launches = lib.launches
     ms = start.elapsed_time(end)
     # ---- timed region 2: end to end (pinned host -> device copies + loss read-back each step) ----
+    # The copies run on a second stream into two staging batches, so the upload of batch i + 1 overlaps the compute
+    # of batch i, as a data loader with pinned memory and non_blocking copies (or the reference's prefetching
+    # iterator) does it.  Every step's inputs are copied inside the timed region (the first one right after the start
+    # event), and every step ends with a device -> host read of its losses.
+    copy_stream = torch.cuda.Stream()
+    staging = [{k: torch.empty_like(v) for k, v in resident.items()} for _ in range(2)]
+    ready = [torch.cuda.Event(), torch.cuda.Event()]
+
+    def upload(i):
+        with torch.cuda.stream(copy_stream):
+            for k, v in host.items():
+                staging[i % 2][k].copy_(v, non_blocking=True)
+            ready[i % 2].record(copy_stream)
+
     barrier()
     start.record()
     d2h = 0
-    for _ in range(args.steps):
-        # eager: fresh device tensors from the pinned host batch; graphed: the same copies, into the graph's inputs
-        data = host if use_graph else {k: v.to(dev, non_blocking=True) for k, v in host.items()}
-        g_loss, d_loss = one_step(data)
+    upload(0)
+    for i in range(args.steps):
+        if i + 1 < args.steps:
+            upload(i + 1)       # staging[(i + 1) % 2] was last read by step i - 1, which the loss read-back has waited for
+        torch.cuda.current_stream().wait_event(ready[i % 2])
+        g_loss, d_loss = one_step(staging[i % 2])
         losses = torch.stack([g_loss.reshape(()), d_loss.reshape(())]).cpu()   # device -> host read of the step's result
         d2h = losses.numel() * losses.element_size()
     end.record()
