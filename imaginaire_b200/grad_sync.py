@@ -237,7 +237,7 @@ _FLAT = []
 
 def broadcast_state(model, group=None, src=0):
     """Rank `src`'s parameters and buffers to every rank (what the DDP constructor does), coalesced per dtype."""
-    tensors = [t for t in list(model.parameters()) + list(model.buffers()) if t.is_cuda]
+    tensors = list(model.parameters()) + list(model.buffers())
     by_dtype = {}
     for t in tensors:
         by_dtype.setdefault(t.dtype, []).append(t)

@@ -187,3 +187,74 @@ def test_loss_and_pooling_helpers_have_no_cpu_path():
         with pytest.raises(RuntimeError, match='no CPU path'):
             fn(*args)
 
+
+
+def test_imaginaire_alias_package_and_entry_points():
+    """`import imaginaire.x.y` returns the module object imaginaire_b200.x.y, so the reference's config files
+    (cfg.gen.type / cfg.dis.type / cfg.trainer.type name modules by path, train.py:33-60) and user code resolve to the
+    native modules; the trainer and the factory functions have the reference's signatures
+    (trainers/base.py:42-51, utils/trainer.py:40-125)."""
+    import importlib
+    import inspect
+    import imaginaire
+    import imaginaire_b200.generators.spade as g
+    import imaginaire_b200.layers as layers
+    assert importlib.import_module('imaginaire.generators.spade') is g
+    assert importlib.import_module('imaginaire.layers') is layers
+    from imaginaire.layers import Conv2dBlock, Res2dBlock
+    assert Conv2dBlock is layers.Conv2dBlock and Res2dBlock is layers.Res2dBlock
+    from imaginaire.third_party.resample2d.resample2d import Resample2d
+    import imaginaire_b200.third_party.resample2d.resample2d as r2d
+    assert Resample2d is r2d.Resample2d
+    with pytest.raises(ModuleNotFoundError):
+        importlib.import_module('imaginaire.does_not_exist')
+    from imaginaire_b200.config import Config
+    cfg = Config(os.path.join(ROOT, 'configs', 'spade_c3_256x512.yaml'))
+    for key in (cfg.gen.type, cfg.dis.type, cfg.trainer.type):
+        assert importlib.import_module(key).__name__.startswith('imaginaire_b200.')
+    trainer_cls = importlib.import_module(cfg.trainer.type).Trainer
+    assert list(inspect.signature(trainer_cls.__init__).parameters)[1:] == \
+        ['cfg', 'net_G', 'net_D', 'opt_G', 'opt_D', 'sch_G', 'sch_D', 'train_data_loader', 'val_data_loader']
+    from imaginaire.utils import trainer as ut
+    assert list(inspect.signature(ut.get_trainer).parameters) == \
+        ['cfg', 'net_G', 'net_D', 'opt_G', 'opt_D', 'sch_G', 'sch_D', 'train_data_loader', 'val_data_loader']
+    for name in ('gen_update', 'dis_update', 'start_of_iteration', 'end_of_iteration', 'start_of_epoch', 'end_of_epoch',
+                 'save_checkpoint', 'load_checkpoint', 'gen_forward', 'dis_forward'):
+        assert callable(getattr(trainer_cls, name)), name
+
+
+def test_schedulers_and_checkpoint_round_trip(tmp_path):
+    """get_scheduler (utils/trainer.py:219-240) and the checkpoint format of trainers/base.py:199-265, 795-829 on a
+    toy pair of networks (CPU: no kernel is launched)."""
+    import types
+    import torch
+    from imaginaire_b200.config import AttrDict
+    from imaginaire_b200.trainers.base import BaseTrainer, _save_checkpoint
+    from imaginaire_b200.utils.trainer import WrappedModel, get_scheduler
+
+    class Toy(BaseTrainer):
+        def _init_loss(self, cfg):
+            pass
+    cfg = AttrDict(trainer=AttrDict(model_average=False), logdir=str(tmp_path), snapshot_save_iter=10 ** 9,
+                   snapshot_save_epoch=10 ** 9, logging_iter=100,
+                   gen_opt=AttrDict(lr_policy=AttrDict(type='step', step_size=2, gamma=0.5, iteration_mode=True)),
+                   dis_opt=AttrDict(lr_policy=AttrDict(type='constant', iteration_mode=False)))
+    net_G, net_D = WrappedModel(torch.nn.Linear(3, 2)), WrappedModel(torch.nn.Linear(2, 1))
+    opt_G, opt_D = torch.optim.Adam(net_G.parameters(), lr=1e-2), torch.optim.Adam(net_D.parameters(), lr=1e-2)
+    sch_G, sch_D = get_scheduler(cfg.gen_opt, opt_G), get_scheduler(cfg.dis_opt, opt_D)
+    t = Toy(cfg, net_G, net_D, opt_G, opt_D, sch_G, sch_D, (), None)
+    t.start_iteration_time = 0.0
+    for it in range(1, 4):
+        opt_G.step()
+        t.end_of_iteration({}, 0, it)
+    assert abs(sch_G.get_last_lr()[0] - 0.5e-2) < 1e-12 and sch_D.get_last_lr()[0] == 1e-2
+    path = t.save_checkpoint(3, 7)
+    assert os.path.basename(path) == 'epoch_00003_iteration_000000007_checkpoint.pt'
+    assert open(os.path.join(str(tmp_path), 'latest_checkpoint.txt')).read() == 'latest_checkpoint: ' + os.path.basename(path)
+    ck = torch.load(path, weights_only=False)
+    assert set(ck) == {'net_G', 'net_D', 'opt_G', 'opt_D', 'sch_G', 'sch_D', 'current_epoch', 'current_iteration'}
+    assert list(ck['net_G']) == ['module.weight', 'module.bias']           # the wrapper's prefix, as in the reference
+    with torch.no_grad():
+        net_G.module.weight.zero_()
+    assert t.load_checkpoint(cfg, 'no/such/file') == (3, 7)                # resumes from latest_checkpoint.txt
+    assert torch.equal(net_G.module.weight, ck['net_G']['module.weight'])

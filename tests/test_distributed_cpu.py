@@ -45,6 +45,26 @@ def _worker(rank, world, port, out_dir):
     grad = blk.module.layers['conv'].weight_orig.grad.clone()
     both = D.dist_all_gather_tensor(grad)
     assert torch.allclose(both[0], both[1])
+    # the flat all-reduce that replaces a DDP wrapper for the small parameters (grad_sync.FlatGradSync) and the
+    # initial state broadcast: gradients of the trainable parameters are averaged, frozen ones are left alone
+    from imaginaire_b200 import grad_sync
+    torch.manual_seed(rank)                         # different initial weights per rank on purpose
+    net = torch.nn.Sequential(torch.nn.Linear(6, 5), torch.nn.BatchNorm1d(5), torch.nn.Linear(5, 3))
+    grad_sync.broadcast_state(net)
+    w0 = D.dist_all_gather_tensor(net[0].weight.detach().clone())
+    assert torch.equal(w0[0], w0[1])
+    flat = grad_sync.FlatGradSync(list(net.parameters()))
+    net[2].bias.requires_grad_(False)
+    net(torch.full((4, 6), float(rank + 1)) + torch.arange(4.0).view(4, 1)).square().sum().backward()
+    local = [p.grad.clone() if p.grad is not None else None for p in net.parameters()]
+    grad_sync.finish_all()
+    for p, g in zip(net.parameters(), local):
+        if g is None:
+            assert p.grad is None
+            continue
+        both = D.dist_all_gather_tensor(g)
+        assert torch.allclose(p.grad, (both[0] + both[1]) / 2, atol=1e-6)
+    flat.close()
     with open(os.path.join(out_dir, 'ok%d' % rank), 'w') as f:
         f.write('ok')
     dist.destroy_process_group()
