@@ -236,13 +236,17 @@ _FLAT = []
 
 
 def broadcast_state(model, group=None, src=0):
-    """Rank `src`'s parameters and buffers to every rank (what the DDP constructor does), coalesced per dtype."""
-    tensors = list(model.parameters()) + list(model.buffers())
-    by_dtype = {}
-    for t in tensors:
-        by_dtype.setdefault(t.dtype, []).append(t)
+    """Rank `src`'s parameters and buffers to every rank (what the DDP constructor does), coalesced per dtype and
+    device.  Host-side tensors (the EMA wrapper's update counter) are skipped under NCCL, which moves device memory
+    only: they are counters that every rank advances identically."""
+    by_kind = {}
+    nccl = dist.get_backend(group) == 'nccl'
+    for t in list(model.parameters()) + list(model.buffers()):
+        if nccl and not t.is_cuda:
+            continue
+        by_kind.setdefault((t.dtype, t.device), []).append(t)
     with torch.no_grad():
-        for ts in by_dtype.values():
+        for ts in by_kind.values():
             flat = torch.cat([t.reshape(-1) for t in ts])
             dist.broadcast(flat, src=src, group=group)
             torch._foreach_copy_(ts, [c.view_as(t) for c, t in zip(flat.split([t.numel() for t in ts]), ts)])
