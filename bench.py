@@ -131,21 +131,25 @@ class ConvProbe:
                 s.record()
                 out = fn(*a, **k)
                 e.record()
-                probe.records.append((tag, flops_fn(out, *a, **k), s, e, probe.describe(tag, out, a, k)))
+                probe.records.append((tag, flops_fn(out, a, k), s, e, probe.describe(tag, out, a, k)))
                 return out
             return wrapper
 
-        def fprop_flops(out, x, wpk, cout, kh, kw, *a, **k):
+        # (result, positional arguments, keyword arguments) of the wrapped call
+        def fprop_flops(out, a, k):
+            x, wpk, cout, kh, kw = a[:5]
             # algorithmic: the logical channel counts (a 35-channel label map is stored with 40 channels, an image
             # with 8; the padding is the kernel's business, not work the reference does)
             n, _, ho, wo = out.shape
             return 2.0 * n * ho * wo * cout * getattr(wpk, '_imx_inner', x.shape[1]) * kh * kw
 
-        def wgrad_flops(out, x, dy, cin, cout, kh, kw, *a, **k):
+        def wgrad_flops(out, a, k):
+            x, dy, cin, cout, kh, kw = a[:6]
             n, _, ho, wo = dy.shape
             return 2.0 * n * ho * wo * cout * cin * kh * kw
 
-        def gb_flops(out, hidden, wgb, bg, bb, x, mean, rstd, w, b, c, kh, kw, *a, **k):
+        def gb_flops(out, a, k):
+            hidden, c, kh, kw = a[0], a[9], a[10], a[11]
             n, chp, h, wd = hidden.shape
             return 2.0 * n * h * wd * (2 * c) * chp * kh * kw
 

@@ -21,12 +21,23 @@ data = {k: v.to(dev) for k, v in bench.synthetic_batch(cfg, int(sys.argv[1]) if 
 for _ in range(2):
     trainer.step(dict(data))
 torch.cuda.synchronize()
+step = trainer.step
+if os.environ.get('GRAPH'):        # GRAPH=1: profile the CUDA-graph replay (what bench.py times) instead of the eager loop
+    from imaginaire_b200.utils.cuda_graph import GraphedTrainerStep
+    step = GraphedTrainerStep(trainer, data)
+    for _ in range(3):
+        step(dict(data))
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
 ATEN = bool(os.environ.get('ATEN'))     # ATEN=1: also list the ATen ops by their own kernel time, with shapes and call sites
 _xc = torch._C._profiler._ExperimentalConfig(verbose=True) if ATEN else None     # needed for Python stacks in key_averages
 with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], record_shapes=ATEN, with_stack=ATEN,
              experimental_config=_xc) as prof:
-    trainer.step(dict(data))
+    step(dict(data))
     torch.cuda.synchronize()
+if os.environ.get('GRAPH'):
+    step.close()
 if rank != 0:
     sys.exit(0)
 if ATEN:
