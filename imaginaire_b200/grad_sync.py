@@ -44,7 +44,7 @@ def lookup(weight):
 
 
 class PeerGradSync:
-    def __init__(self, weights, workspace_bytes=6 << 30, group=None, max_uses=1):
+    def __init__(self, weights, workspace_bytes=6 << 30, group=None, max_uses=1, extra_params=None):
         import torch.distributed._symmetric_memory as symm_mem
         self.group = group if group is not None else dist.group.WORLD
         self.world = dist.get_world_size(self.group)
@@ -64,6 +64,12 @@ class PeerGradSync:
             for w in self.params:
                 self.offset[(w.data_ptr(), use)] = total
                 total += (w.numel() + 63) // 64 * 64          # 256-byte aligned slots
+        # `extra_params`: everything else that needs averaging (biases, norm parameters, linear layers, filters with
+        # <= 8 channels).  Their gradients are gathered into one more segment at the end of the arena and ride the same
+        # reduce-scatter / all-gather launches and barriers: no NCCL call is left in the iteration.
+        self.extra_params = list(extra_params) if extra_params is not None else []
+        self.extra_off = total
+        total += (sum(p.numel() for p in self.extra_params) + 63) // 64 * 64
         self.arena = symm_mem.empty(total, dtype=torch.float32, device=dev)
         self.arena_hdl = symm_mem.rendezvous(self.arena, self.group.group_name)
         import os
@@ -150,7 +156,8 @@ class PeerGradSync:
             if k not in self.uses and p.grad is not None and p.grad.data_ptr() != self.grad_view(p).data_ptr():
                 dist.all_reduce(p.grad, op=dist.ReduceOp.SUM, group=self.group)
                 p.grad.div_(self.world)
-        if not self.uses:
+        extra = [p.grad for p in self.extra_params if p.requires_grad and p.grad is not None] if self.flat else []
+        if not self.uses and not extra:
             return
         used = tuple(sorted(((k, u) for k, n in self.uses.items() for u in range(n)), key=lambda ku: self.offset[ku]))
         descs = self._gather_descs.get(used)
@@ -162,18 +169,29 @@ class PeerGradSync:
         lib = _C.lib()
         stream = ops._stream()
         if self.flat:
-            segs = self._seg_descs.get(used)
+            n_extra = sum(g.numel() for g in extra)
+            extra_views = None
+            if n_extra:
+                flat = self.arena[self.extra_off:self.extra_off + n_extra]
+                torch.cat([g.reshape(-1) for g in extra], out=flat)
+                extra_views = [c.view_as(g) for c, g in zip(flat.split([g.numel() for g in extra]), extra)]
+            segs = self._seg_descs.get((used, n_extra))
             if segs is None:
                 rows = [[self.offset[ku], self.by_ptr[ku[0]].numel()] for ku in used]
-                segs = (torch.tensor(rows, dtype=torch.int64).to(self.arena.device), max(r[1] for r in rows))
-                self._seg_descs[used] = segs
+                if n_extra:
+                    rows.append([self.extra_off, n_extra])
+                segs = (torch.tensor(rows, dtype=torch.int64).to(self.arena.device), max(r[1] for r in rows), len(rows))
+                self._seg_descs[(used, n_extra)] = segs
+            n_seg = segs[2]
             self.arena_hdl.barrier(channel=0)              # every rank's local gradients of this backward are written
-            lib.call('imx_peer_reduce_scatter_f32', self._arena_table, self.world, self.rank, segs[0].data_ptr(), len(used),
+            lib.call('imx_peer_reduce_scatter_f32', self._arena_table, self.world, self.rank, segs[0].data_ptr(), n_seg,
                      int(segs[1]), 1.0 / self.world, stream)
             self.arena_hdl.barrier(channel=1)              # every rank has reduced its chunks
-            lib.call('imx_peer_all_gather_f32', self._arena_table, self.world, self.rank, segs[0].data_ptr(), len(used),
+            lib.call('imx_peer_all_gather_f32', self._arena_table, self.world, self.rank, segs[0].data_ptr(), n_seg,
                      int(segs[1]), stream)
             self.arena_hdl.barrier(channel=2)              # nobody reads my chunks any more: in-place edits are safe
+            if extra_views is not None:
+                torch._foreach_copy_(extra, extra_views)
             self._finish_local()
             return
         self.ws_hdl.barrier(channel=0)                     # every rank's partial sums of this backward are written

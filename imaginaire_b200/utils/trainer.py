@@ -137,22 +137,24 @@ def _wrap_model(model, find_unused=None, max_uses=1):
             from .. import grad_sync
             filters = grad_sync.eligible_filters(model)
             sync, ok = None, torch.ones(1, device='cuda')
+            flat_grads = os.environ.get('IMX_FLAT_GRADS', '1') != '0'
+            carried = {id(p) for _, p in filters}
             if filters:
                 try:
                     sync = grad_sync.PeerGradSync(
                         [p for _, p in filters], max_uses=max_uses,
+                        extra_params=[p for p in model.parameters() if id(p) not in carried] if flat_grads else None,
                         workspace_bytes=int(float(os.environ.get('IMX_PEER_GRADS_WS_GB', '16' if max_uses == 1 else '8')) * (1 << 30)))
                 except Exception as e:     # noqa: BLE001 - any failure means "use NCCL for everything"
                     print('peer-memory gradient path unavailable (%s); using DDP for all parameters' % repr(e)[:200])
                     ok.zero_()
                 dist.all_reduce(ok, op=dist.ReduceOp.MIN)
                 if float(ok) > 0:
-                    if os.environ.get('IMX_FLAT_GRADS', '1') != '0':
-                        # everything else: one flat all-reduce after the backward instead of a DDP wrapper (no autograd
-                        # hooks / buckets / unused-parameter search; the iteration stays capturable as a CUDA graph)
-                        carried = {id(p) for _, p in filters}
+                    if flat_grads:
+                        # everything else rides the same reduce-scatter / all-gather as one more segment of the arena
+                        # (PeerGradSync extra_params) instead of a DDP wrapper: no autograd hooks / buckets /
+                        # unused-parameter search, no NCCL call, and the iteration stays capturable as a CUDA graph
                         grad_sync.broadcast_state(model)
-                        grad_sync.FlatGradSync([p for p in model.parameters() if id(p) not in carried])
                         return WrappedModel(model)
                     DistributedDataParallel._set_params_and_buffers_to_ignore_for_model(model, [n for n, _ in filters])
                 elif sync is not None:
