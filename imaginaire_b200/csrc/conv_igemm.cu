@@ -68,6 +68,8 @@ struct ConvArgs {
     float* ws;                   // split-K: fp32 [pixels][Cout_p] partial sums (zero-filled by the host code)
     int flags;
     // plain epilogue
+    const float* scale;          // optional: one fp32 on the device, the accumulator is multiplied by it before the
+                                 // bias (1 / sigma of a spectrally normalised layer whose bf16 filter is packed unscaled)
     const float* bias;
     const uint16_t* residual;
     void* out;
@@ -307,6 +309,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 
             if constexpr (kMode == 0) {
                 constexpr int NCH = BN / 32;
+                const float acc_scale = p.scale ? __ldg(p.scale) : 1.0f;
                 const bool has_res = (p.flags & IMX_EPI_RESIDUAL) != 0;
                 const uint4* rbase = reinterpret_cast<const uint4*>(p.residual + pix * p.Cout_p + n0);
                 // residual of chunk ch: four 16-byte pieces of this pixel's row (issued two chunks ahead)
@@ -322,7 +325,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                     if (nb >= p.Cout_p) return;   // warp-uniform
                     float f[32];
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+                    for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * acc_scale;
                     if (p.flags & IMX_EPI_BIAS) {
                         const float4* sb = reinterpret_cast<const float4*>(s_epi + as * BN + ch * 32);
 #pragma unroll
@@ -584,16 +587,18 @@ using imx::aligned16;
 namespace {
 
 // Applies bias / residual / activation to the split-K sums and stores the output tensor.
-__global__ void splitk_finish_kernel(const float* __restrict__ ws, const float* __restrict__ bias,
+__global__ void splitk_finish_kernel(const float* __restrict__ ws, const float* __restrict__ scale,
+                                     const float* __restrict__ bias,
                                      const uint16_t* __restrict__ residual, void* __restrict__ out,
                                      long pixels, int Cout, int Cout_p, int flags) {
     const int c4n = Cout_p / 4;
     const long total = pixels * c4n;
+    const float sc = scale ? __ldg(scale) : 1.0f;
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
         const int c = (int)(i % c4n) * 4;
         const long pix = i / c4n;
         const float4 v4 = __ldg(reinterpret_cast<const float4*>(ws) + i);
-        float f[4] = {v4.x, v4.y, v4.z, v4.w};
+        float f[4] = {v4.x * sc, v4.y * sc, v4.z * sc, v4.w * sc};
         if (flags & IMX_EPI_BIAS) {
 #pragma unroll
             for (int j = 0; j < 4; ++j)
@@ -666,8 +671,8 @@ int check_fprop_args(int N, int H, int W, int Cin_p, int Cout, int Cout_p, int K
     return IMX_OK;
 }
 
-int fprop_impl(const imx_bf16* x, const imx_bf16* wpk, const float* bias, const imx_bf16* residual, void* out,
-               float* stats, void* workspace, int64_t workspace_bytes, int N, int H, int W, int Cin_p, int Cout,
+int fprop_impl(const imx_bf16* x, const imx_bf16* wpk, const float* scale, const float* bias, const imx_bf16* residual,
+               void* out, float* stats, void* workspace, int64_t workspace_bytes, int N, int H, int W, int Cin_p, int Cout,
                int Cout_p, int KH, int KW, int stride, int pad, int flags, imx_stream_t stream) {
     IMX_REQUIRE(x && wpk && out, "conv2d_fprop: null pointer");
     int rc = check_fprop_args(N, H, W, Cin_p, Cout, Cout_p, KH, KW, stride, pad);
@@ -690,7 +695,7 @@ int fprop_impl(const imx_bf16* x, const imx_bf16* wpk, const float* bias, const 
     rc = setup(a, ta, tb, x, wpk, N, H, W, Cin_p, Cout, KH, KW, stride, pad, BN, MT);
     if (rc) return rc;
     a.Cout = Cout; a.Cout_p = Cout_p; a.flags = flags;
-    a.bias = bias; a.residual = residual; a.out = out; a.stats = stats;
+    a.scale = scale; a.bias = bias; a.residual = residual; a.out = out; a.stats = stats;
     a.splits = pl.splits; a.k_per_split = pl.k_per_split; a.ws = reinterpret_cast<float*>(workspace);
     cudaStream_t s = (cudaStream_t)stream;
     if (pl.splits > 1) {
@@ -715,7 +720,7 @@ int fprop_impl(const imx_bf16* x, const imx_bf16* wpk, const float* bias, const 
     const long pixels = (long)N * a.Ho * a.Wo;
     long blocks = (pixels * (Cout_p / 4) + 255) / 256;
     if (blocks > 8L * imx::kNumSMs) blocks = 8L * imx::kNumSMs;
-    splitk_finish_kernel<<<(int)blocks, 256, 0, s>>>(a.ws, bias, reinterpret_cast<const uint16_t*>(residual), out, pixels,
+    splitk_finish_kernel<<<(int)blocks, 256, 0, s>>>(a.ws, scale, bias, reinterpret_cast<const uint16_t*>(residual), out, pixels,
                                                      Cout, Cout_p, flags);
     return imx::check_launch("conv2d_fprop_splitk_finish");
 }
@@ -727,8 +732,21 @@ extern "C" int imx_conv2d_igemm_fprop_bf16(const imx_bf16* x, const imx_bf16* wp
                                            int N, int H, int W, int Cin_p,
                                            int Cout, int Cout_p, int KH, int KW,
                                            int stride, int pad, int flags, imx_stream_t stream) {
-    return fprop_impl(x, wpk, bias, residual, out, stats, nullptr, 0, N, H, W, Cin_p, Cout, Cout_p, KH, KW, stride, pad,
-                      flags, stream);
+    return fprop_impl(x, wpk, nullptr, bias, residual, out, stats, nullptr, 0, N, H, W, Cin_p, Cout, Cout_p, KH, KW, stride,
+                      pad, flags, stream);
+}
+
+// y = act(scale * conv(x, wpk) + bias) (+ residual): `scale` is ONE fp32 in device memory (e.g. 1 / sigma of a
+// spectrally normalised layer), so that the bf16 filter can be packed once per optimizer step instead of once per
+// application with its current sigma folded in.  workspace may be null (no split-K).
+extern "C" int imx_conv2d_igemm_fprop_scaled_bf16(const imx_bf16* x, const imx_bf16* wpk, const float* scale,
+                                                  const float* bias, const imx_bf16* residual, void* out, float* stats,
+                                                  void* workspace, int64_t workspace_bytes,
+                                                  int N, int H, int W, int Cin_p,
+                                                  int Cout, int Cout_p, int KH, int KW,
+                                                  int stride, int pad, int flags, imx_stream_t stream) {
+    return fprop_impl(x, wpk, scale, bias, residual, out, stats, workspace, workspace_bytes, N, H, W, Cin_p, Cout, Cout_p,
+                      KH, KW, stride, pad, flags, stream);
 }
 
 extern "C" int64_t imx_conv2d_fprop_workspace_bytes(int N, int H, int W, int Cin_p, int Cout, int Cout_p,
@@ -746,8 +764,8 @@ extern "C" int imx_conv2d_igemm_fprop_splitk_bf16(const imx_bf16* x, const imx_b
                                                   int N, int H, int W, int Cin_p,
                                                   int Cout, int Cout_p, int KH, int KW,
                                                   int stride, int pad, int flags, imx_stream_t stream) {
-    return fprop_impl(x, wpk, bias, residual, out, stats, workspace, workspace_bytes, N, H, W, Cin_p, Cout, Cout_p, KH, KW,
-                      stride, pad, flags, stream);
+    return fprop_impl(x, wpk, nullptr, bias, residual, out, stats, workspace, workspace_bytes, N, H, W, Cin_p, Cout, Cout_p,
+                      KH, KW, stride, pad, flags, stream);
 }
 
 extern "C" int imx_spade_gb_conv_modulate_bf16(const imx_bf16* hidden, const imx_bf16* wgb,

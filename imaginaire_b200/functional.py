@@ -168,9 +168,13 @@ class _Conv2d(torch.autograd.Function):
             # few output channels: per-tap products as a 1x1 GEMM, then the shifted sum over taps
             y = _small_cout_conv(x, weight.detach().permute(2, 3, 0, 1), bias, kh, kw, pad, cout, inv_sigma)
         else:
-            wpk = _packed_weight(weight, cin_p, False, inv_sigma)
+            # spectrally normalised parameter: the bf16 filter is packed unscaled once per optimizer step (cached on
+            # the parameter's version) and 1 / sigma, which every application's power iteration changes, multiplies the
+            # accumulator in the epilogue
+            cached = inv_sigma is not None and isinstance(weight, torch.nn.Parameter)
+            wpk = _packed_weight(weight, cin_p, False, None if cached else inv_sigma)
             y = ops.conv2d_fprop(x, wpk, cout, kh, kw, stride, pad, bias=bias, residual=residual, flags=flags,
-                                 stats=stats)
+                                 stats=stats, scale=inv_sigma if cached else None)
         ctx.stride, ctx.pad, ctx.act = stride, pad, act
         ctx.geom = (cout, cin, kh, kw, x.shape[2], x.shape[3])
         ctx.has_bias = bias is not None
@@ -273,8 +277,9 @@ def conv2d_dgrad(dy, weight, stride, pad, h, w, cin_p, inv_sigma=None):
         # the input had 8 channels (image layers): per-tap products + shifted sum
         w_taps = weight.detach().flip(2, 3).permute(2, 3, 1, 0)    # (KH, KW, Cin, Cout) of the flipped filter
         return _small_cout_conv(dy, w_taps, None, kh, kw, pad_t, cin, inv_sigma)
-    wt = _packed_weight(weight, cout_p, True, inv_sigma)   # [Cin, KH, KW, Cout_p]
-    return ops.conv2d_fprop(dy, wt, cin, kh, kw, 1, pad_t, cout_p=cin_p)
+    cached = inv_sigma is not None and isinstance(weight, torch.nn.Parameter)      # see _Conv2d.forward
+    wt = _packed_weight(weight, cout_p, True, None if cached else inv_sigma)   # [Cin, KH, KW, Cout_p]
+    return ops.conv2d_fprop(dy, wt, cin, kh, kw, 1, pad_t, cout_p=cin_p, scale=inv_sigma if cached else None)
 
 
 def conv2d(x, weight, bias=None, residual=None, stride=1, pad=0, act=ops.ACT_NONE, stats_mode=None, sn=None):

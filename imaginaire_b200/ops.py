@@ -435,8 +435,9 @@ def spade_modulate_bwd(x, dy, mean, rstd, w, b, gamma, beta, per_instance, act, 
 # ------------------------------------------------------------ convolutions
 
 def conv2d_fprop(x, wpk, cout, kh, kw, stride=1, pad=0, bias=None, residual=None, flags=0, stats=None,
-                 cout_p=None, out_f32=False):
-    """x: NHWC bf16 (C = Cin_p), wpk: packed bf16 [Cout, KH, KW, Cin_p]."""
+                 cout_p=None, out_f32=False, scale=None):
+    """x: NHWC bf16 (C = Cin_p), wpk: packed bf16 [Cout, KH, KW, Cin_p].  scale: optional 1-element fp32 device
+    tensor; the accumulator is multiplied by it before the bias (1 / sigma with an unscaled packed filter)."""
     _req_cuda(x, wpk); _req_nhwc(x, 'x')
     n, cin_p, h, w = x.shape
     if wpk.dtype != torch.bfloat16 or not wpk.is_contiguous() or wpk.shape[-1] != cin_p:
@@ -470,7 +471,14 @@ def conv2d_fprop(x, wpk, cout, kh, kw, stride=1, pad=0, bias=None, residual=None
         nbytes = lib.raw('imx_conv2d_fprop_workspace_bytes')(n, h, w, cin_p, cout, cout_p, kh, kw, stride, pad, flags)
         if nbytes < 0:
             raise _C.ImxError('imx_conv2d_fprop_workspace_bytes: %s' % lib.last_error())
-    if nbytes > 0:
+    if scale is not None:
+        _req_f32c(scale, 'scale')
+        ws = torch.empty((int(nbytes),), dtype=torch.uint8, device=x.device) if nbytes > 0 else None
+        lib.call('imx_conv2d_igemm_fprop_scaled_bf16', _ptr(x), _ptr(wpk), _ptr(scale), _ptr(bias), _ptr(residual), _ptr(out),
+                 _ptr(stats), _ptr(ws), int(nbytes), n, h, w, cin_p, cout, cout_p, kh, kw, stride, pad, flags, _stream())
+        if nbytes > 0:
+            lib.launches += 1
+    elif nbytes > 0:
         ws = torch.empty((int(nbytes),), dtype=torch.uint8, device=x.device)
         lib.call('imx_conv2d_igemm_fprop_splitk_bf16', _ptr(x), _ptr(wpk), _ptr(bias), _ptr(residual), _ptr(out),
                  _ptr(stats), _ptr(ws), int(nbytes), n, h, w, cin_p, cout, cout_p, kh, kw, stride, pad, flags, _stream())

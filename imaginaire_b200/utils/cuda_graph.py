@@ -32,6 +32,7 @@ class GraphedTrainerStep:
         self.key = None
         self.warmup = warmup
         self.launches_per_replay = 0
+        self._params = [p for opt in (trainer.opt_G, trainer.opt_D) for g in opt.param_groups for p in g['params']]
         for opt in (trainer.opt_G, trainer.opt_D):
             if hasattr(opt, 'make_capturable'):
                 opt.make_capturable()
@@ -60,6 +61,11 @@ class GraphedTrainerStep:
                 self._body()              # eager iterations: lazy set-up (kernel attributes, plans, caches) happens here
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
+        # Packed bf16 filters are cached per parameter version.  An entry left by the eager iterations would be a cache
+        # HIT during capture: no pack kernel would be recorded, every replay would read that one tensor, never
+        # refreshed -- and freed for reuse as soon as the cache drops it.  Start the capture with an empty cache.
+        from .. import functional as NF
+        NF._PACK_CACHE.clear()
         lib = _C.lib()
         before = lib.launches
         steps_before = ema._steps if ema is not None else None
@@ -97,6 +103,9 @@ class GraphedTrainerStep:
         for k, v in self.static.items():
             v.copy_(data[k], non_blocking=True)
         self.graph.replay()
+        # the captured optimizer steps rewrite the parameters on the device; tell the host-side caches that key on
+        # Tensor._version (packed bf16 filters, identity-affine checks) that their values moved
+        torch._C._increment_version(self._params)
         t = self.trainer
         if t.cfg.trainer.model_average:
             t.net_G.module.note_graph_replay()

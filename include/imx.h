@@ -337,6 +337,18 @@ IMX_API int imx_conv2d_igemm_fprop_splitk_bf16(const imx_bf16* x, const imx_bf16
                                        int Cout, int Cout_p, int KH, int KW,
                                        int stride, int pad, int flags, imx_stream_t stream);
 
+/* The same convolution with the accumulator multiplied by *scale (ONE fp32 in device memory) before the bias:
+ * y = act(scale * conv(x, wpk) + bias) (+ residual).  For spectrally normalised layers: the bf16 filter is packed
+ * unscaled once per optimizer step and 1 / sigma -- which changes with every application's power iteration -- enters
+ * here.  workspace / workspace_bytes as in imx_conv2d_igemm_fprop_splitk_bf16, or null / 0 for no split-K.
+ * ref: torch.nn.utils.spectral_norm's weight = weight_orig / sigma (imaginaire/layers/weight_norm.py:85) */
+IMX_API int imx_conv2d_igemm_fprop_scaled_bf16(const imx_bf16* x, const imx_bf16* wpk, const float* scale,
+                                               const float* bias, const imx_bf16* residual, void* out, float* stats,
+                                               void* workspace, int64_t workspace_bytes,
+                                               int N, int H, int W, int Cin_p,
+                                               int Cout, int Cout_p, int KH, int KW,
+                                               int stride, int pad, int flags, imx_stream_t stream);
+
 /* SPADE projection conv fused with the modulation (gamma/beta never reach HBM):
  *   gb = conv(hidden; wgb) (+bias), wgb rows interleaved per 64-channel block as
  *   [64 gamma rows | 64 beta rows] (imx_pack_spade_gb_weight_bf16),
