@@ -75,6 +75,7 @@ struct ConvArgs {
     void* out;
     float* stats;
     // SPADE-fused epilogue (mode 1)
+    const float* scale_beta;     // mode 1: `scale` multiplies the gamma accumulators, `scale_beta` the beta ones
     const float* bias_beta;
     const uint16_t* x;
     const float* mean;
@@ -442,6 +443,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                 const size_t xpix = ((size_t)img * Hx + oyx) * Wx + oxx;
                 const float4* cf = reinterpret_cast<const float4*>(s_epi) + as * (BN / 2);
                 const float* cbb = s_epi + 4 * BN + as * (BN / 2);
+                const float sc_g = p.scale ? __ldg(p.scale) : 1.0f, sc_b = p.scale_beta ? __ldg(p.scale_beta) : 1.0f;
                 constexpr int NCH = BN / 64;     // chunks of 32 channels (32 gamma + 32 beta columns)
                 auto chan0 = [&](int cc) { return (n0 / 128 + (cc >> 1)) * 64 + (cc & 1) * 32; };
                 auto load_x = [&](int cc, uint4 (&xr)[4]) {
@@ -484,8 +486,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                             const float xv = e == 0 ? imx::bf16_lo(xr[j >> 1]) : imx::bf16_hi(xr[j >> 1]);
                             const float4 k4 = cf[g * 64 + h * 32 + c];
                             const float xh = fmaf(xv - k4.x, k4.y, k4.z);
-                            const float gam1 = __uint_as_float(vg[c]) + k4.w;
-                            const float bet = __uint_as_float(vb[c]) + cbb[g * 64 + h * 32 + c];
+                            const float gam1 = fmaf(__uint_as_float(vg[c]), sc_g, k4.w);
+                            const float bet = fmaf(__uint_as_float(vb[c]), sc_b, cbb[g * 64 + h * 32 + c]);
                             y2[e] = act_apply(fmaf(xh, gam1, bet), p.act_slope);
                         }
                         o[j >> 1] = imx::pack_bf16(y2[0], y2[1]);
@@ -768,13 +770,13 @@ extern "C" int imx_conv2d_igemm_fprop_splitk_bf16(const imx_bf16* x, const imx_b
                       KH, KW, stride, pad, flags, stream);
 }
 
-extern "C" int imx_spade_gb_conv_modulate_bf16(const imx_bf16* hidden, const imx_bf16* wgb,
-                                               const float* bias_gamma, const float* bias_beta,
-                                               const imx_bf16* x, const float* mean, const float* rstd,
-                                               const float* w, const float* b, imx_bf16* y,
-                                               int N, int H, int W, int Ch_p, int C, int KH, int KW, int pad,
-                                               int stats_per_instance, int act, int up2x,
-                                               imx_stream_t stream) {
+static int spade_gb_impl(const imx_bf16* hidden, const imx_bf16* wgb, const float* scale_gamma, const float* scale_beta,
+                         const float* bias_gamma, const float* bias_beta,
+                         const imx_bf16* x, const float* mean, const float* rstd,
+                         const float* w, const float* b, imx_bf16* y,
+                         int N, int H, int W, int Ch_p, int C, int KH, int KW, int pad,
+                         int stats_per_instance, int act, int up2x,
+                         imx_stream_t stream) {
     IMX_REQUIRE(hidden && wgb && x && mean && rstd && y, "spade_gb_conv_modulate: null pointer");
     IMX_REQUIRE(N >= 0 && H > 0 && W > 0, "spade_gb_conv_modulate: bad size");
     IMX_REQUIRE(Ch_p > 0 && Ch_p % 8 == 0, "spade_gb_conv_modulate: Ch_p must be a positive multiple of 8");
@@ -793,9 +795,36 @@ extern "C" int imx_spade_gb_conv_modulate_bf16(const imx_bf16* hidden, const imx
     int rc = setup(a, ta, tb, hidden, wgb, N, H, W, Ch_p, rows_b, KH, KW, 1, pad, BN);
     if (rc) return rc;
     a.out = y; a.bias = bias_gamma; a.bias_beta = bias_beta;
+    a.scale = scale_gamma; a.scale_beta = scale_beta;
     a.x = x; a.mean = mean; a.rstd = rstd; a.nw = w; a.nb = b;
     a.C = C; a.per_instance = stats_per_instance; a.up2x = up2x;
     a.act_slope = act == 1 ? 0.2f : (act == 2 ? 0.0f : 1.0f);
     cudaStream_t s = (cudaStream_t)stream;
     return BN == 256 ? launch<256, 1>(ta, tb, a, s) : launch<128, 1>(ta, tb, a, s);
+}
+
+extern "C" int imx_spade_gb_conv_modulate_bf16(const imx_bf16* hidden, const imx_bf16* wgb,
+                                               const float* bias_gamma, const float* bias_beta,
+                                               const imx_bf16* x, const float* mean, const float* rstd,
+                                               const float* w, const float* b, imx_bf16* y,
+                                               int N, int H, int W, int Ch_p, int C, int KH, int KW, int pad,
+                                               int stats_per_instance, int act, int up2x,
+                                               imx_stream_t stream) {
+    return spade_gb_impl(hidden, wgb, nullptr, nullptr, bias_gamma, bias_beta, x, mean, rstd, w, b, y, N, H, W, Ch_p, C, KH,
+                         KW, pad, stats_per_instance, act, up2x, stream);
+}
+
+// The same with the gamma accumulators multiplied by *scale_gamma and the beta accumulators by *scale_beta (one fp32
+// each in device memory, either may be null) before their biases: 1 / sigma of the two spectrally normalised
+// projections when the interleaved filter is packed unscaled, once per optimizer step.
+extern "C" int imx_spade_gb_conv_modulate_scaled_bf16(const imx_bf16* hidden, const imx_bf16* wgb,
+                                                      const float* scale_gamma, const float* scale_beta,
+                                                      const float* bias_gamma, const float* bias_beta,
+                                                      const imx_bf16* x, const float* mean, const float* rstd,
+                                                      const float* w, const float* b, imx_bf16* y,
+                                                      int N, int H, int W, int Ch_p, int C, int KH, int KW, int pad,
+                                                      int stats_per_instance, int act, int up2x,
+                                                      imx_stream_t stream) {
+    return spade_gb_impl(hidden, wgb, scale_gamma, scale_beta, bias_gamma, bias_beta, x, mean, rstd, w, b, y, N, H, W, Ch_p, C,
+                         KH, KW, pad, stats_per_instance, act, up2x, stream);
 }

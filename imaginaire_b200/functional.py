@@ -470,13 +470,28 @@ def spade_gb_fused(hidden, w_gamma, w_beta, b_gamma, b_beta, x, ns, act, pad, in
     epilogue, so gamma and beta never reach HBM."""
     mean, rstd, _ = compute_norm_stats(x, ns)
     c, ch, kh, kw = w_gamma.shape
-    wgb = ops.pack_spade_gb_weight(w_gamma, w_beta, inv_sigma_gamma, inv_sigma_beta, ch_p=hidden.shape[1])
+    sg = sb = None
+    if isinstance(w_gamma, torch.nn.Parameter) and isinstance(w_beta, torch.nn.Parameter) and \
+            (inv_sigma_gamma is not None or inv_sigma_beta is not None):
+        # spectrally normalised projections: the interleaved bf16 filter is packed unscaled once per optimizer step
+        # (cached on the two parameters' versions); the two 1 / sigma multiply the accumulators in the epilogue
+        key = (id(w_gamma), id(w_beta), hidden.shape[1], 'gb')
+        hit = _PACK_CACHE.get(key)
+        stamp = (w_gamma._version, w_beta._version, w_gamma.data_ptr(), w_beta.data_ptr())
+        if hit is None or hit[0] != stamp:
+            hit = (stamp, None, ops.pack_spade_gb_weight(w_gamma, w_beta, None, None, ch_p=hidden.shape[1]))
+            _PACK_CACHE[key] = hit
+        wgb = hit[2]
+        sg = None if inv_sigma_gamma is None else inv_sigma_gamma.detach().float().reshape(1)
+        sb = None if inv_sigma_beta is None else inv_sigma_beta.detach().float().reshape(1)
+    else:
+        wgb = ops.pack_spade_gb_weight(w_gamma, w_beta, inv_sigma_gamma, inv_sigma_beta, ch_p=hidden.shape[1])
     w = ns.weight.float() if ns.weight is not None else None
     b = ns.bias.float() if ns.bias is not None else None
     if w is None and b is not None:
         w = torch.ones_like(b)
     return ops.spade_gb_conv_modulate(hidden, wgb, b_gamma, b_beta, x, mean, rstd, w, b, c, kh, kw, pad,
-                                      ns.per_instance, act)
+                                      ns.per_instance, act, scale_gamma=sg, scale_beta=sb)
 
 
 def _require_cuda(name, *ts):

@@ -489,10 +489,17 @@ def conv2d_fprop(x, wpk, cout, kh, kw, stride=1, pad=0, bias=None, residual=None
 
 
 def spade_gb_conv_modulate(hidden, wgb, bias_gamma, bias_beta, x, mean, rstd, w, b, c, kh, kw, pad,
-                           per_instance, act, up2x=False):
+                           per_instance, act, up2x=False, scale_gamma=None, scale_beta=None):
+    """scale_gamma / scale_beta: optional 1-element fp32 device tensors multiplying the gamma / beta accumulators
+    (1 / sigma with an unscaled packed filter)."""
     _req_cuda(hidden, wgb, x); _req_nhwc(hidden, 'hidden'); _req_nhwc(x, 'x')
     n, ch_p, h, wd = hidden.shape
     y = empty_nhwc(n, c, h, wd, x.device)
+    if scale_gamma is not None or scale_beta is not None:
+        _C.lib().call('imx_spade_gb_conv_modulate_scaled_bf16', _ptr(hidden), _ptr(wgb), _ptr(scale_gamma), _ptr(scale_beta),
+                      _ptr(bias_gamma), _ptr(bias_beta), _ptr(x), _ptr(mean), _ptr(rstd), _ptr(w), _ptr(b), _ptr(y), n, h, wd,
+                      ch_p, c, kh, kw, pad, int(per_instance), int(act), int(up2x), _stream())
+        return y
     _C.lib().call('imx_spade_gb_conv_modulate_bf16', _ptr(hidden), _ptr(wgb), _ptr(bias_gamma), _ptr(bias_beta),
                   _ptr(x), _ptr(mean), _ptr(rstd), _ptr(w), _ptr(b), _ptr(y), n, h, wd, ch_p, c, kh, kw, pad,
                   int(per_instance), int(act), int(up2x), _stream())

@@ -364,6 +364,19 @@ IMX_API int imx_spade_gb_conv_modulate_bf16(const imx_bf16* hidden, const imx_bf
                                     int stats_per_instance, int act, int up2x,
                                     imx_stream_t stream);
 
+/* imx_spade_gb_conv_modulate_bf16 with the gamma accumulators multiplied by *scale_gamma and the beta accumulators
+ * by *scale_beta (one fp32 each in device memory; null = 1) before their biases.  With spectrally normalised
+ * projections the interleaved filter is packed unscaled once per optimizer step and the two 1 / sigma enter here.
+ * ref: as imx_spade_gb_conv_modulate_bf16 + imaginaire/layers/weight_norm.py:85 */
+IMX_API int imx_spade_gb_conv_modulate_scaled_bf16(const imx_bf16* hidden, const imx_bf16* wgb,
+                                                   const float* scale_gamma, const float* scale_beta,
+                                                   const float* bias_gamma, const float* bias_beta,
+                                                   const imx_bf16* x, const float* mean, const float* rstd,
+                                                   const float* w, const float* b, imx_bf16* y,
+                                                   int N, int H, int W, int Ch_p, int C, int KH, int KW, int pad,
+                                                   int stats_per_instance, int act, int up2x,
+                                                   imx_stream_t stream);
+
 IMX_API int imx_pack_spade_gb_weight_bf16(const float* w_gamma, const float* w_beta,
                                   const float* inv_sigma_gamma, const float* inv_sigma_beta,
                                   imx_bf16* packed, int C, int Ch, int KH, int KW, int Ch_p,
