@@ -204,20 +204,31 @@ def conv_traffic_from_profile():
 
 def hbm_rooflines(dev, hbm_peak_gbs):
     """Second half of BASELINE.json's metric: achieved HBM GB/s of the norm / modulation / warp kernels, each timed
-    alone with CUDA events (5 calls after 2 warm-ups) on tensors far larger than L2: the C3 layer 8 x 512 x 128 x 256
+    alone with CUDA events (5 calls replayed as a CUDA graph after 2 warm-ups) on tensors far larger than L2: the C3 layer 8 x 512 x 128 x 256
     (bf16 NHWC) for the norm kernels, 8 x 64 x 512 x 1024 fp32 on the SURVEY 8(d) flow for the warps.  Bytes are the
     algorithmic ones of DESIGN.md section 3."""
     import torch
     from imaginaire_b200 import ops
 
     def timed(fn):
-        for _ in range(2):
-            fn()
+        # five calls recorded in a CUDA graph and replayed: the kernels run back to back, so a 50 us kernel is not
+        # timed together with the host's launch gaps
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                fn()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            for _ in range(5):
+                fn()
+        graph.replay()
         torch.cuda.synchronize()
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         s.record()
-        for _ in range(5):
-            fn()
+        graph.replay()
         e.record()
         torch.cuda.synchronize()
         return s.elapsed_time(e) / 5 * 1e-3

@@ -7,7 +7,7 @@ gamma/beta path) and forward+backward; beside it the same block written with pla
 ops (cuDNN bf16 channels_last convs + ATen batch norm / elementwise) as the on-GPU reference.
 Prints one JSON line per case and a final summary line; CUDA-event timing, 3 warm-ups.
 
-    python tools/resblk_sweep.py [--quick]
+    python tools/resblk_sweep.py [--quick | --full]      (--full: SURVEY 8(d)'s grid C in 64..1024 x 16x32..256x512)
 """
 import json
 import os
@@ -102,9 +102,11 @@ def main():
              (64, 256, 512)]
     if quick:
         cases = cases[1:4]
+    if '--full' in sys.argv:
+        cases = [(c, h, w) for c in (64, 128, 256, 512, 1024) for h, w in ((16, 32), (32, 64), (64, 128), (128, 256), (256, 512))]
     results = []
     for c, h, w in cases:
-        for cout in (c, c // 2):
+        for cout in ((c, c // 2) if '--full' not in sys.argv else (c,)):
             blk = make_block(c, cout)
             x = nhwc((torch.randn(n, c, h, w, device='cuda') * 1.5 + 0.3))
             fl = block_flops(c, cout, n, h, w)
