@@ -480,7 +480,7 @@ def run_ours(args):
     probe.remove()
     by, conv_flops, conv_ms = probe.summary()
     if os.environ.get('IMX_BENCH_VERBOSE') and rank == 0:
-        print(probe.table(), file=sys.stderr, flush=True)
+        print(probe.table(int(os.environ.get("IMX_BENCH_TABLE_TOP", "40"))), file=sys.stderr, flush=True)
     peaks = load_peaks()
     achieved = conv_flops / (conv_ms * 1e-3) / 1e12 if conv_ms > 0 else 0.0
     ms_per_step = ms / args.steps

@@ -126,42 +126,271 @@ __global__ void nhwc_to_nchw_kernel(const __nv_bfloat16* __restrict__ src, float
     }
 }
 
-// packed[co][tap][ci_p] = w[co][ci][tap] * inv_sigma                       (kFlip == false)
-// packed[ci][T-1-tap][co_p] = w[co][ci][tap] * inv_sigma                   (kFlip == true)
-// A [inner x taps] -> [taps x inner] transpose per row of the packed matrix, staged through
-// shared memory so that the fp32 filter is read in contiguous runs and the bf16 rows are
-// written as contiguous 256-byte segments.  grid = (ceil(Cp / kPackTile), rows).
+// packed[co][tap][ci_p] = w[co][ci][tap] * inv_sigma                       (kMode == kPackPlain)
+// packed[ci][T-1-tap][co_p] = w[co][ci][tap] * inv_sigma                   (kMode == kPackFlip)
+// kMode == kPackGB: the plain pack of the interleaved gamma/beta filter of pack_gb_weight_kernel (packed row
+// R -> channel (R / 128) * 64 + R % 64 of gamma (R % 128 < 64) or beta), each with its own scale.
+//
+// A [inner x taps] -> [taps x inner] transpose per row of the packed matrix through shared memory.  A CTA owns
+// 128 inner indices of `rpb` consecutive packed rows (8 for 3x3: 36 KB of fp32 in flight per CTA, ~6 CTAs per SM):
+// the training step packs ~0.9 G filter elements per iteration and the first version (one row, 4.6 KB per CTA,
+// 4 loads per thread, a division per element) ran at a quarter of the HBM peak.  Plain: every row is one contiguous
+// run of 128 * taps floats, copied by the warps of that row, kPackBatch loads in flight per thread.  Flip: the rows are
+// consecutive input channels, so for every output channel the CTA reads ONE run of rpb * taps floats
+// (w[co][r0 .. r0 + rpb)[:]) instead of rpb runs of `taps` floats.  Index arithmetic by multiplication
+// (__umulhi with 2^32 / d, exact for the index range here).  The bf16 rows leave as 4-byte pairs, 256 B per row.
 constexpr int kPackTile = 128;
 constexpr int kPackMaxTaps = 49;   // up to 7x7; larger kernels take the scalar path
+constexpr int kPackPlain = 0, kPackFlip = 1, kPackGB = 2;
+constexpr int kPackBatch = 18;     // loads in flight per thread: 8 left the kernel at half of the HBM peak (~50 KB per SM)
 
-template <bool kFlip>
-__global__ void __launch_bounds__(256)
-pack_weight_tiled_kernel(const float* __restrict__ w, const float* __restrict__ inv_sigma,
-                         __nv_bfloat16* __restrict__ packed, int Cout, int Cin, int taps, int Cp) {
-    extern __shared__ float tile[];   // [kPackTile][taps + 1]
-    const float s = inv_sigma ? __ldg(inv_sigma) : 1.0f;
-    const int r = blockIdx.y;                       // co (plain) or ci (flip)
-    const int i0 = blockIdx.x * kPackTile;          // first inner index of the tile: ci (plain) or co (flip)
+__device__ __forceinline__ unsigned magic_of(int d) { return d > 1 ? 0xFFFFFFFFu / (unsigned)d + 1u : 0u; }
+__device__ __forceinline__ int div_magic(int e, int d, unsigned m) { return d > 1 ? (int)__umulhi((unsigned)e, m) : e; }
+
+// rows per CTA: the largest of 8 / 4 / 2 / 1 whose staging tile fits 48 KB
+__host__ __device__ constexpr int pack_rows_per_cta(int taps) {
+    return 8 * (kPackTile * (taps | 1) + taps) * 4 <= 48 * 1024 ? 8
+         : 4 * (kPackTile * (taps | 1) + taps) * 4 <= 48 * 1024 ? 4
+         : 2 * (kPackTile * (taps | 1) + taps) * 4 <= 48 * 1024 ? 2 : 1;
+}
+
+// One tile with run-time tap count and ragged edges (any tile of a filter with an unusual tap count; the edge tiles of
+// the others).
+template <int kMode, int rpb>
+__device__ __forceinline__ void pack_tile_generic(const float* __restrict__ w, const float* __restrict__ w2,
+                                                  const float* __restrict__ inv_sigma, const float* __restrict__ inv_sigma2,
+                                                  __nv_bfloat16* __restrict__ packed, int Cout, int Cin, int taps, int Cp,
+                                                  int r0, int i0, float* tile) {
+    constexpr bool kFlip = kMode == kPackFlip;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rows_total = kMode == kPackGB ? 2 * ((Cout + 63) / 64 * 64) : (kFlip ? Cin : Cout);
     const int inner = kFlip ? Cout : Cin;
-    const int n_in = min(kPackTile, inner - i0);    // valid inner entries (may be <= 0 for pure padding tiles)
-    const int pitch = taps + 1;
+    const int nrows = min(rpb, rows_total - r0);
+    const int n_in = max(0, min(kPackTile, inner - i0));   // valid inner entries (0 for a pure padding tile)
+    const int pitch = taps | 1;                            // odd: consecutive j fall into different banks
+    const int rowstride = kPackTile * pitch + taps;        // = taps (mod 32): a flip run (rr, t) walks the banks
+    const unsigned m_taps = magic_of(taps);
     if (!kFlip) {
-        // contiguous run w[r][i0 .. i0+n_in)[0..taps)
-        const float* src = w + ((size_t)r * Cin + i0) * taps;
-        for (int e = threadIdx.x; e < n_in * taps; e += 256) tile[(e / taps) * pitch + e % taps] = __ldg(src + e) * s;
+        constexpr int nsub = 8 / rpb;                      // warps per row
+        const int row = warp % rpb, sub = warp / rpb;
+        int c = r0 + row;                                  // source output channel
+        const float* src_base = w;
+        float s = 1.0f;
+        bool valid = row < nrows;
+        if (kMode == kPackGB) {
+            const int within = c & 127;
+            const bool is_beta = within >= 64;
+            c = (c >> 7) * 64 + (within & 63);
+            valid = valid && c < Cout;
+            src_base = is_beta ? w2 : w;
+            const float* sc = is_beta ? inv_sigma2 : inv_sigma;
+            s = sc ? __ldg(sc) : 1.0f;
+        } else {
+            s = inv_sigma ? __ldg(inv_sigma) : 1.0f;
+        }
+        const int n = valid ? n_in * taps : 0;
+        const float* src = src_base + ((size_t)c * Cin + i0) * taps;
+        float* dst = tile + row * rowstride;
+        constexpr int step = 32 * nsub;
+        for (int e0 = sub * 32 + lane; e0 < n; e0 += kPackBatch * step) {
+            float v[kPackBatch];
+#pragma unroll
+            for (int u = 0; u < kPackBatch; ++u) {
+                const int e = e0 + u * step;
+                v[u] = e < n ? __ldg(src + e) : 0.0f;
+            }
+#pragma unroll
+            for (int u = 0; u < kPackBatch; ++u) {
+                const int e = e0 + u * step;
+                if (e < n) dst[pitch == taps ? e : e + div_magic(e, taps, m_taps)] = v[u] * s;
+            }
+        }
+        if (kMode == kPackGB && row < nrows && !valid) {   // rows past C of the last 64-channel block: zeros
+            for (int e = sub * 32 + lane; e < n_in * pitch; e += step) dst[e] = 0.0f;
+        }
     } else {
-        // for each co in the tile a run of `taps` floats at w[co][r][:]
-        for (int e = threadIdx.x; e < n_in * taps; e += 256) {
-            const int j = e / taps, t = e - j * taps;
-            tile[j * pitch + t] = __ldg(w + ((size_t)(i0 + j) * Cin + r) * taps + t) * s;
+        const float s = inv_sigma ? __ldg(inv_sigma) : 1.0f;
+        // One run per output channel j: w[i0 + j][r0 .. r0 + nrows)[:], L = nrows * taps <= 96 floats (the 48 KB
+        // staging limit), read by ONE warp with lane-fixed positions lane, lane + 32, lane + 64 -- their (row, tap)
+        // and shared-memory offsets are the same for every run, so the loop body is loads and stores only
+        // (flat indexing cost ~20 instructions per element and left the kernel issue-bound at 0.40 of the HBM peak).
+        const int L = nrows * taps;
+        int sidx[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const int rem = lane + 32 * k;
+            const int rr = div_magic(rem, taps, m_taps);
+            sidx[k] = rem < L ? rr * rowstride + (rem - rr * taps) : -1;
+        }
+        const size_t CT = (size_t)Cin * taps;
+        const float* run0 = w + ((size_t)i0 * Cin + r0) * taps + lane;
+        constexpr int kRuns = kPackBatch / 3;              // runs in flight per warp
+        for (int j0 = warp; j0 < n_in; j0 += 8 * kRuns) {
+            float v[kRuns][3];
+#pragma unroll
+            for (int q = 0; q < kRuns; ++q) {
+                const int j = j0 + 8 * q;
+#pragma unroll
+                for (int k = 0; k < 3; ++k)
+                    v[q][k] = (j < n_in && sidx[k] >= 0) ? __ldg(run0 + (size_t)j * CT + 32 * k) : 0.0f;
+            }
+#pragma unroll
+            for (int q = 0; q < kRuns; ++q) {
+                const int j = j0 + 8 * q;
+#pragma unroll
+                for (int k = 0; k < 3; ++k)
+                    if (j < n_in && sidx[k] >= 0) tile[sidx[k] + j * pitch] = v[q][k] * s;
+            }
         }
     }
     __syncthreads();
-    const int n_out = min(kPackTile, Cp - i0);
-    for (int e = threadIdx.x; e < taps * n_out; e += 256) {
-        const int t = e / n_out, j = e - t * n_out;
-        const float v = j < n_in ? tile[j * pitch + (kFlip ? taps - 1 - t : t)] : 0.0f;
-        packed[((size_t)r * taps + t) * Cp + i0 + j] = __float2bfloat16_rn(v);
+    const int npair = min(kPackTile, Cp - i0) >> 1;        // Cp is a multiple of 8
+    const int nrt = nrows * taps;
+    for (int rt = warp; rt < nrt; rt += 8) {
+        const int row = div_magic(rt, taps, m_taps), t = rt - row * taps;
+        const float* srow = tile + row * rowstride + t;
+        __nv_bfloat162* dst = reinterpret_cast<__nv_bfloat162*>(
+            packed + ((size_t)(r0 + row) * taps + (kFlip ? taps - 1 - t : t)) * Cp + i0);
+        for (int jp = lane; jp < npair; jp += 32) {
+            const int j = 2 * jp;
+            const float a = j < n_in ? srow[j * pitch] : 0.0f;
+            const float b = j + 1 < n_in ? srow[(j + 1) * pitch] : 0.0f;
+            dst[jp] = __floats2bfloat162_rn(a, b);
+        }
+    }
+}
+
+// grid: plain / gamma-beta (inner tiles, row groups); flip (row groups, inner tiles) -- consecutive CTAs of a flip pack
+// take consecutive row groups of the same 128 output channels, i.e. adjacent runs of the same filter rows.
+template <int kMode, int rpb>
+__global__ void __launch_bounds__(256, 5)
+pack_weight_rows_kernel(const float* __restrict__ w, const float* __restrict__ w2, const float* __restrict__ inv_sigma,
+                        const float* __restrict__ inv_sigma2, __nv_bfloat16* __restrict__ packed, int Cout, int Cin,
+                        int taps, int Cp) {
+    extern __shared__ float tile[];   // [rpb] x (128 * pitch + taps): element (row, j, t) at row * rowstride + j * pitch + t
+    constexpr bool kFlip = kMode == kPackFlip;
+    pack_tile_generic<kMode, rpb>(w, w2, inv_sigma, inv_sigma2, packed, Cout, Cin, taps, Cp,
+                                  (kFlip ? blockIdx.x : blockIdx.y) * rpb, (kFlip ? blockIdx.y : blockIdx.x) * kPackTile, tile);
+}
+
+// The same for the tap counts the networks use (3x3, 4x4, 5x5), everything but the pointers a compile-time constant:
+// a full tile costs ~5 instructions per element (load, scale, shared store; two shared loads, convert, store per
+// pair) where the run-time-indexed loops above issue ~40 and are bound by instruction issue, not by memory
+// (profiles/r02_pack_kernel.md).  Ragged tiles fall through to pack_tile_generic.
+template <int kMode, int kTaps>
+__global__ void __launch_bounds__(256, 5)
+pack_weight_taps_kernel(const float* __restrict__ w, const float* __restrict__ w2, const float* __restrict__ inv_sigma,
+                        const float* __restrict__ inv_sigma2, __nv_bfloat16* __restrict__ packed, int Cout, int Cin, int Cp) {
+    extern __shared__ float tile[];
+    constexpr bool kFlip = kMode == kPackFlip;
+    constexpr int rpb = pack_rows_per_cta(kTaps);
+    constexpr int pitch = kTaps | 1, rowstride = kPackTile * pitch + kTaps;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rows_total = kMode == kPackGB ? 2 * ((Cout + 63) / 64 * 64) : (kFlip ? Cin : Cout);
+    const int inner = kFlip ? Cout : Cin;
+    const int r0 = (kFlip ? blockIdx.x : blockIdx.y) * rpb;
+    const int i0 = (kFlip ? blockIdx.y : blockIdx.x) * kPackTile;
+    bool full = rows_total - r0 >= rpb && inner - i0 >= kPackTile && Cp - i0 >= kPackTile;
+    if (kMode == kPackGB) {            // the rows of a group lie in one 64-channel block: the last one decides
+        const int rl = r0 + rpb - 1;
+        full = full && ((rl >> 7) * 64 + (rl & 63)) < Cout;
+    }
+    if (!full) {
+        pack_tile_generic<kMode, rpb>(w, w2, inv_sigma, inv_sigma2, packed, Cout, Cin, kTaps, Cp, r0, i0, tile);
+        return;
+    }
+    if (!kFlip) {
+        constexpr int nsub = 8 / rpb, step = 32 * nsub, T = 4 * kTaps / nsub;   // T loads per thread
+        static_assert((4 * kTaps) % nsub == 0, "a row must divide evenly over its warps");
+        const int row = warp % rpb, sub = warp / rpb;
+        int c = r0 + row;
+        const float* base = w;
+        const float* sc = inv_sigma;
+        if (kMode == kPackGB) {
+            const bool is_beta = (c & 127) >= 64;
+            c = (c >> 7) * 64 + (c & 63);
+            base = is_beta ? w2 : w;
+            sc = is_beta ? inv_sigma2 : inv_sigma;
+        }
+        const float s = sc ? __ldg(sc) : 1.0f;
+        const int e_first = sub * 32 + lane;
+        const float* src = base + ((size_t)c * Cin + i0) * kTaps + e_first;
+        float* dst = tile + row * rowstride;
+#pragma unroll
+        for (int b = 0; b < T; b += kPackBatch) {
+            float v[kPackBatch];
+#pragma unroll
+            for (int u = 0; u < kPackBatch; ++u)
+                if (b + u < T) v[u] = __ldg(src + (b + u) * step);
+#pragma unroll
+            for (int u = 0; u < kPackBatch; ++u)
+                if (b + u < T) {
+                    const int e = e_first + (b + u) * step;
+                    dst[pitch == kTaps ? e : e + e / kTaps] = v[u] * s;
+                }
+        }
+    } else {
+        constexpr int L = rpb * kTaps, K = (L + 31) / 32, kRuns = kPackBatch / K, kRunsPerWarp = kPackTile / 8;
+        static_assert(L <= 96, "a run is read by one warp in at most three loads");
+        const float s = inv_sigma ? __ldg(inv_sigma) : 1.0f;
+        const bool last_ok = lane + 32 * (K - 1) < L;
+        int sidx[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            const int rem = lane + 32 * k, rr = rem / kTaps;
+            sidx[k] = rr * rowstride + (rem - rr * kTaps);
+        }
+        const size_t CT = (size_t)Cin * kTaps;
+        const float* run0 = w + ((size_t)i0 * Cin + r0) * kTaps + lane;
+#pragma unroll
+        for (int q0 = 0; q0 < kRunsPerWarp; q0 += kRuns) {
+            float v[kRuns][K];
+#pragma unroll
+            for (int q = 0; q < kRuns; ++q)
+                if (q0 + q < kRunsPerWarp) {
+                    const float* pr = run0 + (size_t)(warp + 8 * (q0 + q)) * CT;
+#pragma unroll
+                    for (int k = 0; k < K; ++k)
+                        if (k < K - 1 || last_ok) v[q][k] = __ldg(pr + 32 * k);
+                }
+#pragma unroll
+            for (int q = 0; q < kRuns; ++q)
+                if (q0 + q < kRunsPerWarp) {
+                    float* tj = tile + (warp + 8 * (q0 + q)) * pitch;
+#pragma unroll
+                    for (int k = 0; k < K; ++k)
+                        if (k < K - 1 || last_ok) tj[sidx[k]] = v[q][k] * s;
+                }
+        }
+    }
+    __syncthreads();
+    constexpr int nrt = rpb * kTaps;
+    const float* sl = tile + 2 * lane * pitch;
+#pragma unroll 3
+    for (int rt = warp; rt < nrt; rt += 8) {
+        const int row = rt / kTaps, t = rt - row * kTaps;
+        const float* sr = sl + row * rowstride + t;
+        __nv_bfloat162* dst = reinterpret_cast<__nv_bfloat162*>(
+            packed + ((size_t)(r0 + row) * kTaps + (kFlip ? kTaps - 1 - t : t)) * Cp + i0) + lane;
+        const float a0 = sr[0], b0 = sr[pitch], a1 = sr[64 * pitch], b1 = sr[65 * pitch];
+        dst[0] = __floats2bfloat162_rn(a0, b0);
+        dst[32] = __floats2bfloat162_rn(a1, b1);
+    }
+}
+
+template <int kMode>
+void launch_pack_rows(dim3 grid, cudaStream_t st, const float* w, const float* w2, const float* s1, const float* s2,
+                      __nv_bfloat16* packed, int Cout, int Cin, int taps, int Cp) {
+    const int rpb = pack_rows_per_cta(taps);
+    const size_t smem = (size_t)rpb * (kPackTile * (taps | 1) + taps) * sizeof(float);
+    if (taps == 9) { pack_weight_taps_kernel<kMode, 9><<<grid, 256, smem, st>>>(w, w2, s1, s2, packed, Cout, Cin, Cp); return; }
+    if (taps == 16) { pack_weight_taps_kernel<kMode, 16><<<grid, 256, smem, st>>>(w, w2, s1, s2, packed, Cout, Cin, Cp); return; }
+    if (taps == 25) { pack_weight_taps_kernel<kMode, 25><<<grid, 256, smem, st>>>(w, w2, s1, s2, packed, Cout, Cin, Cp); return; }
+    switch (rpb) {
+        case 8: pack_weight_rows_kernel<kMode, 8><<<grid, 256, smem, st>>>(w, w2, s1, s2, packed, Cout, Cin, taps, Cp); break;
+        case 4: pack_weight_rows_kernel<kMode, 4><<<grid, 256, smem, st>>>(w, w2, s1, s2, packed, Cout, Cin, taps, Cp); break;
+        case 2: pack_weight_rows_kernel<kMode, 2><<<grid, 256, smem, st>>>(w, w2, s1, s2, packed, Cout, Cin, taps, Cp); break;
+        default: pack_weight_rows_kernel<kMode, 1><<<grid, 256, smem, st>>>(w, w2, s1, s2, packed, Cout, Cin, taps, Cp); break;
     }
 }
 
@@ -559,14 +788,15 @@ extern "C" int imx_pack_conv_weight_bf16(const float* w, const float* inv_sigma,
     const int taps = KH * KW;
     const int rows = transpose_flip ? Cin : Cout;
     if (taps <= kPackMaxTaps && rows <= 65535) {
-        dim3 grid((Cin_p + kPackTile - 1) / kPackTile, rows);
-        const size_t smem = (size_t)kPackTile * (taps + 1) * sizeof(float);
+        const int rpb = pack_rows_per_cta(taps);
+        dim3 grid((Cin_p + kPackTile - 1) / kPackTile, (rows + rpb - 1) / rpb);
+        if (transpose_flip) grid = dim3(grid.y, grid.x);
         if (transpose_flip)
-            pack_weight_tiled_kernel<true><<<grid, 256, smem, (cudaStream_t)stream>>>(
-                w, inv_sigma, reinterpret_cast<__nv_bfloat16*>(packed), Cout, Cin, taps, Cin_p);
+            launch_pack_rows<kPackFlip>(grid, (cudaStream_t)stream, w, nullptr, inv_sigma, nullptr,
+                                        reinterpret_cast<__nv_bfloat16*>(packed), Cout, Cin, taps, Cin_p);
         else
-            pack_weight_tiled_kernel<false><<<grid, 256, smem, (cudaStream_t)stream>>>(
-                w, inv_sigma, reinterpret_cast<__nv_bfloat16*>(packed), Cout, Cin, taps, Cin_p);
+            launch_pack_rows<kPackPlain>(grid, (cudaStream_t)stream, w, nullptr, inv_sigma, nullptr,
+                                         reinterpret_cast<__nv_bfloat16*>(packed), Cout, Cin, taps, Cin_p);
         return imx::check_launch("pack_conv_weight");
     }
     const long total = (long)rows * taps * Cin_p;
@@ -582,6 +812,16 @@ extern "C" int imx_pack_spade_gb_weight_bf16(const float* w_gamma, const float* 
     IMX_REQUIRE(w_gamma && w_beta && packed, "pack_spade_gb_weight: null pointer");
     IMX_REQUIRE(C > 0 && Ch > 0 && KH > 0 && KW > 0, "pack_spade_gb_weight: bad size");
     IMX_REQUIRE(Ch_p % 8 == 0 && Ch_p >= Ch, "pack_spade_gb_weight: bad Ch_p");
+    const int taps_gb = KH * KW, rows_gb = 2 * ((C + 63) / 64 * 64);
+    if (taps_gb <= kPackMaxTaps && rows_gb <= 65535 * 8) {
+        const int rpb = pack_rows_per_cta(taps_gb);
+        dim3 grid((Ch_p + kPackTile - 1) / kPackTile, (rows_gb + rpb - 1) / rpb);
+        if (grid.y <= 65535) {
+            launch_pack_rows<kPackGB>(grid, (cudaStream_t)stream, w_gamma, w_beta, inv_sigma_gamma, inv_sigma_beta,
+                                      reinterpret_cast<__nv_bfloat16*>(packed), C, Ch, taps_gb, Ch_p);
+            return imx::check_launch("pack_spade_gb_weight");
+        }
+    }
     const long total = (long)2 * ((C + 63) / 64 * 64) * KH * KW * Ch_p;
     pack_gb_weight_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(
         w_gamma, w_beta, inv_sigma_gamma, inv_sigma_beta, reinterpret_cast<__nv_bfloat16*>(packed),

@@ -907,3 +907,48 @@ def test_channel_dot_vs_torch(shape):
     ref.backward(g.float())
     assert H.rel_err(a1.grad.float(), a2.grad) < 1e-2 and H.rel_err(b1.grad.float(), b2.grad) < 1e-2
 
+
+
+# ---------------------------------------------------------------- filter packs (layout.cu: pack_weight_rows_kernel)
+PACK_CASES = [  # cout, cin, k, padded inner (None: next multiple of 8)
+    (64, 3, 3, None), (40, 35, 4, 40), (128, 38, 4, None), (3, 256, 5, None), (130, 72, 1, None), (257, 129, 3, 136),
+    (96, 64, 7, None), (512, 128, 5, None), (1, 1, 3, None), (300, 520, 3, None), (33, 17, 2, 24), (256, 384, 3, None),
+    (128, 256, 4, None), (264, 136, 4, None), (130, 256, 5, 256),
+]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('cout,cin,k,inner_p', PACK_CASES)
+def test_filter_packs_are_bit_exact(cout, cin, k, inner_p):
+    """packed[co][tap][ci_p] = bf16(w * s) and the flipped / transposed dgrad filter, against torch indexing:
+    ragged tiles (inner % 128 != 0), fewer rows than a CTA's row group, even and odd tap counts, padding columns."""
+    from imaginaire_b200 import ops
+    g = torch.Generator().manual_seed(cout * 1000 + cin * 10 + k)
+    w = torch.randn(cout, cin, k, k, generator=g).to(DEV)
+    s = torch.tensor([0.731], device=DEV)
+    for flip in (False, True):
+        inner = cout if flip else cin
+        ip = inner_p if (inner_p is not None and inner_p >= inner) else (inner + 7) // 8 * 8
+        got = ops.pack_conv_weight(w, inv_sigma=s, cin_p=ip, transpose_flip=flip)
+        ws = (w * s).bfloat16()
+        ref = ws.flip(2, 3).permute(1, 2, 3, 0) if flip else ws.permute(0, 2, 3, 1)
+        want = torch.zeros(got.shape, dtype=torch.bfloat16, device=DEV)
+        want[..., :inner] = ref
+        assert torch.equal(got.view(torch.int16), want.view(torch.int16)), 'flip=%s' % flip
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('c,ch,k', [(64, 128, 5), (96, 128, 3), (200, 40, 5), (32, 16, 1), (512, 128, 5)])
+def test_interleaved_gamma_beta_pack_is_bit_exact(c, ch, k):
+    from imaginaire_b200 import ops
+    g = torch.Generator().manual_seed(c + ch + k)
+    wg, wb = torch.randn(c, ch, k, k, generator=g).to(DEV), torch.randn(c, ch, k, k, generator=g).to(DEV)
+    sg, sb = torch.tensor([1.3], device=DEV), torch.tensor([0.4], device=DEV)
+    got = ops.pack_spade_gb_weight(wg, wb, sg, sb)
+    cr = (c + 63) // 64 * 64
+    want = torch.zeros(2 * cr, k, k, (ch + 7) // 8 * 8, dtype=torch.bfloat16, device=DEV)
+    cs = torch.arange(c, device=DEV)
+    rows = (cs // 64) * 128 + cs % 64
+    want[rows, :, :, :ch] = (wg * sg).bfloat16().permute(0, 2, 3, 1)
+    want[rows + 64, :, :, :ch] = (wb * sb).bfloat16().permute(0, 2, 3, 1)
+    assert torch.equal(got.view(torch.int16), want.view(torch.int16))
