@@ -168,6 +168,63 @@ sn_grad_kernel(float* __restrict__ G, const float* __restrict__ u, const float* 
     }
 }
 
+// The same for C % 4 == 0 (every filter but the few with 3 input channels): a thread keeps its four columns of v and
+// walks down the rows, four 16-byte loads of G in flight.  sn_grad_kernel spends a 64-bit division per element and
+// moves 4 bytes per instruction: 1.8 ms per iteration for 5.5 GB, a third of what the memory system allows.
+__global__ void __launch_bounds__(kT)
+sn_grad_rows_kernel(float* __restrict__ G, const float* __restrict__ u, const float* __restrict__ v,
+                    const float* __restrict__ inv_sigma, const float* __restrict__ dot, int R, int C4) {
+    const int c4 = blockIdx.x * kT + threadIdx.x;
+    if (c4 >= C4) return;
+    const float is = __ldg(inv_sigma);
+    const float coef = -__ldg(dot) * is * is;
+    // v is often a slice of the batched power-iteration output at an odd offset: four scalar loads, once per thread
+    const float4 v4 = make_float4(__ldg(v + 4 * c4), __ldg(v + 4 * c4 + 1), __ldg(v + 4 * c4 + 2), __ldg(v + 4 * c4 + 3));
+    float4* g = reinterpret_cast<float4*>(G) + c4;
+    const int step = gridDim.y;
+    int r = blockIdx.y;
+    for (; r + 3 * step < R; r += 4 * step) {
+        float4 a[4];
+        float ur[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            a[k] = g[(size_t)(r + k * step) * C4];
+            ur[k] = coef * __ldg(u + r + k * step);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            a[k].x = fmaf(a[k].x, is, ur[k] * v4.x); a[k].y = fmaf(a[k].y, is, ur[k] * v4.y);
+            a[k].z = fmaf(a[k].z, is, ur[k] * v4.z); a[k].w = fmaf(a[k].w, is, ur[k] * v4.w);
+            g[(size_t)(r + k * step) * C4] = a[k];
+        }
+    }
+    for (; r < R; r += step) {
+        float4 a = g[(size_t)r * C4];
+        const float ur = coef * __ldg(u + r);
+        a.x = fmaf(a.x, is, ur * v4.x); a.y = fmaf(a.y, is, ur * v4.y);
+        a.z = fmaf(a.z, is, ur * v4.z); a.w = fmaf(a.w, is, ur * v4.w);
+        g[(size_t)r * C4] = a;
+    }
+}
+
+int launch_sn_grad(float* G, const float* u, const float* v, const float* inv_sigma, const float* dot, int R, int C,
+                   cudaStream_t st) {
+    if ((C & 3) == 0 && (reinterpret_cast<uintptr_t>(G) & 15) == 0) {
+        const int C4 = C / 4;
+        const int gx = (C4 + kT - 1) / kT;
+        int gy = (8 * imx::kNumSMs + gx - 1) / gx;
+        if (gy > R) gy = R;
+        if (gy > 65535) gy = 65535;
+        sn_grad_rows_kernel<<<dim3(gx, gy), kT, 0, st>>>(G, u, v, inv_sigma, dot, R, C4);
+        return imx::check_launch("spectral_norm_weight_grad");
+    }
+    const long n = (long)R * C;
+    long b2 = (n + kT - 1) / kT;
+    if (b2 > 8L * imx::kNumSMs) b2 = 8L * imx::kNumSMs;
+    sn_grad_kernel<<<(int)b2, kT, 0, st>>>(G, u, v, inv_sigma, dot, R, C);
+    return imx::check_launch("spectral_norm_weight_grad");
+}
+
 inline int slices_for(int R, int C) {
     const int col_blocks = (C + kT * 4 - 1) / (kT * 4);
     int s = (2 * imx::kNumSMs + col_blocks - 1) / col_blocks;
@@ -226,10 +283,7 @@ extern "C" int imx_spectral_norm_weight_grad_f32(float* G, const float* W, const
     if (blocks > 4L * imx::kNumSMs) blocks = 4L * imx::kNumSMs;
     if (blocks < 1) blocks = 1;
     sn_dot_kernel<<<(int)blocks, kT, 0, st>>>(G, W, dot_scratch, n);
-    long b2 = (n + kT - 1) / kT;
-    if (b2 > 8L * imx::kNumSMs) b2 = 8L * imx::kNumSMs;
-    sn_grad_kernel<<<(int)b2, kT, 0, st>>>(G, u, v, inv_sigma, dot_scratch, R, C);
-    return imx::check_launch("spectral_norm_weight_grad");
+    return launch_sn_grad(G, u, v, inv_sigma, dot_scratch, R, C, st);
 }
 
 // The correction alone, for a caller that already holds dot = <G, W> (imx_conv2d_igemm_wgrad_dot_bf16 forms it while
@@ -238,11 +292,7 @@ extern "C" int imx_spectral_norm_weight_grad_apply_f32(float* G, const float* u,
                                                        const float* dot, int R, int C, imx_stream_t stream) {
     IMX_REQUIRE(R > 0 && C > 0, "spectral_norm_weight_grad_apply: bad size");
     IMX_REQUIRE(G && u && v && inv_sigma && dot, "spectral_norm_weight_grad_apply: null pointer");
-    const long n = (long)R * C;
-    long b2 = (n + kT - 1) / kT;
-    if (b2 > 8L * imx::kNumSMs) b2 = 8L * imx::kNumSMs;
-    sn_grad_kernel<<<(int)b2, kT, 0, (cudaStream_t)stream>>>(G, u, v, inv_sigma, dot, R, C);
-    return imx::check_launch("spectral_norm_weight_grad_apply");
+    return launch_sn_grad(G, u, v, inv_sigma, dot, R, C, (cudaStream_t)stream);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -952,3 +952,37 @@ def test_interleaved_gamma_beta_pack_is_bit_exact(c, ch, k):
     want[rows, :, :, :ch] = (wg * sg).bfloat16().permute(0, 2, 3, 1)
     want[rows + 64, :, :, :ch] = (wb * sb).bfloat16().permute(0, 2, 3, 1)
     assert torch.equal(got.view(torch.int16), want.view(torch.int16))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('shape,cp', [((2, 38, 37, 53), 40), ((8, 3, 64, 128), 8), ((1, 35, 1, 5), 40), ((3, 64, 16, 24), 64),
+                                      ((2, 9, 128, 1), 16), ((2, 72, 19, 21), 72), ((1, 130, 8, 40), 136)])
+def test_nchw_to_nhwc_conversion_is_bit_exact(shape, cp):
+    """fp32 NCHW -> bf16 NHWC with zero-filled padding channels: the 128-pixel strip kernel (Cp <= 64) with ragged
+    strips, and the 32 x 32 tile kernel for wider tensors."""
+    from imaginaire_b200 import ops
+    g = torch.Generator().manual_seed(sum(shape))
+    x = torch.randn(*shape, generator=g).to(DEV)
+    got = ops.nchw_f32_to_nhwc_bf16(x, cp=cp)
+    assert got.shape == (shape[0], cp, shape[2], shape[3]) and got.is_contiguous(memory_format=torch.channels_last)
+    want = torch.zeros(shape[0], cp, shape[2], shape[3], dtype=torch.bfloat16, device=DEV)
+    want[:, :shape[1]] = x.bfloat16()
+    assert torch.equal(got.contiguous().view(torch.int16), want.view(torch.int16))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('r,c', [(64, 576), (37, 100), (2048, 1152), (5, 27), (1, 4)])
+def test_spectral_norm_weight_gradient_correction(r, c):
+    """G <- G / sigma - (<G, W> / sigma^2) u v^T (imx_spectral_norm_weight_grad_f32): the row-walking float4 kernel
+    (C % 4 == 0) and the scalar one, against float64."""
+    from imaginaire_b200 import ops
+    g = torch.Generator().manual_seed(r + c)
+    G, W = torch.randn(r, c, generator=g), torch.randn(r, c, generator=g)
+    u = torch.nn.functional.normalize(torch.randn(r, generator=g), dim=0)
+    v = torch.nn.functional.normalize(torch.randn(c, generator=g), dim=0)
+    inv_sigma = torch.tensor([0.37])
+    Gd = G.clone().to(DEV)
+    ops.spectral_norm_weight_grad_(Gd, W.to(DEV), u.to(DEV), v.to(DEV), inv_sigma.to(DEV))
+    dot = (G.double() * W.double()).sum()
+    ref = G.double() * 0.37 - dot * 0.37 ** 2 * torch.outer(u.double(), v.double())
+    assert H.rel_err(Gd.cpu(), ref) < 1e-5
