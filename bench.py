@@ -122,7 +122,7 @@ class ConvProbe:
     def install(self):
         import torch
         from imaginaire_b200 import ops
-        self._orig = (ops.conv2d_fprop, ops.conv2d_wgrad, ops.spade_gb_conv_modulate)
+        self._orig = (ops.conv2d_fprop, ops.conv2d_wgrad, ops.spade_gb_conv_modulate, ops.conv2d_fprop_window)
         probe = self
 
         def timed(fn, flops_fn, tag):
@@ -153,12 +153,19 @@ class ConvProbe:
             n, chp, h, wd = hidden.shape
             return 2.0 * n * h * wd * (2 * c) * chp * kh * kw
 
+        def window_flops(out, a, k):      # one parity class of a stride-2 data gradient
+            x, wpk, cout, kh, kw, _, _, ho, wo = a[:9]
+            return 2.0 * x.shape[0] * ho * wo * cout * getattr(wpk, '_imx_inner', x.shape[1]) * kh * kw
+
+        ops.conv2d_fprop_window = timed(self._orig[3], window_flops, 'fprop')
         ops.conv2d_fprop = timed(self._orig[0], fprop_flops, 'fprop')
         ops.conv2d_wgrad = timed(self._orig[1], wgrad_flops, 'wgrad')
         ops.spade_gb_conv_modulate = timed(self._orig[2], gb_flops, 'spade_gb')
 
     @staticmethod
     def describe(tag, out, a, k):
+        if tag == 'fprop' and len(a) > 12:
+            return 'x%s k%dx%d window %dx%d of %s (stride-2 dgrad class)' % (tuple(a[0].shape), a[3], a[4], a[7], a[8], tuple(a[9].shape))
         if tag == 'fprop':
             return 'x%s k%dx%d s%d -> %s' % (tuple(a[0].shape), a[3], a[4], a[5] if len(a) > 5 else k.get('stride', 1),
                                               tuple(out.shape))
@@ -178,7 +185,7 @@ class ConvProbe:
 
     def remove(self):
         from imaginaire_b200 import ops
-        ops.conv2d_fprop, ops.conv2d_wgrad, ops.spade_gb_conv_modulate = self._orig
+        ops.conv2d_fprop, ops.conv2d_wgrad, ops.spade_gb_conv_modulate, ops.conv2d_fprop_window = self._orig
 
     def summary(self):
         by = {}

@@ -60,7 +60,10 @@ struct ConvArgs {
     // geometry
     int N, H, W, Ho, Wo;
     int Cout, Cout_p;
-    int KH, KW, stride, pad;
+    int KH, KW, stride, pad_y, pad_x;
+    // where output pixel (oy, ox) goes: row oy * oys + oy0, column ox * oxs + ox0 of an out_H x out_W tensor (the whole
+    // tensor unless the launch fills one parity class of a stride-2 data gradient)
+    int out_H, out_W, oys, oxs, oy0, ox0;
     int tw_log2, tw, th;
     int tiles_x, tiles_y, tiles_n, total_tiles;
     int kc_blocks;
@@ -161,8 +164,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                 const int img = m_tile / tiles_per_img;
                 const int rem = m_tile - img * tiles_per_img;
                 const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
-                const int iy0 = ty * p.th * p.stride - p.pad;
-                const int ix0 = tx * p.tw * p.stride - p.pad;
+                const int iy0 = ty * p.th * p.stride - p.pad_y;
+                const int ix0 = tx * p.tw * p.stride - p.pad_x;
                 const int n0 = n_tile * BN;
                 const int kb = split * p.k_per_split;
                 const int ke = kb + p.k_per_split < k_iters ? kb + p.k_per_split : k_iters;
@@ -244,7 +247,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                     const int pr = prow >> p.tw_log2, pc = prow & (p.tw - 1);
                     const int oy = ty * p.th + pr, ox = tx * p.tw + pc;
                     const bool valid = (oy < p.Ho) && (ox < p.Wo);
-                    const size_t pix = ((size_t)img * p.Ho + oy) * p.Wo + ox;
+                    const size_t pix = ((size_t)img * p.out_H + oy * p.oys + p.oy0) * p.out_W + ox * p.oxs + p.ox0;
                     const uint32_t t_acc = tmem_base + as * (MT * BN) + mt * BN + (static_cast<uint32_t>(q * 32) << 16);
 #pragma unroll 1
                     for (int ch = 0; ch < BN / 32; ++ch) {
@@ -305,7 +308,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             const int pr = prow >> p.tw_log2, pc = prow & (p.tw - 1);
             const int oy = ty * p.th + pr, ox = tx * p.tw + pc;
             const bool valid = (oy < p.Ho) && (ox < p.Wo);
-            const size_t pix = ((size_t)img * p.Ho + oy) * p.Wo + ox;
+            const size_t pix = kMode == 0 ? ((size_t)img * p.out_H + oy * p.oys + p.oy0) * p.out_W + ox * p.oxs + p.ox0
+                                         : ((size_t)img * p.Ho + oy) * p.Wo + ox;
             const uint32_t t_acc = tmem_base + as * (MT * BN) + mt * BN + (static_cast<uint32_t>(q * 32) << 16);
 
             if constexpr (kMode == 0) {
@@ -544,12 +548,21 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const ConvArgs& a, cuda
 }
 
 // Common geometry + tensor maps.  `rows_b` = number of rows of the packed filter matrix.
+struct OutWindow { int pad_y, pad_x, Ho, Wo, out_H, out_W, oys, oxs, oy0, ox0; };
+
 int setup(ConvArgs& a, CUtensorMap& ta, CUtensorMap& tb, const void* x, const void* wpk, int N, int H, int W,
-          int Cin_p, int rows_b, int KH, int KW, int stride, int pad, int BN, int MT = 1) {
+          int Cin_p, int rows_b, int KH, int KW, int stride, int pad, int BN, int MT = 1, const OutWindow* win = nullptr) {
     a.N = N; a.H = H; a.W = W;
-    a.KH = KH; a.KW = KW; a.stride = stride; a.pad = pad;
+    a.KH = KH; a.KW = KW; a.stride = stride; a.pad_y = pad; a.pad_x = pad;
     a.Ho = (H + 2 * pad - KH) / stride + 1;
     a.Wo = (W + 2 * pad - KW) / stride + 1;
+    if (win) {           // explicit output size and per-axis left padding (rows / columns past the input read zeros)
+        a.pad_y = win->pad_y; a.pad_x = win->pad_x;
+        a.Ho = win->Ho; a.Wo = win->Wo;
+    }
+    a.out_H = win ? win->out_H : a.Ho; a.out_W = win ? win->out_W : a.Wo;
+    a.oys = win ? win->oys : 1; a.oxs = win ? win->oxs : 1;
+    a.oy0 = win ? win->oy0 : 0; a.ox0 = win ? win->ox0 : 0;
     if (a.Ho <= 0 || a.Wo <= 0) return imx::set_error(IMX_ERR_INVALID_ARG, "conv_igemm: empty output (%d x %d)", a.Ho, a.Wo);
     // pixel tile: tw = largest power of two <= min(Wo, 128) (at least 8 so th <= 16), th = 128 / tw
     int tw = 128;
@@ -632,9 +645,10 @@ struct FpropPlan { int BN, MT, splits, k_per_split; long ws_bytes; };
 // the K loop (taps x channel blocks) over several CTAs, which add fp32 partial sums into a
 // workspace; that costs a memset and a finishing kernel (~15 units).
 void plan_fprop(FpropPlan& pl, int N, int H, int W, int Cin_p, int Cout, int Cout_p, int KH, int KW, int stride, int pad,
-                int flags, bool allow_split) {
+                int flags, bool allow_split, const OutWindow* win = nullptr) {
     pl.BN = Cout_p > 128 ? 256 : (Cout_p > 64 ? 128 : (Cout_p > 32 ? 64 : 32));
-    const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
+    const int Ho = win ? win->Ho : (H + 2 * pad - KH) / stride + 1, Wo = win ? win->Wo : (W + 2 * pad - KW) / stride + 1;
+    if (win) allow_split = false;      // the finishing kernel addresses a dense output
     const long k_iters = (long)KH * KW * ((Cin_p + BK - 1) / BK);
     const int tiles_n = (Cout + pl.BN - 1) / pl.BN;
     const bool mt2_ok = pl.BN <= 128 &&
@@ -675,7 +689,8 @@ int check_fprop_args(int N, int H, int W, int Cin_p, int Cout, int Cout_p, int K
 
 int fprop_impl(const imx_bf16* x, const imx_bf16* wpk, const float* scale, const float* bias, const imx_bf16* residual,
                void* out, float* stats, void* workspace, int64_t workspace_bytes, int N, int H, int W, int Cin_p, int Cout,
-               int Cout_p, int KH, int KW, int stride, int pad, int flags, imx_stream_t stream) {
+               int Cout_p, int KH, int KW, int stride, int pad, int flags, imx_stream_t stream,
+               const OutWindow* win = nullptr) {
     IMX_REQUIRE(x && wpk && out, "conv2d_fprop: null pointer");
     int rc = check_fprop_args(N, H, W, Cin_p, Cout, Cout_p, KH, KW, stride, pad);
     if (rc) return rc;
@@ -685,7 +700,7 @@ int fprop_impl(const imx_bf16* x, const imx_bf16* wpk, const float* scale, const
     IMX_REQUIRE(aligned16(x) && aligned16(wpk) && aligned16(out) && aligned16(residual), "conv2d_fprop: pointers must be 16-byte aligned");
     if (N == 0) return IMX_OK;
     FpropPlan pl;
-    plan_fprop(pl, N, H, W, Cin_p, Cout, Cout_p, KH, KW, stride, pad, flags, workspace != nullptr);
+    plan_fprop(pl, N, H, W, Cin_p, Cout, Cout_p, KH, KW, stride, pad, flags, workspace != nullptr, win);
     if (pl.splits > 1) {
         IMX_REQUIRE(workspace_bytes >= pl.ws_bytes && aligned16(workspace),
                     "conv2d_fprop: split-K workspace too small (%lld bytes given, %lld needed) or misaligned",
@@ -694,7 +709,7 @@ int fprop_impl(const imx_bf16* x, const imx_bf16* wpk, const float* scale, const
     const int BN = pl.BN, MT = pl.MT;
     ConvArgs a{};
     CUtensorMap ta, tb;
-    rc = setup(a, ta, tb, x, wpk, N, H, W, Cin_p, Cout, KH, KW, stride, pad, BN, MT);
+    rc = setup(a, ta, tb, x, wpk, N, H, W, Cin_p, Cout, KH, KW, stride, pad, BN, MT, win);
     if (rc) return rc;
     a.Cout = Cout; a.Cout_p = Cout_p; a.flags = flags;
     a.scale = scale; a.bias = bias; a.residual = residual; a.out = out; a.stats = stats;
@@ -749,6 +764,27 @@ extern "C" int imx_conv2d_igemm_fprop_scaled_bf16(const imx_bf16* x, const imx_b
                                                   int stride, int pad, int flags, imx_stream_t stream) {
     return fprop_impl(x, wpk, scale, bias, residual, out, stats, workspace, workspace_bytes, N, H, W, Cin_p, Cout, Cout_p,
                       KH, KW, stride, pad, flags, stream);
+}
+
+// One piece of a larger output: y[n][oy * oys + oy0][ox * oxs + ox0][:] = act(scale * sum_taps x[n][oy + kh - pad_y]
+// [ox + kw - pad_x][:] . w[:][kh][kw][:] + bias) for oy < Ho, ox < Wo, stride 1, rows / columns outside the input read
+// as zeros on every side.  The data gradient of a stride-2 convolution is four such launches, one per parity class of
+// the input pixel, each with the taps of that parity (imaginaire_b200/functional.py: conv2d_dgrad) -- a quarter of the
+// multiply-adds of the zero-insertion form and no zero-filled copy of dy.
+extern "C" int imx_conv2d_igemm_fprop_window_bf16(const imx_bf16* x, const imx_bf16* wpk, const float* scale,
+                                                  const float* bias, const imx_bf16* residual, void* out,
+                                                  int N, int H, int W, int Cin_p, int Cout, int Cout_p, int KH, int KW,
+                                                  int pad_y, int pad_x, int Ho, int Wo, int out_H, int out_W,
+                                                  int out_stride_y, int out_stride_x, int out_y0, int out_x0,
+                                                  int flags, imx_stream_t stream) {
+    IMX_REQUIRE(pad_y >= 0 && pad_x >= 0 && Ho > 0 && Wo > 0, "conv2d_fprop_window: bad padding or output size");
+    IMX_REQUIRE(out_stride_y >= 1 && out_stride_x >= 1 && out_y0 >= 0 && out_x0 >= 0 &&
+                (Ho - 1) * out_stride_y + out_y0 < out_H && (Wo - 1) * out_stride_x + out_x0 < out_W,
+                "conv2d_fprop_window: the window leaves the %d x %d output", out_H, out_W);
+    IMX_REQUIRE(!(flags & IMX_EPI_STATS), "conv2d_fprop_window: no statistics epilogue");
+    const OutWindow win{pad_y, pad_x, Ho, Wo, out_H, out_W, out_stride_y, out_stride_x, out_y0, out_x0};
+    return fprop_impl(x, wpk, scale, bias, residual, out, nullptr, nullptr, 0, N, H, W, Cin_p, Cout, Cout_p, KH, KW, 1,
+                      pad_y > pad_x ? pad_y : pad_x, flags, stream, &win);
 }
 
 extern "C" int64_t imx_conv2d_fprop_workspace_bytes(int N, int H, int W, int Cin_p, int Cout, int Cout_p,

@@ -6,6 +6,7 @@ Activations are bf16 NHWC (channels_last) tensors with the channel count padded
 to a multiple of 8 (padding channels are zero).
 """
 import math
+import os
 
 import torch
 import torch.distributed as dist
@@ -253,6 +254,54 @@ def _conv2d_wgrad(x, dy, cin, cout, kh, kw, stride, pad, sn=None):
     return dw
 
 
+def _parity_taps(k, pad, a):
+    """Taps of a size-k, stride-2, padding-`pad` filter that reach input pixels of parity a (i = 2m + a):
+    (first tap k0, number of taps T, left padding of the stride-1 correlation over dy), or None when no tap does or
+    the padding would be negative.  dx[2m + a] = sum_t dy[m + t - left] * w[k0 + 2 (T - 1 - t)]."""
+    k0 = (a + pad) % 2
+    if k0 >= k:
+        return None
+    t = (k - k0 + 1) // 2
+    left = (k0 + 2 * (t - 1) - a - pad) // 2
+    return None if left < 0 else (k0, t, left)
+
+
+def _dgrad_stride2(dy, weight, pad, h, w, cin_p, inv_sigma):
+    """Data gradient of a stride-2 convolution as four stride-1 convolutions of dy, one per parity class of the input
+    pixel, each with the filter taps of that parity, written straight into its pixels of dx
+    (imx_conv2d_igemm_fprop_window_bf16).  A quarter of the multiply-adds of the zero-insertion form below, no
+    zero-filled copy of dy.  The four transposed sub-filters are packed once per optimizer step."""
+    cout, cin, kh, kw = weight.shape
+    cout_p = dy.shape[1]
+    plan = []
+    for a in (0, 1):
+        for b in (0, 1):
+            ty, tx = _parity_taps(kh, pad, a), _parity_taps(kw, pad, b)
+            if ty is None or tx is None:
+                return None
+            plan.append((a, b, ty, tx))
+    is_param = isinstance(weight, torch.nn.Parameter)
+    dx = ops.empty_nhwc(dy.shape[0], cin_p, h, w, dy.device)
+    for a, b, (ky0, nty, py), (kx0, ntx, px) in plan:
+        ma, mb = (h - a + 1) // 2, (w - b + 1) // 2
+        if ma <= 0 or mb <= 0:
+            continue
+        key = (id(weight), cout_p, 'dgrad2', pad, a, b)
+        hit = _PACK_CACHE.get(key) if is_param else None
+        if hit is not None and hit[0] == weight._version and hit[1] == weight.data_ptr():
+            wpk = hit[2]
+        else:
+            # flip-pack of the plain strided slice: packed[ci][t][co] = w[co][ci][k0 + 2 (T - 1 - t)]
+            sub = weight.detach()[:, :, ky0::2, kx0::2].contiguous()
+            wpk = ops.pack_conv_weight(sub, None if is_param else inv_sigma, cin_p=cout_p, transpose_flip=True)
+            wpk._imx_inner = cout
+            if is_param:
+                _PACK_CACHE[key] = (weight._version, weight.data_ptr(), wpk)
+        ops.conv2d_fprop_window(dy, wpk, cin, nty, ntx, py, px, ma, mb, dx, 2, 2, a, b,
+                                scale=inv_sigma if is_param else None)
+    return dx
+
+
 def conv2d_dgrad(dy, weight, stride, pad, h, w, cin_p, inv_sigma=None):
     """Data gradient of conv2d as a stride-1 convolution of dy with the transposed,
     spatially flipped filter.  A stride-2 forward is handled by zero-insertion."""
@@ -260,6 +309,10 @@ def conv2d_dgrad(dy, weight, stride, pad, h, w, cin_p, inv_sigma=None):
     cout_p = dy.shape[1]
     if kh != kw:
         raise RuntimeError('conv2d_dgrad: only square kernels are supported')
+    if stride == 2 and not _small_cin(cout_p, kh, kw) and cin_p != 8 and os.environ.get('IMX_DGRAD_S2', '1') != '0':
+        dx = _dgrad_stride2(dy, weight, pad, h, w, cin_p, inv_sigma)
+        if dx is not None:
+            return dx
     if stride != 1:
         n, _, ho, wo = dy.shape
         dh = (ho - 1) * stride + 1 + (h + 2 * pad - kh) % stride

@@ -434,6 +434,24 @@ def spade_modulate_bwd(x, dy, mean, rstd, w, b, gamma, beta, per_instance, act, 
 
 # ------------------------------------------------------------ convolutions
 
+def conv2d_fprop_window(x, wpk, cout, kh, kw, pad_y, pad_x, ho, wo, out, stride_y, stride_x, y0, x0, scale=None):
+    """Stride-1 convolution of x (NHWC bf16) whose ho x wo output pixels land at rows oy * stride_y + y0, columns
+    ox * stride_x + x0 of the existing NHWC bf16 tensor `out` (imx_conv2d_igemm_fprop_window_bf16)."""
+    _req_cuda(x, wpk, out); _req_nhwc(x, 'x'); _req_nhwc(out, 'out')
+    n, cin_p, h, w = x.shape
+    if wpk.dtype != torch.bfloat16 or not wpk.is_contiguous() or wpk.shape[-1] != cin_p:
+        raise RuntimeError('packed weight must be contiguous bf16 [rows, KH, KW, Cin_p=%d]; got %s' %
+                           (cin_p, tuple(wpk.shape)))
+    if out.dtype != torch.bfloat16 or out.shape[0] != n:
+        raise RuntimeError('out must be an NHWC bf16 tensor of the same batch size')
+    if scale is not None:
+        _req_f32c(scale, 'scale')
+    _C.lib().call('imx_conv2d_igemm_fprop_window_bf16', _ptr(x), _ptr(wpk), _ptr(scale), None, None, _ptr(out),
+                  n, h, w, cin_p, cout, out.shape[1], kh, kw, pad_y, pad_x, ho, wo, out.shape[2], out.shape[3],
+                  stride_y, stride_x, y0, x0, 0, _stream())
+    return out
+
+
 def conv2d_fprop(x, wpk, cout, kh, kw, stride=1, pad=0, bias=None, residual=None, flags=0, stats=None,
                  cout_p=None, out_f32=False, scale=None):
     """x: NHWC bf16 (C = Cin_p), wpk: packed bf16 [Cout, KH, KW, Cin_p].  scale: optional 1-element fp32 device

@@ -349,6 +349,24 @@ IMX_API int imx_conv2d_igemm_fprop_scaled_bf16(const imx_bf16* x, const imx_bf16
                                                int Cout, int Cout_p, int KH, int KW,
                                                int stride, int pad, int flags, imx_stream_t stream);
 
+/* One piece of a larger output tensor, stride 1:
+ *   out[n][oy * out_stride_y + out_y0][ox * out_stride_x + out_x0][:] =
+ *       act(scale * sum_{kh,kw} x[n][oy + kh - pad_y][ox + kw - pad_x][:] . w[:][kh][kw][:] + bias) (+ residual)
+ * for oy < Ho, ox < Wo; out (and residual) are N x out_H x out_W x Cout_p; rows / columns outside x read as zeros on
+ * every side, so pad_y / pad_x are the LEFT paddings only and Ho / Wo are free.  scale, bias, residual may be null.
+ * The data gradient of a stride-2 convolution is four such launches -- one per parity class (a, b) of the input pixel
+ * (2m + a, 2n + b), x = dy, w = the taps kh = (a + pad) mod 2, +2, ... of the filter, transposed
+ * (imaginaire_b200/functional.py: conv2d_dgrad) -- instead of a stride-1 convolution over a zero-inserted copy of dy
+ * that spends three quarters of its multiply-adds on zeros.
+ * ref: the cuDNN data gradient behind torch's conv2d backward for the stride-2 layers of
+ * imaginaire/discriminators/multires_patch.py:197-215 and fpse.py:62-75 */
+IMX_API int imx_conv2d_igemm_fprop_window_bf16(const imx_bf16* x, const imx_bf16* wpk, const float* scale,
+                                               const float* bias, const imx_bf16* residual, void* out,
+                                               int N, int H, int W, int Cin_p, int Cout, int Cout_p, int KH, int KW,
+                                               int pad_y, int pad_x, int Ho, int Wo, int out_H, int out_W,
+                                               int out_stride_y, int out_stride_x, int out_y0, int out_x0,
+                                               int flags, imx_stream_t stream);
+
 /* SPADE projection conv fused with the modulation (gamma/beta never reach HBM):
  *   gb = conv(hidden; wgb) (+bias), wgb rows interleaved per 64-channel block as
  *   [64 gamma rows | 64 beta rows] (imx_pack_spade_gb_weight_bf16),

@@ -327,7 +327,9 @@ def test_conv2d_wgrad_vs_oracle(case):
 
 
 @pytest.mark.parametrize('case', [(2, 64, 64, 16, 32, 3, 1, 1), (1, 40, 72, 13, 11, 5, 1, 2), (2, 64, 128, 32, 32, 3, 2, 1),
-                                  (2, 32, 64, 33, 47, 4, 2, 1)])
+                                  (2, 32, 64, 33, 47, 4, 2, 1), (1, 40, 128, 64, 128, 4, 2, 1), (2, 128, 256, 30, 62, 4, 2, 2),
+                                  (3, 72, 40, 17, 9, 3, 2, 1), (1, 512, 512, 16, 32, 4, 2, 1), (2, 64, 64, 21, 35, 5, 2, 2),
+                                  (2, 64, 96, 16, 16, 2, 2, 0)])
 def test_conv2d_dgrad_vs_oracle(case):
     from imaginaire_b200 import ops, functional as NF
     n, cin, cout, h, w, k, s, p = case
@@ -341,6 +343,20 @@ def test_conv2d_dgrad_vs_oracle(case):
     ref = torch.nn.grad.conv2d_input((n, cin, h, w), wt, dy, stride=s, padding=p)
     assert dx.shape == (n, cin_p, h, w)
     assert H.rel_err(dx[:, :cin].float().cpu(), ref) < 4e-3
+    if s == 2:
+        # the parity-class form (four stride-1 convolutions) and the zero-insertion form are the same sums
+        os.environ['IMX_DGRAD_S2'] = '0'
+        try:
+            dz = NF.conv2d_dgrad(nhwc(dp), wt.to(DEV), s, p, h, w, cin_p)
+        finally:
+            del os.environ['IMX_DGRAD_S2']
+        assert H.rel_err(dx[:, :cin].float().cpu(), dz[:, :cin].float().cpu()) < 4e-3
+        # a Parameter with 1 / sigma: sub-filters packed unscaled (cached), the scale applied in the epilogue
+        wp = torch.nn.Parameter(wt.to(DEV))
+        inv_sigma = torch.tensor([0.61], device=DEV)
+        for _ in range(2):          # second call: cache hit
+            ds = NF.conv2d_dgrad(nhwc(dp), wp, s, p, h, w, cin_p, inv_sigma=inv_sigma)
+        assert H.rel_err(ds[:, :cin].float().cpu(), ref * 0.61) < 4e-3
 
 
 @pytest.mark.parametrize('case', [(2, 3, 16, 20, 33, 3, 1, 1),      # few input channels (image -> first layer)
@@ -982,7 +998,9 @@ def test_spectral_norm_weight_gradient_correction(r, c):
     v = torch.nn.functional.normalize(torch.randn(c, generator=g), dim=0)
     inv_sigma = torch.tensor([0.37])
     Gd = G.clone().to(DEV)
-    ops.spectral_norm_weight_grad_(Gd, W.to(DEV), u.to(DEV), v.to(DEV), inv_sigma.to(DEV))
+    vb = torch.zeros(c + 1, device=DEV)          # v at an odd offset of a larger buffer, as the batched power iteration leaves it
+    vb[1:] = v.to(DEV)
+    ops.spectral_norm_weight_grad_(Gd, W.to(DEV), u.to(DEV), vb[1:], inv_sigma.to(DEV))
     dot = (G.double() * W.double()).sum()
     ref = G.double() * 0.37 - dot * 0.37 ** 2 * torch.outer(u.double(), v.double())
     assert H.rel_err(Gd.cpu(), ref) < 1e-5
