@@ -441,6 +441,28 @@ void launch_pack_rows(dim3 grid, cudaStream_t st, const float* w, const float* w
     }
 }
 
+// Splits the transposed, flipped filter of a stride-2 convolution, full[ci][KH-1-kh][KW-1-kw][co_p] (the dgrad pack),
+// into the four parity-class sub-filters of imx_conv2d_igemm_fprop_window_bf16's stride-2 data gradient, stored one
+// after the other in class order (a, b) = (0,0), (0,1), (1,0), (1,1):
+//   cls[a][b][ci][ty][tx][:] = full[ci][KH-1-kh][KW-1-kw][:],  kh = k0(a) + 2 (T(a) - 1 - ty),  k0(a) = (a + pad) mod 2
+// One thread per 16-byte chunk of `full` (coalesced both ways: whole co_p runs move).
+struct ParitySplit { long long base[2][2]; int ty[2], tx[2]; };   // class offsets in 16-byte chunks, taps per class
+
+__global__ void split_dgrad_s2_kernel(const uint4* __restrict__ full, uint4* __restrict__ out, ParitySplit ps, long total,
+                                      int KH, int KW, int c8n, int pad) {
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const int c8 = (int)(i % c8n);
+        long t = i / c8n;
+        const int fx = (int)(t % KW); t /= KW;
+        const int fy = (int)(t % KH);
+        const long ci = t / KH;
+        const int kh = KH - 1 - fy, kw = KW - 1 - fx;
+        const int a = (kh + pad) & 1, b = (kw + pad) & 1;          // parity of the input pixels this tap reaches
+        const int ty = ps.ty[a] - 1 - (kh >> 1), tx = ps.tx[b] - 1 - (kw >> 1);   // (kh - k0) / 2 == kh >> 1 as k0 = kh & 1
+        out[ps.base[a][b] + ((ci * ps.ty[a] + ty) * ps.tx[b] + tx) * c8n + c8] = __ldg(full + i);
+    }
+}
+
 // Scalar fallback for very large kernels.
 __global__ void pack_weight_kernel(const float* __restrict__ w, const float* __restrict__ inv_sigma,
                                    __nv_bfloat16* __restrict__ packed, int Cout, int Cin, int KH, int KW,
@@ -856,6 +878,34 @@ extern "C" int imx_pack_conv_weight_bf16(const float* w, const float* inv_sigma,
     pack_weight_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(
         w, inv_sigma, reinterpret_cast<__nv_bfloat16*>(packed), Cout, Cin, KH, KW, Cin_p, transpose_flip);
     return imx::check_launch("pack_conv_weight");
+}
+
+extern "C" int imx_split_dgrad_s2_filter_bf16(const imx_bf16* full, imx_bf16* out, int Cin, int KH, int KW, int Cout_p,
+                                             int pad, int64_t* class_offsets, imx_stream_t stream) {
+    IMX_REQUIRE(full && out, "split_dgrad_s2_filter: null pointer");
+    IMX_REQUIRE(Cin > 0 && KH >= 2 && KW >= 2 && KH <= 16 && KW <= 16 && pad >= 0, "split_dgrad_s2_filter: bad filter geometry");
+    IMX_REQUIRE(Cout_p > 0 && Cout_p % 8 == 0, "split_dgrad_s2_filter: Cout_p must be a positive multiple of 8");
+    IMX_REQUIRE(((reinterpret_cast<uintptr_t>(full) | reinterpret_cast<uintptr_t>(out)) & 15) == 0, "split_dgrad_s2_filter: pointers must be 16-byte aligned");
+    ParitySplit ps;
+    for (int a = 0; a < 2; ++a) {
+        const int k0 = (a + pad) & 1;
+        ps.ty[a] = (KH - k0 + 1) / 2;
+        ps.tx[a] = (KW - k0 + 1) / 2;
+    }
+    const int c8n = Cout_p / 8;
+    long long off = 0;
+    for (int a = 0; a < 2; ++a)
+        for (int b = 0; b < 2; ++b) {
+            ps.base[a][b] = off;
+            if (class_offsets) class_offsets[a * 2 + b] = off * 8;      // in elements
+            off += (long long)Cin * ps.ty[a] * ps.tx[b] * c8n;
+        }
+    const long total = (long)Cin * KH * KW * c8n;
+    long blocks = (total + 255) / 256;
+    if (blocks > 8L * imx::kNumSMs) blocks = 8L * imx::kNumSMs;
+    split_dgrad_s2_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const uint4*>(full),
+                                                                         reinterpret_cast<uint4*>(out), ps, total, KH, KW, c8n, pad);
+    return imx::check_launch("split_dgrad_s2_filter");
 }
 
 extern "C" int imx_pack_spade_gb_weight_bf16(const float* w_gamma, const float* w_beta,

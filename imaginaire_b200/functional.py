@@ -270,7 +270,7 @@ def _dgrad_stride2(dy, weight, pad, h, w, cin_p, inv_sigma):
     """Data gradient of a stride-2 convolution as four stride-1 convolutions of dy, one per parity class of the input
     pixel, each with the filter taps of that parity, written straight into its pixels of dx
     (imx_conv2d_igemm_fprop_window_bf16).  A quarter of the multiply-adds of the zero-insertion form below, no
-    zero-filled copy of dy.  The four transposed sub-filters are packed once per optimizer step."""
+    zero-filled copy of dy.  The four transposed sub-filters are built once per optimizer step (two launches)."""
     cout, cin, kh, kw = weight.shape
     cout_p = dy.shape[1]
     plan = []
@@ -281,23 +281,24 @@ def _dgrad_stride2(dy, weight, pad, h, w, cin_p, inv_sigma):
                 return None
             plan.append((a, b, ty, tx))
     is_param = isinstance(weight, torch.nn.Parameter)
+    key = (id(weight), cout_p, 'dgrad2', pad)
+    hit = _PACK_CACHE.get(key) if is_param else None
+    if hit is not None and hit[0] == weight._version and hit[1] == weight.data_ptr():
+        parts = hit[2]
+    else:
+        # one flip pack of the whole filter + one launch that sorts its taps into the four classes
+        full = ops.pack_conv_weight(weight, None if is_param else inv_sigma, cin_p=cout_p, transpose_flip=True)
+        parts = ops.split_dgrad_s2_filter(full, pad)
+        for wpk in parts.values():
+            wpk._imx_inner = cout
+        if is_param:
+            _PACK_CACHE[key] = (weight._version, weight.data_ptr(), parts)
     dx = ops.empty_nhwc(dy.shape[0], cin_p, h, w, dy.device)
     for a, b, (ky0, nty, py), (kx0, ntx, px) in plan:
         ma, mb = (h - a + 1) // 2, (w - b + 1) // 2
         if ma <= 0 or mb <= 0:
             continue
-        key = (id(weight), cout_p, 'dgrad2', pad, a, b)
-        hit = _PACK_CACHE.get(key) if is_param else None
-        if hit is not None and hit[0] == weight._version and hit[1] == weight.data_ptr():
-            wpk = hit[2]
-        else:
-            # flip-pack of the plain strided slice: packed[ci][t][co] = w[co][ci][k0 + 2 (T - 1 - t)]
-            sub = weight.detach()[:, :, ky0::2, kx0::2].contiguous()
-            wpk = ops.pack_conv_weight(sub, None if is_param else inv_sigma, cin_p=cout_p, transpose_flip=True)
-            wpk._imx_inner = cout
-            if is_param:
-                _PACK_CACHE[key] = (weight._version, weight.data_ptr(), wpk)
-        ops.conv2d_fprop_window(dy, wpk, cin, nty, ntx, py, px, ma, mb, dx, 2, 2, a, b,
+        ops.conv2d_fprop_window(dy, parts[(a, b)], cin, nty, ntx, py, px, ma, mb, dx, 2, 2, a, b,
                                 scale=inv_sigma if is_param else None)
     return dx
 

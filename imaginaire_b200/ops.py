@@ -195,6 +195,27 @@ def pack_conv_weight(w, inv_sigma=None, cin_p=None, transpose_flip=False):
     return out
 
 
+def split_dgrad_s2_filter(full, pad):
+    """full: the transposed, flipped filter [Cin, KH, KW, Cout_p] (pack_conv_weight(..., transpose_flip=True)) of a
+    stride-2 convolution.  Returns {(a, b): sub-filter [Cin, T(a), T(b), Cout_p]} for the four parity classes of its
+    data gradient -- views of one buffer, one launch (imx_split_dgrad_s2_filter_bf16)."""
+    _req_cuda(full)
+    cin, kh, kw, cp = full.shape
+    if full.dtype != torch.bfloat16 or not full.is_contiguous():
+        raise RuntimeError('split_dgrad_s2_filter: full must be contiguous bf16 [Cin, KH, KW, Cout_p]')
+    out = torch.empty(full.numel(), dtype=torch.bfloat16, device=full.device)
+    _C.lib().call('imx_split_dgrad_s2_filter_bf16', _ptr(full), _ptr(out), cin, kh, kw, cp, pad, None, _stream())
+    parts, off = {}, 0
+    for a in (0, 1):
+        ty = (kh - (a + pad) % 2 + 1) // 2
+        for b in (0, 1):
+            tx = (kw - (b + pad) % 2 + 1) // 2
+            n = cin * ty * tx * cp
+            parts[(a, b)] = out[off:off + n].view(cin, ty, tx, cp)
+            off += n
+    return parts
+
+
 def pack_spade_gb_weight(w_gamma, w_beta, inv_sigma_gamma=None, inv_sigma_beta=None, ch_p=None):
     _req_cuda(w_gamma, w_beta)
     w_gamma = w_gamma.detach().float().contiguous()

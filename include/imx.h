@@ -367,6 +367,14 @@ IMX_API int imx_conv2d_igemm_fprop_window_bf16(const imx_bf16* x, const imx_bf16
                                                int out_stride_y, int out_stride_x, int out_y0, int out_x0,
                                                int flags, imx_stream_t stream);
 
+/* The four parity-class sub-filters of a stride-2 data gradient (see imx_conv2d_igemm_fprop_window_bf16) from the
+ * transposed, flipped filter full = imx_pack_conv_weight_bf16(..., transpose_flip = 1): Cin x KH x KW x Cout_p bf16.
+ * out (as many elements as full) receives the classes (a, b) = (0,0), (0,1), (1,0), (1,1) one after the other, class
+ * (a, b) as Cin x T(a) x T(b) x Cout_p with T(a) = number of taps k = (a + pad) mod 2, +2, ... below KH (KW);
+ * class_offsets (host memory, 4 entries, may be null) receives where each class starts, in elements. */
+IMX_API int imx_split_dgrad_s2_filter_bf16(const imx_bf16* full, imx_bf16* out, int Cin, int KH, int KW, int Cout_p,
+                                           int pad, int64_t* class_offsets, imx_stream_t stream);
+
 /* SPADE projection conv fused with the modulation (gamma/beta never reach HBM):
  *   gb = conv(hidden; wgb) (+bias), wgb rows interleaved per 64-channel block as
  *   [64 gamma rows | 64 beta rows] (imx_pack_spade_gb_weight_bf16),
