@@ -305,7 +305,9 @@ def _dgrad_stride2(dy, weight, pad, h, w, cin_p, inv_sigma):
 
 def conv2d_dgrad(dy, weight, stride, pad, h, w, cin_p, inv_sigma=None):
     """Data gradient of conv2d as a stride-1 convolution of dy with the transposed,
-    spatially flipped filter.  A stride-2 forward is handled by zero-insertion."""
+    spatially flipped filter.  A stride-2 forward goes through _dgrad_stride2 (four parity-class convolutions);
+    zero insertion remains for the few-channel layers and for geometries a parity class cannot express (a filter
+    smaller than the stride, padding larger than the filter reaches)."""
     cout, cin, kh, kw = weight.shape
     cout_p = dy.shape[1]
     if kh != kw:

@@ -1,3 +1,10 @@
+"""Forward flow warps with and without the TMA-staged shared-memory window (developer tool; one GPU).
+
+    FLOWGRID=32,64 IMX_WARPWIN=0|1 IMX_WARPWIN_R2D=0|1 IMX_WARPWIN_CPB=32 python tools/warp_window_bench.py
+
+FLOWGRID: size of the random grid the flow field is interpolated from (smaller = smoother flow); the table in
+profiles/r02_warp_window.md is a sweep over it.
+"""
 import sys, os, json
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
