@@ -179,7 +179,7 @@ __global__ void nhwc_to_nchw_kernel(const __nv_bfloat16* __restrict__ src, float
 // R -> channel (R / 128) * 64 + R % 64 of gamma (R % 128 < 64) or beta), each with its own scale.
 //
 // A [inner x taps] -> [taps x inner] transpose per row of the packed matrix through shared memory.  A CTA owns
-// 128 inner indices of `rpb` consecutive packed rows (8 for 3x3: 36 KB of fp32 in flight per CTA, ~6 CTAs per SM):
+// 128 inner indices of `rpb` consecutive packed rows (8 for 3x3: 36 KB of fp32 per CTA, 5 CTAs per SM):
 // the training step packs ~0.9 G filter elements per iteration and the first version (one row, 4.6 KB per CTA,
 // 4 loads per thread, a division per element) ran at a quarter of the HBM peak.  Plain: every row is one contiguous
 // run of 128 * taps floats, copied by the warps of that row, kPackBatch loads in flight per thread.  Flip: the rows are
