@@ -277,41 +277,48 @@ def hbm_rooflines(dev, hbm_peak_gbs):
 # ---------------------------------------------------------------------- CPU baseline
 
 def cpu_reference_step(cfg, batch=1, seed=0):
-    """One bounded sample of the reference's CPU path: the SPADE generator forward (training
-    mode, fp32, all host cores) through the CPU oracle port of the reference's PyTorch code.
-    Returns (seconds, images)."""
+    """One bounded sample of the reference's CPU path: ONE REAL TRAINING ITERATION of the benchmark's configuration at
+    batch 1 -- dis_update, gen_update, moving average: three generator passes, two discriminator calls on real and
+    fake, hinge + feature-matching + KL + VGG-19 perceptual losses, both backward passes, both Adam steps -- in fp32 on
+    all host cores through the CPU oracle port of the reference's PyTorch code (oracle/train_oracle.py, pinned to the
+    reference trainer's own outputs by tests/test_train_oracle.py).  Returns (seconds, images)."""
     import torch
-    from oracle import spade_oracle as so
+    from oracle import train_oracle as to
+    from imaginaire_b200.discriminators.spade import Discriminator
     from imaginaire_b200.generators.spade import Generator
     from imaginaire_b200.utils.data import get_crop_h_w
     from imaginaire_b200.utils.init_weight import weights_init
     state = cpu_reference_step.__dict__
-    if 'sd' not in state:
+    if 'sd_g' not in state:
+        from torchvision.models.vgg import vgg19
         torch.manual_seed(seed)
-        net = Generator(cfg.gen, cfg.data)
-        net.apply(weights_init('xavier', 0.02))
-        state['sd'] = net.state_dict()
-        state['spec'] = so.generator_spec_from_cfg(cfg.gen, get_crop_h_w(cfg.data.train.augmentations))
+        net_G, net_D = Generator(cfg.gen, cfg.data), Discriminator(cfg.dis, cfg.data)
+        fn = weights_init(cfg.trainer.init.type, cfg.trainer.init.gain)
+        net_G.apply(fn)
+        net_D.apply(fn)
+        state['sd_g'], state['sd_d'] = net_G.state_dict(), net_D.state_dict()
+        state['vgg'] = vgg19(weights=None).features.state_dict()     # random filters, as on the GPU arm (no download)
+        state['spec'] = to.trainer_spec_from_cfg(cfg, get_crop_h_w(cfg.data.train.augmentations))
+        ema = {k[:-5] if k.endswith('weight_orig') else k: None for k in state['sd_g']
+               if not k.endswith(('weight_u', 'weight_v'))}
+        zeros = {k: torch.zeros_like(state['sd_g'].get(k, state['sd_g'].get(k + '_orig'))) for k in ema}
+        state['train'] = {'opt_d': {}, 'opt_g': {}, 'ema_updates': 0,
+                          'ema': to.model_average_update(zeros, state['sd_g'], 0.0),
+                          'ema_start': int(getattr(cfg.trainer, 'model_average_start_iteration', 1000)),
+                          'ema_beta': float(getattr(cfg.trainer, 'model_average_beta', 0.9999))}
     data = synthetic_batch(cfg, batch, seed)
-    eps = torch.randn(batch, cfg.gen.style_dims)
+    eps_d, eps_g = torch.randn(batch, cfg.gen.style_dims), torch.randn(batch, cfg.gen.style_dims)
     t0 = time.perf_counter()
-    with torch.no_grad():
-        so.generator(state['sd'], data, state['spec'], True, eps)
+    _, _, state['sd_g'], state['sd_d'], state['train'] = to.train_iteration(
+        state['sd_g'], state['sd_d'], state['vgg'], data, state['spec'], eps_d, eps_g, state['train'])
     return time.perf_counter() - t0, batch
-
-
-# Algorithmic FLOPs per image (SURVEY.md section 3.1 / BASELINE.md section 3): one training
-# iteration = 4 F_G + 4.5 F_D + 3 F_VGG; the generator forward alone is F_G.
-F_G, F_D, F_VGG = 2883.0, 172.0, 102.0
-STEP_FLOP_SHARE_OF_G_FWD = F_G / (4 * F_G + 4.5 * F_D + 3 * F_VGG)
 
 
 def run_reference(args):
     """Reference arm: the reference's own (CPU, PyTorch) implementation of the path, as ported in
     oracle/, timed on this box's host cores.  /root/reference is Python and does not travel;
-    the oracle is pinned to it by tests/golden.  Each step is a bounded sample: one generator
-    forward at batch 1 of the same config; img/s for the training step is the sample's
-    throughput times the generator forward's share of the step's algorithmic FLOPs."""
+    the oracle is pinned to it by tests/golden.  Each step is a bounded sample of the workload: one whole training
+    iteration of the same configuration at batch 1 (the GPU arm runs batch 8 per step)."""
     import torch
     from imaginaire_b200.config import Config
     rank = int(os.environ.get('RANK', '0'))
@@ -323,29 +330,33 @@ def run_reference(args):
     steps, warmup = args.steps, max(args.warmup, 1)
     if steps + warmup > 8:   # keep the whole run within a few minutes
         warmup = 1
-        steps = min(steps, 6)
+        steps = min(steps, 4)
     for _ in range(warmup):
         cpu_reference_step(cfg)
-    t = 0.0
+    t, images = 0.0, 0
     for _ in range(steps):
-        dt, _ = cpu_reference_step(cfg)
+        dt, n = cpu_reference_step(cfg)
         t += dt
-    fwd_img_s = steps / t
-    value = fwd_img_s * STEP_FLOP_SHARE_OF_G_FWD
-    sample = ('generator forward (train mode, fp32), batch 1, 256x512, CPU oracle port of the reference; '
-              'train img/s = forward img/s (%.4f) x F_G/(4F_G+4.5F_D+3F_VGG) (%.4f)' % (fwd_img_s, STEP_FLOP_SHARE_OF_G_FWD))
+        images += n
+    value = images / t
+    sample = CPU_SAMPLE % (t / steps)
     line = {
         'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': steps,
         'warmup': warmup, 'ms_per_step': 1000.0 * t / steps, 'higher_is_better': True, 'scaling': 'weak',
         'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-        'config': {'workload': 'SPADE G+D training step, base128 generator, 256x512, 35 labels (CPU sample: generator '
-                               'forward at batch 1, extrapolated to the training step by its share of the algorithmic FLOPs)',
+        'config': {'workload': 'SPADE G+D training step, base128 generator + SPADE discriminator, 256x512, 35 labels, '
+                               'SyncBN, Adam, EMA (CPU sample: one whole training iteration at batch 1)',
                    'config_file': 'configs/' + args.config},
         'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
         'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
     }
     print(json.dumps(line), flush=True)
+
+
+CPU_SAMPLE = ('one whole G+D training iteration (dis_update + gen_update + moving average, fp32) of the same '
+              'configuration at batch 1, 256x512, through the CPU oracle port of the reference trainer '
+              '(oracle/train_oracle.py): %.2f s per iteration')
 
 
 # ------------------------------------------------------------------------- our arm
@@ -530,14 +541,9 @@ def run_ours(args):
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
             torch.set_num_threads(cores)
-            cpu_reference_step(cfg)            # warm-up (weight build, thread pool)
+            cpu_reference_step(cfg)            # warm-up (weight build, thread pool, first Adam step)
             dt, n = cpu_reference_step(cfg)
-            fwd = n / dt
-            line['cpu_baseline'] = {
-                'value': fwd * STEP_FLOP_SHARE_OF_G_FWD, 'unit': UNIT, 'cores': cores, 'kind': 'port',
-                'sample': 'one generator forward (train mode, fp32), batch 1, 256x512 through the CPU oracle port '
-                          '(%.2f s); train img/s = forward img/s x F_G/(4F_G+4.5F_D+3F_VGG) = %.4f x %.4f'
-                          % (dt, fwd, STEP_FLOP_SHARE_OF_G_FWD)}
+            line['cpu_baseline'] = {'value': n / dt, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': CPU_SAMPLE % dt}
         print(json.dumps(line), flush=True)
     if use_graph:
         graphed.close()
