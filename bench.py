@@ -314,6 +314,11 @@ def cpu_reference_step(cfg, batch=1, seed=0):
     return time.perf_counter() - t0, batch
 
 
+# Algorithmic FLOPs per image (SURVEY.md section 3.1 / BASELINE.md section 3): one training
+# iteration = 4 F_G + 4.5 F_D + 3 F_VGG (GFLOP).
+F_G, F_D, F_VGG = 2883.0, 172.0, 102.0
+
+
 def run_reference(args):
     """Reference arm: the reference's own (CPU, PyTorch) implementation of the path, as ported in
     oracle/, timed on this box's host cores.  /root/reference is Python and does not travel;
