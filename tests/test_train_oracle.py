@@ -140,3 +140,27 @@ def test_generator_update_oracle_vs_reference_trainer(setup):
             diff = np.abs(H.subsample(ema[k]).numpy() - ref)
             assert np.mean(diff <= 1e-4 * np.abs(ref).max()) > 0.97, k
             assert _rel_l2(H.subsample(ema[k]), ref) < 5e-2, k
+
+
+def test_full_iteration_oracle_vs_reference_trainer(setup):
+    """train.py:76-79: dis_update then gen_update through the discriminator that has just stepped, then the moving
+    average.  The discriminator terms are held as tightly as above; the generator terms that pass through the stepped
+    discriminator are compared loosely (its first Adam step moves every weight by +-lr, so elements whose gradient is
+    fp32 rounding residue may step the other way in two fp32 evaluation orders), the others tightly."""
+    cfg, sd_g, sd_d, vgg, spec, d = setup
+    state = {'opt_d': {}, 'opt_g': {}, 'ema_updates': 0, 'ema_start': cfg.trainer.model_average_start_iteration,
+             'ema_beta': cfg.trainer.model_average_beta,
+             'ema': {k[len('ema_after.'):]: torch.zeros(1) for k in d if k.startswith('ema_after.')}}
+    dl, gl, g_after, d_after, state = to.train_iteration(sd_g, sd_d, vgg, H.c3mini_batch(), spec,
+                                                         torch.from_numpy(d['eps_dis']), torch.from_numpy(d['eps_gen']), state)
+    for k in ('GAN/fake', 'GAN/true', 'GAN', 'total'):
+        assert abs(dl[k] - float(d['dis_loss.' + k])) <= 1e-5 * max(1.0, abs(float(d['dis_loss.' + k]))), k
+    for k in ('GAN', 'FeatureMatching', 'GaussianKL', 'Perceptual', 'total'):
+        ref = float(d['seq_gen_loss.' + k])
+        tol = 1e-3 if k in ('GaussianKL', 'Perceptual') else 5e-2
+        assert abs(gl[k] - ref) <= tol * max(abs(ref), 1e-3), (k, gl[k], ref)
+    assert state['ema_updates'] == int(d['seq_ema_num_updates'])
+    # the generator's buffers moved twice (dis_update's forward, gen_update's forward); its parameters once
+    moved = [k for k in sd_g if to.is_parameter(k) and not torch.equal(sd_g[k], g_after[k])]
+    assert len(moved) > 0.9 * sum(to.is_parameter(k) for k in sd_g)
+    assert all(float((g_after[k] - sd_g[k]).abs().max()) <= cfg.gen_opt.lr * 1.001 for k in moved)
