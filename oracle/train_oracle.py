@@ -63,25 +63,25 @@ def fpse_discriminator(sd, prefix, images, segmaps, kernel_size, training):
     def up(t):                   # nn.Upsample(scale_factor=2, mode='bilinear', align_corners=False), :73-74
         return F.interpolate(t, scale_factor=2, mode='bilinear', align_corners=False)
 
-    feat11 = down('enc1', images)
-    feat12 = down('enc2', feat11)
-    feat13 = down('enc3', feat12)
-    feat14 = down('enc4', feat13)
-    feat15 = down('enc5', feat14)
-    feat25 = lat('lat5', feat15)
-    feat24 = up(feat25) + lat('lat4', feat14)
-    feat23 = up(feat24) + lat('lat3', feat13)
-    feat22 = up(feat23) + lat('lat2', feat12)
-    feats = [final('final2', feat22), final('final3', feat23), final('final4', feat24)]
+    # bottom-up: five stride-2 stages; top-down: 1x1 laterals added to the bilinearly upsampled coarser level
+    c = [images]
+    for i in range(1, 6):
+        c.append(down('enc%d' % i, c[-1]))
+    top = lat('lat5', c[5])
+    pyramid = {}
+    for level in (4, 3, 2):
+        top = up(top) + lat('lat%d' % level, c[level])
+        pyramid[level] = top
+    heads = [final('final%d' % level, pyramid[level]) for level in (2, 3, 4)]
     # true/false prediction and the semantic-alignment projection: plain 1x1 convolutions, no weight norm (:82-85)
-    preds = [conv_block(sd, prefix + 'output.', f, 1, 0, training, False) for f in feats]
-    segs = [conv_block(sd, prefix + 'seg.', f, 1, 0, training, False) for f in feats]
-    emb = conv_block(sd, prefix + 'embedding.', segmaps, 1, 0, training, False)
-    emb = F.avg_pool2d(emb, kernel_size=2, stride=2)
+    logits = [conv_block(sd, prefix + 'output.', h, 1, 0, training, False) for h in heads]
+    proj = [conv_block(sd, prefix + 'seg.', h, 1, 0, training, False) for h in heads]
+    # label embedding, average-pooled to each head's resolution (1/4, 1/8, 1/16 of the input)
+    emb = F.avg_pool2d(conv_block(sd, prefix + 'embedding.', segmaps, 1, 0, training, False), kernel_size=2, stride=2)
     out = []
-    for p, s in zip(preds, segs):
+    for logit, pr in zip(logits, proj):
         emb = F.avg_pool2d(emb, kernel_size=2, stride=2)
-        out.append(p + (emb * s).sum(dim=1, keepdim=True))
+        out.append(logit + (emb * pr).sum(dim=1, keepdim=True))
     return out
 
 
